@@ -1,0 +1,339 @@
+// go2_b200 - per-environment collision detection for the Go2 scene (28 convex primitives).
+//
+// Same contact model as the reference collider (MPR with warm-started centres + 4 perturbed
+// re-detections for non-sphere pairs; collider/mpr.py, collider/narrowphase.py:515-961,
+// collider/contact.py:165-370) with a GPU-friendly front end:
+//   * no sweep-and-prune: the valid pair list is a compile-time table; each pair gets a direct AABB test
+//     (same candidate set as collider/broadphase.py, canonical order instead of sort order);
+//   * the per-pair contact-normal cache (319 x vec3 per env in the reference) is stored compactly as the
+//     list of pairs that were in contact at the previous detection - equivalent because the reference
+//     zeroes a pair's cache entry whenever it is not in contact;
+//   * geom poses are derived on demand from link poses (never stored).
+#pragma once
+#include "go2_phys.cuh"
+
+namespace go2 {
+
+struct GeomPose {
+    v3 pos;
+    q4 quat;
+};
+
+G2_HD GeomPose geom_pose(const Go2Model& m, const Phys& p, int g) {
+    GeomPose r;
+    int l = m.g_link[g];
+    if (l < 0) {
+        r.pos = ld3(m.g_pos[g]);
+        r.quat = qnormalize(ld4(m.g_quat[g]));
+    } else {
+        r.pos = p.lpos[l] + qrot(ld3(m.g_pos[g]), p.lquat[l]);
+        r.quat = qcompose(ld4(m.g_quat[g]), p.lquat[l]);
+    }
+    return r;
+}
+
+// World AABBs from the oriented local box: centre +- |R| h  (== min/max over the 8 rotated corners).
+G2_HDN void geom_aabbs(const Go2Model& m, Phys& p) {
+    for (int g = 0; g < NGEOM; ++g) {
+        GeomPose gp = geom_pose(m, p, g);
+        m3 R = qmat(gp.quat);
+        v3 h = ld3(m.g_half[g]);
+        p.g_c[g] = gp.pos;
+        p.g_h[g] = mk3(fabsf(R.a[0][0]) * h.x + fabsf(R.a[0][1]) * h.y + fabsf(R.a[0][2]) * h.z,
+                       fabsf(R.a[1][0]) * h.x + fabsf(R.a[1][1]) * h.y + fabsf(R.a[1][2]) * h.z,
+                       fabsf(R.a[2][0]) * h.x + fabsf(R.a[2][1]) * h.y + fabsf(R.a[2][2]) * h.z);
+    }
+}
+
+// Support point of geom g (type/size from the model) posed at (pos, R) in world direction d.
+G2_HD v3 support(const Go2Model& m, int g, v3 pos, const m3& R, v3 d) {
+    int t = m.g_type[g];
+    if (t == GEOM_SPHERE) return pos + d * m.g_size[g][0];
+    v3 dl = mtmul(R, d);
+    v3 v;
+    if (t == GEOM_BOX) {
+        v = mk3(dl.x < 0.0f ? -m.g_half[g][0] : m.g_half[g][0], dl.y < 0.0f ? -m.g_half[g][1] : m.g_half[g][1],
+                dl.z < 0.0f ? -m.g_half[g][2] : m.g_half[g][2]);
+    } else {
+        // cylinder collision mesh = 32-gon prism: nearest ring vertex to the direction's azimuth
+        const float step = 6.283185307179586f / 32.0f;
+        float th = atan2f(dl.y, dl.x);
+        float k = floorf(th / step + 0.5f);
+        float s, c;
+#ifdef __CUDA_ARCH__
+        sincosf(k * step, &s, &c);
+#else
+        s = sinf(k * step); c = cosf(k * step);
+#endif
+        float r = m.g_size[g][0];
+        v = mk3(r * c, r * s, dl.z < 0.0f ? -m.g_half[g][2] : m.g_half[g][2]);
+    }
+    return pos + mmul(R, v);
+}
+
+struct PairCtx {
+    int ga, gb;
+    v3 pa, pb;
+    m3 Ra, Rb;
+};
+struct Portal {
+    v3 v[4], v1[4], v2[4];
+};
+
+G2_HD void mink_support(const Go2Model& m, const PairCtx& c, v3 d, v3& v, v3& v1, v3& v2) {
+    v1 = support(m, c.ga, c.pa, c.Ra, d);
+    v2 = support(m, c.gb, c.pb, c.Rb, -d);
+    v = v1 - v2;
+}
+G2_HD v3 portal_dir(const Portal& s) { return normalize3(cross(s.v[2] - s.v[1], s.v[3] - s.v[1])); }
+G2_HD bool reach_tol(const Portal& s, v3 v, v3 d) {
+    float dv4 = dot(v, d);
+    float d1 = fminf3(dv4 - dot(s.v[1], d), dv4 - dot(s.v[2], d), dv4 - dot(s.v[3], d));
+    return d1 < CCD_TOL + CCD_EPS * fmaxf(1.0f, d1);
+}
+G2_HD void expand_portal(Portal& s, v3 v, v3 v1, v3 v2) {
+    v3 v4v0 = cross(v, s.v[0]);
+    int i;
+    if (dot(s.v[1], v4v0) > 0.0f) i = dot(s.v[2], v4v0) > 0.0f ? 1 : 3;
+    else i = dot(s.v[3], v4v0) > 0.0f ? 2 : 1;
+    s.v[i] = v; s.v1[i] = v1; s.v2[i] = v2;
+}
+G2_HD bool tiny3(v3 a) { return fabsf(a.x) < CCD_EPS && fabsf(a.y) < CCD_EPS && fabsf(a.z) < CCD_EPS; }
+
+// Minkowski portal refinement.  Returns true on collision with (normal: b -> a, penetration, position).
+G2_HDN bool mpr(const Go2Model& m, const PairCtx& c, v3 ca, v3 cb, v3& normal, float& pen, v3& pos) {
+    Portal s;
+    s.v1[0] = ca; s.v2[0] = cb; s.v[0] = ca - cb;
+    if (tiny3(s.v[0])) s.v[0].x += 10.0f * CCD_EPS;
+    v3 d = -normalize3(s.v[0]);
+    v3 v, v1, v2;
+    mink_support(m, c, d, v, v1, v2);
+    s.v[1] = v; s.v1[1] = v1; s.v2[1] = v2;
+    if (dot(v, d) < CCD_EPS) return false;
+    d = cross(s.v[0], s.v[1]);
+    if (dot(d, d) < CCD_EPS) {
+        if (tiny3(s.v[1])) {  // touching at the origin
+            pen = 0.0f;
+            normal = -normalize3(s.v[0]);
+        } else {              // origin on the v0-v1 segment
+            pen = norm3(s.v[1]);
+            normal = -normalize3(s.v[1]);
+        }
+        pos = (s.v1[1] + s.v2[1]) * 0.5f;
+        return true;
+    }
+    d = normalize3(d);
+    mink_support(m, c, d, v, v1, v2);
+    if (dot(v, d) < CCD_EPS) return false;
+    s.v[2] = v; s.v1[2] = v1; s.v2[2] = v2;
+    d = normalize3(cross(s.v[1] - s.v[0], s.v[2] - s.v[0]));
+    if (dot(d, s.v[0]) > 0.0f) {
+        v3 t;
+        t = s.v[1]; s.v[1] = s.v[2]; s.v[2] = t;
+        t = s.v1[1]; s.v1[1] = s.v1[2]; s.v1[2] = t;
+        t = s.v2[1]; s.v2[1] = s.v2[2]; s.v2[2] = t;
+        d = -d;
+    }
+    // discover the portal
+    int trials = 0;
+    for (;;) {
+        mink_support(m, c, d, v, v1, v2);
+        if (dot(v, d) < CCD_EPS) return false;
+        bool again = false;
+        if (dot(cross(s.v[1], v), s.v[0]) < -CCD_EPS) {
+            s.v[2] = v; s.v1[2] = v1; s.v2[2] = v2;
+            again = true;
+        } else if (dot(cross(v, s.v[2]), s.v[0]) < -CCD_EPS) {
+            s.v[1] = v; s.v1[1] = v1; s.v2[1] = v2;
+            again = true;
+        }
+        if (!again) {
+            s.v[3] = v; s.v1[3] = v1; s.v2[3] = v2;
+            break;
+        }
+        d = normalize3(cross(s.v[1] - s.v[0], s.v[2] - s.v[0]));
+        if (++trials == 15) return false;
+    }
+    // refine until the portal encloses the origin
+    for (;;) {
+        d = portal_dir(s);
+        if (dot(s.v[1], d) > -CCD_EPS) break;
+        mink_support(m, c, d, v, v1, v2);
+        if (!(dot(v, d) > -CCD_EPS) || reach_tol(s, v, d)) return false;
+        expand_portal(s, v, v1, v2);
+    }
+    // penetration along the final portal normal
+    for (int it = 0;; ++it) {
+        d = portal_dir(s);
+        mink_support(m, c, d, v, v1, v2);
+        if (reach_tol(s, v, d) || it > CCD_ITERS) {
+            pen = dot(d, s.v[1]);
+            normal = -d;
+            float b1 = dot(cross(s.v[2], s.v[3]), d), b2 = dot(cross(s.v[3], s.v[1]), d), b3 = dot(cross(s.v[1], s.v[2]), d);
+            float inv = 0.5f / (b1 + b2 + b3);
+            pos = ((b1 * s.v1[1] + b2 * s.v1[2] + b3 * s.v1[3]) + (b1 * s.v2[1] + b2 * s.v2[2] + b3 * s.v2[3])) * inv;
+            return true;
+        }
+        expand_portal(s, v, v1, v2);
+    }
+}
+
+// Geometry centres used to seed MPR; with a cached normal the centres are slid inside their bounding
+// boxes so that the initial ray is aligned with it (collider/mpr.py:602-684).
+G2_HD void seed_centres(const Go2Model& m, const PairCtx& c, v3 nws, bool have, v3& ca, v3& cb) {
+    ca = c.pa;  // primitive centres coincide with the geom origin (local AABB is symmetric)
+    cb = c.pb;
+    if (have) {
+        v3 delta = ca - cb;
+        v3 nrm = normalize3(delta);
+        if (norm3(cross(nws, nrm)) > 0.01f) {
+            v3 off = dot(delta, nws) * nws - delta;
+            float on = norm3(off);
+            if (on > EPSF) {
+                v3 dir = off * (1.0f / on);
+                v3 da = mtmul(c.Ra, dir), db = mtmul(c.Rb, dir);
+                float la = 2.0f * (m.g_half[c.ga][0] * fabsf(da.x) + m.g_half[c.ga][1] * fabsf(da.y) + m.g_half[c.ga][2] * fabsf(da.z));
+                float lb = 2.0f * (m.g_half[c.gb][0] * fabsf(db.x) + m.g_half[c.gb][1] * fabsf(db.y) + m.g_half[c.gb][2] * fabsf(db.z));
+                float ratio = fminf(on / (la + lb), 0.5f);
+                ca = ca + dir * (la * ratio);
+                cb = cb - dir * (lb * ratio);
+            }
+        }
+    }
+}
+
+G2_HD void push_contact(const Go2Model& m, Phys& p, int ga, int gb, v3 n, v3 pos, float pen, float mu) {
+    if (p.n_contacts < MAX_CONTACTS) {
+        Contact& c = p.con[p.n_contacts++];
+        c.pos = pos; c.normal = n; c.pen = pen; c.mu = mu;
+        c.la = m.g_link[ga]; c.lb = m.g_link[gb];
+    } else {
+        p.err |= ERR_CONTACT_OVERFLOW;
+    }
+}
+
+G2_HD float aabb_diag(const Go2Model& m, int g) {
+    return 2.0f * sqrtf(m.g_half[g][0] * m.g_half[g][0] + m.g_half[g][1] * m.g_half[g][1] + m.g_half[g][2] * m.g_half[g][2]);
+}
+
+// One geom pair: first detection (+ up to 4 perturbed detections for non-sphere pairs).
+// `nws`/`have`: cached normal from the previous detection.  Returns whether the pair is in contact and
+// the normal to cache.
+G2_HDN bool pair_contacts(const Go2Model& m, Phys& p, int ga, int gb, v3 nws, bool have, float mu, v3& n_out) {
+    bool multi = m.g_type[ga] != GEOM_SPHERE && m.g_type[gb] != GEOM_SPHERE;
+    float tol = 0.5f * MC_TOL * fminf(aabb_diag(m, ga), aabb_diag(m, gb));
+    GeomPose A = geom_pose(m, p, ga), B = geom_pose(m, p, gb);
+    PairCtx c;
+    c.ga = ga; c.gb = gb; c.pa = A.pos; c.pb = B.pos; c.Ra = qmat(A.quat); c.Rb = qmat(B.quat);
+    v3 ca, cb, n0, pos0;
+    float pen0;
+    seed_centres(m, c, nws, have, ca, cb);
+    bool col0 = mpr(m, c, ca, cb, n0, pen0, pos0);
+    if (!col0 && have) {  // retry without the warm start (narrowphase.py:690-700)
+        seed_centres(m, c, nws, false, ca, cb);
+        col0 = mpr(m, c, ca, cb, n0, pen0, pos0);
+        have = false;
+    }
+    if (!col0) return false;
+    n_out = n0;
+    int first = p.n_contacts;
+    push_contact(m, p, ga, gb, n0, pos0, pen0, mu);
+    if (!multi) return true;
+    // perturbation axes: mix the principal axes of the smaller geom's link inertia with the normal
+    v3 ax0, ax1;
+    {
+        float va = m.g_half[ga][0] * m.g_half[ga][1] * m.g_half[ga][2], vb = m.g_half[gb][0] * m.g_half[gb][1] * m.g_half[gb][2];
+        int l = m.g_link[va < vb ? ga : gb];
+        m3 R;
+        if (l < 0) { q4 id = mk4(1, 0, 0, 0); R = qmat(id); }
+        else R = qmat(qcompose(ld4(m.inertial_quat[l]), p.lquat[l]));
+        int best = 0;
+        float amax = 0.0f;
+        for (int i = 0; i < 3; ++i) {
+            float a = fabsf(dot(mcol(R, i), n0));
+            if (a > amax) { amax = a; best = i; }
+        }
+        ax0 = mcol(R, (best + 1) % 3);
+        ax0 = normalize3(ax0 - dot(n0, ax0) * n0);
+        ax1 = cross(n0, ax0);
+    }
+    int n_pair = 1;
+    for (int k = 1; k < 5; ++k) {
+        v3 axis = (float)(2 * (k % 2) - 1) * ax0 + (float)(1 - 2 * ((k / 2) % 2)) * ax1;
+        q4 qr = rotvec_quat(axis * MC_PERTURB);
+        q4 qri = qconj(qr);
+        // rotate both geoms about the first contact point, in opposite directions
+        PairCtx cp = c;
+        {
+            q4 qa = qcompose(A.quat, qr);
+            v3 rel = pos0 - A.pos;
+            cp.pa = A.pos - (qrot(rel, qr) - rel);
+            cp.Ra = qmat(qa);
+            q4 qb = qcompose(B.quat, qri);
+            rel = pos0 - B.pos;
+            cp.pb = B.pos - (qrot(rel, qri) - rel);
+            cp.Rb = qmat(qb);
+        }
+        v3 n, pos;
+        float pen;
+        seed_centres(m, cp, n0, true, ca, cb);  // the cache already holds this detection's first normal
+        if (!mpr(m, cp, ca, cb, n, pen, pos)) continue;
+        // undo the perturbation on the two surface points, first-order normal correction
+        v3 pA = qrot((pos - 0.5f * pen * n) - pos0, qri) + pos0;
+        v3 pB = qrot((pos + 0.5f * pen * n) - pos0, qr) + pos0;
+        pos = 0.5f * (pA + pB);
+        v3 tw = cross(n, n0);
+        tw = mk3(clampf(tw.x, -MC_PERTURB, MC_PERTURB), clampf(tw.y, -MC_PERTURB, MC_PERTURB), clampf(tw.z, -MC_PERTURB, MC_PERTURB));
+        n = n + cross(tw, n);
+        pen = dot(n, pB - pA);
+        bool rep = false;
+        for (int i = 0; i < n_pair && !rep; ++i) {
+            int idx = p.n_contacts - 1 - i;
+            if (idx >= first && norm3(pos - p.con[idx].pos) < tol) rep = true;
+        }
+        if (!rep && pen > -tol) {
+            push_contact(m, p, ga, gb, n, pos, fmaxf(pen, 0.0f), mu);
+            n_pair++;
+        }
+    }
+    return true;
+}
+
+// Full detection for one env: AABBs -> static pair table -> narrow phase; rebuilds the normal cache.
+G2_HDN void detect_collisions(const Go2Model& m, Phys& p, float friction) {
+    geom_aabbs(m, p);
+    p.n_contacts = 0;
+    int n_new = 0;
+    int new_pair[MAX_CPAIRS];
+    v3 new_n[MAX_CPAIRS];
+    float mu = fmaxf(friction, 1e-2f);  // max(mu_a, mu_b, 0.01); the envs set one global mu on every geom
+    for (int ip = 0; ip < m.npairs; ++ip) {
+        int a = m.pair_a[ip], b = m.pair_b[ip];
+        v3 dc = p.g_c[a] - p.g_c[b], hs = p.g_h[a] + p.g_h[b];
+        if (!(fabsf(dc.x) < hs.x && fabsf(dc.y) < hs.y && fabsf(dc.z) < hs.z)) continue;
+        // narrow phase wants the lower geom type first (sphere < cylinder < box)
+        int ga = a, gb = b;
+        if (m.g_type[ga] > m.g_type[gb]) { ga = b; gb = a; }
+        v3 nws = mk3(0, 0, 0);
+        bool have = false;
+        for (int k = 0; k < p.n_cache; ++k)
+            if (p.cache_pair[k] == ip) { nws = p.cache_n[k]; have = true; }
+        v3 n;
+        if (pair_contacts(m, p, ga, gb, nws, have, mu, n)) {
+            if (n_new < MAX_CPAIRS) {
+                new_pair[n_new] = ip;
+                new_n[n_new] = n;
+                n_new++;
+            } else {
+                p.err |= ERR_CPAIR_OVERFLOW;
+            }
+        }
+    }
+    p.n_cache = n_new;
+    for (int k = 0; k < n_new; ++k) {
+        p.cache_pair[k] = new_pair[k];
+        p.cache_n[k] = new_n[k];
+    }
+}
+
+}  // namespace go2

@@ -1,0 +1,582 @@
+// go2_b200 - one fused environment step for one env (host+device; the CUDA kernel calls this per thread).
+//
+// Covers, in the reference's order (examples/locomotion/final/go2_env_walk.py:985-1109 and
+// go2_env_base.py:123-192): action clip + delay ring, PLS / fixed-gain / solver-side PD torque law with
+// torque clamp, push forces, `substeps` rigid substeps, state read-back, foot contacts, command
+// resampling, termination, every reward term (+episode sums), reset with domain-randomisation draws,
+// observation + privileged observation assembly with noise.  Walk/stair: termination -> rewards ->
+// reset -> obs.  Base: termination -> reset -> rewards -> obs.
+#pragma once
+#include "go2_buffers.cuh"
+#include "go2_solve.cuh"
+
+namespace go2 {
+
+#define F32(id) ((float*)bf.p[id])
+#define I32(id) ((int*)bf.p[id])
+#define U8(id) ((uint8_t*)bf.p[id])
+
+enum RngSlot { SLOT_ACT_NOISE = 0, SLOT_OBS_NOISE = 8, SLOT_PUSH = 32, SLOT_CMD = 33, SLOT_CMD_RESET = 34, SLOT_RESET = 40 };
+
+struct EnvStepOut {
+    int reset, timeout;
+    float tracking_per_sec;
+    float ep_stat[MAX_REW];
+};
+
+struct Rng {
+    uint32_t env, step, k0, k1;
+};
+G2_HD u4 rng4(const Rng& r, uint32_t slot) { return philox(r.env, r.step, slot, 0u, r.k0, r.k1); }
+G2_HD float urange(float lo, float hi, uint32_t x) { return (hi - lo) * u01(x) + lo; }
+
+// quaternion -> extrinsic roll/pitch/yaw in degrees (genesis/utils/geom.py:718-775 with rpy=True)
+G2_HD v3 quat_to_rpy_deg(q4 q) {
+    float ww = q.w * q.w, wx = q.w * q.x, wy = q.w * q.y, wz = q.w * q.z;
+    float xx = q.x * q.x, xy = q.x * q.y, xz = q.x * q.z, yy = q.y * q.y, yz = q.y * q.z, zz = q.z * q.z;
+    float sinp = wy - xz, sinrcosp = wx + yz, sinycosp = wz + xy;
+    float cosrcosp = (ww - xx - yy + zz) * 0.5f, cosycosp = (ww + xx - yy - zz) * 0.5f;
+    float cosp = sqrtf(cosycosp * cosycosp + sinycosp * sinycosp);
+    float r = atan2f(sinrcosp, cosrcosp), pch = atan2f(sinp, cosp), y = atan2f(sinycosp, cosycosp);
+    if (cosp < EPSF) {
+        r = 0.0f;
+        y = atan2f(wz - xy, (ww - xx + yy - zz) * 0.5f);
+    }
+    const float k = 57.29577951308232f;
+    return mk3(r * k, pch * k, y * k);
+}
+
+G2_HD void load_phys(const Buffers& bf, int b, Phys& p) {
+    int B = bf.B;
+    for (int i = 0; i < NQ; ++i) p.qpos[i] = F32(B_QPOS)[i * B + b];
+    for (int i = 0; i < NV; ++i) p.qvel[i] = F32(B_QVEL)[i * B + b];
+    for (int i = 0; i < NV; ++i) p.qacc_ws[i] = F32(B_QACC_WS)[i * B + b];
+    p.warm = I32(B_WARM)[b];
+    int nc = I32(B_NCACHE)[b];
+    p.n_cache = nc;
+    for (int k = 0; k < nc; ++k) {
+        p.cache_pair[k] = I32(B_CACHE_PAIR)[k * B + b];
+        p.cache_n[k] = mk3(F32(B_CACHE_N)[(3 * k) * B + b], F32(B_CACHE_N)[(3 * k + 1) * B + b], F32(B_CACHE_N)[(3 * k + 2) * B + b]);
+    }
+    p.err = 0;
+    p.cost = 0.0f;
+    p.pd_mode = 0; p.pd_kp = 0.0f; p.pd_kv = 0.0f;
+    for (int l = 0; l < NLINK; ++l) p.cforce[l] = mk3(0, 0, 0);
+    p.n_contacts = 0;
+    p.n_rows = 0;
+    p.n_newton = 0;
+}
+G2_HD void store_phys(const Buffers& bf, int b, const Phys& p) {
+    int B = bf.B;
+    for (int i = 0; i < NQ; ++i) F32(B_QPOS)[i * B + b] = p.qpos[i];
+    for (int i = 0; i < NV; ++i) F32(B_QVEL)[i * B + b] = p.qvel[i];
+    for (int i = 0; i < NV; ++i) F32(B_QACC_WS)[i * B + b] = p.qacc_ws[i];
+    I32(B_WARM)[b] = p.warm;
+    I32(B_NCACHE)[b] = p.n_cache;
+    for (int k = 0; k < p.n_cache; ++k) {
+        I32(B_CACHE_PAIR)[k * B + b] = p.cache_pair[k];
+        F32(B_CACHE_N)[(3 * k) * B + b] = p.cache_n[k].x;
+        F32(B_CACHE_N)[(3 * k + 1) * B + b] = p.cache_n[k].y;
+        F32(B_CACHE_N)[(3 * k + 2) * B + b] = p.cache_n[k].z;
+    }
+}
+
+G2_HD v3 link_vel_world(const Phys& p, int l) { return p.cd_v[l] + cross(p.cd_a[l], p.lpos[l] - p.root_com); }
+
+G2_HD void resample_commands(const EnvConfig& cfg, const StepParams& sp, const Rng& rng, uint32_t slot, int gid, float* cmd) {
+    u4 r = rng4(rng, slot);
+    if (cfg.compound_commands) {
+        cmd[0] = urange(sp.cmd_lo[0], sp.cmd_hi[0], r.a);
+        cmd[1] = urange(sp.cmd_lo[1], sp.cmd_hi[1], r.b);
+        cmd[2] = urange(sp.cmd_lo[2], sp.cmd_hi[2], r.c);
+    } else {
+        int choice = (int)(r.d % 3u);
+        cmd[0] = cmd[1] = cmd[2] = 0.0f;
+        uint32_t rr = choice == 0 ? r.a : (choice == 1 ? r.b : r.c);
+        cmd[choice] = urange(sp.cmd_lo[choice], sp.cmd_hi[choice], rr);
+    }
+    if (gid < cfg.n_standing) cmd[0] = cmd[1] = cmd[2] = 0.0f;
+}
+
+// Everything the step needs from the env-level buffers, held in registers / local memory.
+struct EnvLocal {
+    float act[NACT_MAX], last_act[NACT_MAX], applied[NACT_MAX];
+    float dof_pos[NHINGE], dof_vel[NHINGE], last_dof_vel[NHINGE], target[NHINGE], torque[NHINGE];
+    float cmd[3];
+    v3 base_pos, lin_vel, ang_vel, proj_g, euler, vel_world;
+    q4 base_quat;
+    float air[4];
+    int fc[4], lfc[4];
+    int ep_len;
+};
+
+G2_HDN float reward_term(int id, const Go2Model& m, const EnvConfig& cfg, const Phys& p, EnvLocal& e) {
+    const float dt = 0.02f;
+    switch (id) {
+        case R_TRACKING_LIN_VEL: {
+            float ex = e.cmd[0] - e.lin_vel.x, ey = e.cmd[1] - e.lin_vel.y;
+            return expf(-(ex * ex + ey * ey) / cfg.tracking_sigma);
+        }
+        case R_TRACKING_ANG_VEL: {
+            float ez = e.cmd[2] - e.ang_vel.z;
+            return expf(-(ez * ez) / cfg.tracking_sigma);
+        }
+        case R_LIN_VEL_Z: return e.lin_vel.z * e.lin_vel.z;
+        case R_BASE_HEIGHT: { float d = e.base_pos.z - cfg.base_height_target; return d * d; }
+        case R_ACTION_RATE: {
+            float s = 0.0f;
+            for (int i = 0; i < cfg.num_actions; ++i) { float d = e.last_act[i] - e.act[i]; s += d * d; }
+            return s;
+        }
+        case R_SIMILAR_TO_DEFAULT: {
+            float s = 0.0f;
+            for (int i = 0; i < NHINGE; ++i) s += fabsf(e.dof_pos[i] - cfg.default_dof_pos[i]);
+            return s;
+        }
+        case R_ORIENTATION_PENALTY: return e.proj_g.x * e.proj_g.x + e.proj_g.y * e.proj_g.y;
+        case R_DOF_ACC: {
+            float s = 0.0f;
+            for (int i = 0; i < NHINGE; ++i) { float d = (e.dof_vel[i] - e.last_dof_vel[i]) / dt; s += d * d; }
+            return s;
+        }
+        case R_DOF_VEL: {
+            float s = 0.0f;
+            for (int i = 0; i < NHINGE; ++i) s += e.dof_vel[i] * e.dof_vel[i];
+            return s;
+        }
+        case R_ANG_VEL_XY: return e.ang_vel.x * e.ang_vel.x + e.ang_vel.y * e.ang_vel.y;
+        case R_FEET_AIR_TIME: {
+            float rew = 0.0f;
+            for (int i = 0; i < 4; ++i) {
+                bool first = e.air[i] > 0.0f && e.fc[i];
+                e.air[i] += dt;
+                e.air[i] *= e.fc[i] ? 0.0f : 1.0f;
+                rew += (e.air[i] - cfg.feet_air_time_target) * (first ? 1.0f : 0.0f);
+            }
+            float mv = sqrtf(e.cmd[0] * e.cmd[0] + e.cmd[1] * e.cmd[1]) > 0.1f ? 1.0f : 0.0f;
+            return rew * mv;
+        }
+        case R_FOOT_SLIP: {
+            float s = 0.0f;
+            for (int i = 0; i < 4; ++i) {
+                v3 v = link_vel_world(p, cfg.foot_link[i]);
+                s += (e.fc[i] ? 1.0f : 0.0f) * (v.x * v.x + v.y * v.y);
+            }
+            return s;
+        }
+        case R_FOOT_CLEARANCE: {
+            float s = 0.0f;
+            for (int i = 0; i < 4; ++i) {
+                int l = cfg.foot_link[i];
+                v3 v = link_vel_world(p, l);
+                float he = cfg.feet_height_target - p.lpos[l].z;
+                s += (e.fc[i] ? 0.0f : 1.0f) * (he * he) * sqrtf(v.x * v.x + v.y * v.y);
+            }
+            float mv = sqrtf(e.cmd[0] * e.cmd[0] + e.cmd[1] * e.cmd[1]) > 0.1f ? 1.0f : 0.0f;
+            return s * mv;
+        }
+        case R_JOINT_TRACKING: {
+            float s = 0.0f;
+            for (int i = 0; i < NHINGE; ++i) { float d = e.target[i] - e.dof_pos[i]; s += d * d; }
+            return s;
+        }
+        case R_ENERGY: {
+            float s = 0.0f;
+            for (int i = 0; i < NHINGE; ++i) s += fabsf(e.torque[i] * e.dof_vel[i]);
+            return s;
+        }
+        case R_TORQUE_LOAD: {
+            float s = 0.0f;
+            for (int i = 0; i < NHINGE; ++i) s += fabsf(e.torque[i]);
+            return cfg.kind == ENV_BASE ? -0.001f * s : s;
+        }
+        case R_STAND_STILL: {
+            float cn = sqrtf(e.cmd[0] * e.cmd[0] + e.cmd[1] * e.cmd[1] + e.cmd[2] * e.cmd[2]);
+            float s = 0.0f;
+            for (int i = 0; i < NHINGE; ++i) s += fabsf(e.dof_pos[i] - cfg.default_dof_pos[i]);
+            return s * (cn < 0.1f ? 1.0f : 0.0f);
+        }
+        case R_STAND_STILL_VEL: {
+            float cn = sqrtf(e.cmd[0] * e.cmd[0] + e.cmd[1] * e.cmd[1] + e.cmd[2] * e.cmd[2]);
+            float lv = e.lin_vel.x * e.lin_vel.x + e.lin_vel.y * e.lin_vel.y;
+            return (lv + 0.5f * e.ang_vel.z * e.ang_vel.z) * (cn < 0.1f ? 1.0f : 0.0f);
+        }
+        case R_FEET_STANCE: {
+            float cn = sqrtf(e.cmd[0] * e.cmd[0] + e.cmd[1] * e.cmd[1] + e.cmd[2] * e.cmd[2]);
+            float s = 0.0f;
+            for (int i = 0; i < 4; ++i) s += e.air[i];
+            for (int i = 0; i < 4; ++i) s += e.fc[i] ? 0.0f : 1.0f;
+            return s * (cn < 0.1f ? 1.0f : 0.0f);
+        }
+        // ---- base env (crouch / jump), go2_env_base.py:246-390
+        case R_JUMP_IMPULSE: return (e.base_pos.z < 0.50f ? 1.0f : 0.0f) * fmaxf(e.lin_vel.z, 0.0f);
+        case R_JUMP_APEX: { float d = (e.base_pos.z - cfg.rp[0]) / cfg.rp[1]; return expf(-(d * d)); }
+        case R_XY_STABILITY: return -(e.vel_world.x * e.vel_world.x + e.vel_world.y * e.vel_world.y);
+        case R_ORIENTATION: return -e.proj_g.z;
+        case R_NO_SHAKE: return -(e.ang_vel.x * e.ang_vel.x + e.ang_vel.y * e.ang_vel.y + e.ang_vel.z * e.ang_vel.z) / 1.0f;
+        case R_CROUCH: return e.base_pos.z < 0.25f ? 1.0f : 0.0f;
+        case R_CROUCH_2: return (e.base_pos.z <= 0.30f && e.base_pos.z >= 0.20f) ? 1.0f : 0.0f;
+        case R_GROUND_PENALTY: { float x = clampf((0.15f - e.base_pos.z) / (0.15f - 0.05f), 0.0f, 1.0f); return -(x * x); }
+        case R_CROUCH_TARGET: { float d = (e.base_pos.z - 0.15f) / 0.03f; return expf(-(d * d)); }
+        case R_NO_FALL: { float dn = fmaxf(-e.lin_vel.z - 0.5f, 0.0f); return -(dn * dn); }
+        case R_Y_STABILITY: return -(e.vel_world.y * e.vel_world.y);
+        case R_CROUCH_PROGRESS: return fmaxf(0.35f - e.base_pos.z, 0.0f);
+        case R_CROUCH_SPEED: return -(e.lin_vel.z * e.lin_vel.z);
+        default: return 0.0f;
+    }
+}
+
+// Reset of one env (walk: go2_env_walk.py:1156-1240; base: go2_env_base.py:201-238).
+G2_HDN void reset_env(const Go2Model& m, const EnvConfig& cfg, const StepParams& sp, const Buffers& bf, int b, const Rng& rng,
+                      Phys& p, EnvLocal& e, EnvStepOut& out) {
+    const float dt = 0.02f;
+    int A = cfg.num_actions;
+    if (cfg.kind != ENV_BASE) {
+        // per-episode domain randomisation (per-env draws; the global ones are host-side scalars)
+        if (cfg.ctrl == CTRL_MANUAL_PLS || cfg.ctrl == CTRL_MANUAL_FIXED) {
+            for (int k = 0; k < 3; ++k) {
+                u4 r1 = rng4(rng, SLOT_RESET + k), r2 = rng4(rng, SLOT_RESET + 3 + k);
+                uint32_t a1[4] = {r1.a, r1.b, r1.c, r1.d}, a2[4] = {r2.a, r2.b, r2.c, r2.d};
+                for (int j = 0; j < 4; ++j) {
+                    if (cfg.has_kp_factor) F32(B_KP_FACTORS)[b * NHINGE + 4 * k + j] = urange(sp.kpf_lo, sp.kpf_hi, a1[j]);
+                    if (cfg.has_kd_factor) F32(B_KD_FACTORS)[b * NHINGE + 4 * k + j] = urange(sp.kdf_lo, sp.kdf_hi, a2[j]);
+                }
+            }
+        }
+        if (cfg.ctrl == CTRL_MANUAL_FIXED && cfg.has_kp_range) {  // go2_env_walk.py:775-795
+            u4 r = rng4(rng, SLOT_RESET + 11);
+            float kp = urange(sp.kp_lo, sp.kp_hi, r.a), kd = urange(sp.kd_lo, sp.kd_hi, r.b);
+            for (int j = 0; j < NHINGE; ++j) {
+                F32(B_EFF_KP)[b * NHINGE + j] = kp * F32(B_KP_FACTORS)[b * NHINGE + j];
+                F32(B_EFF_KD)[b * NHINGE + j] = kd * F32(B_KD_FACTORS)[b * NHINGE + j];
+            }
+        }
+        if (cfg.has_motor_strength) {
+            for (int k = 0; k < 3; ++k) {
+                u4 r = rng4(rng, SLOT_RESET + 6 + k);
+                uint32_t a[4] = {r.a, r.b, r.c, r.d};
+                for (int j = 0; j < 4; ++j) F32(B_MOTOR_STRENGTH)[b * NHINGE + 4 * k + j] = urange(sp.ms_lo, sp.ms_hi, a[j]);
+            }
+        }
+        u4 rg = rng4(rng, SLOT_RESET + 9);
+        if (cfg.has_gravity_offset) {
+            F32(B_GRAV_OFF)[b * 3 + 0] = urange(sp.go_lo, sp.go_hi, rg.a);
+            F32(B_GRAV_OFF)[b * 3 + 1] = urange(sp.go_lo, sp.go_hi, rg.b);
+            F32(B_GRAV_OFF)[b * 3 + 2] = urange(sp.go_lo, sp.go_hi, rg.c);
+        }
+        I32(B_DELAY)[b] = sp.delay_lo + (int)(rg.d % (uint32_t)(sp.delay_hi - sp.delay_lo + 1));
+    }
+    // joint + base state
+    for (int j = 0; j < NHINGE; ++j) {
+        e.dof_pos[j] = cfg.default_dof_pos[j];
+        e.dof_vel[j] = 0.0f;
+        p.qpos[cfg.motors_dof[j] + 1] = cfg.default_dof_pos[j];
+    }
+    for (int d = 0; d < NV; ++d) p.qvel[d] = 0.0f;
+    e.base_pos = ld3(cfg.base_init_pos);
+    e.base_quat = ld4(cfg.base_init_quat);
+    u4 rp = rng4(rng, SLOT_RESET + 10);
+    if (cfg.has_init_z) e.base_pos.z = urange(cfg.init_z_lo, cfg.init_z_hi, rp.a);
+    if (cfg.has_init_euler) {
+        float roll = urange(cfg.init_euler_lo, cfg.init_euler_hi, rp.b), pitch = urange(cfg.init_euler_lo, cfg.init_euler_hi, rp.c);
+        float cr = cosf(roll * 0.5f), sr = sinf(roll * 0.5f), cp = cosf(pitch * 0.5f), sp_ = sinf(pitch * 0.5f);
+        e.base_quat = mk4(cr * cp, sr * cp, cr * sp_, -sr * sp_);  // yaw = 0
+    }
+    p.qpos[0] = e.base_pos.x; p.qpos[1] = e.base_pos.y; p.qpos[2] = e.base_pos.z;
+    p.qpos[3] = e.base_quat.w; p.qpos[4] = e.base_quat.x; p.qpos[5] = e.base_quat.y; p.qpos[6] = e.base_quat.z;
+    e.lin_vel = mk3(0, 0, 0);
+    e.ang_vel = mk3(0, 0, 0);
+    e.vel_world = mk3(0, 0, 0);
+    for (int i = 0; i < A; ++i) e.last_act[i] = 0.0f;
+    for (int j = 0; j < NHINGE; ++j) e.last_dof_vel[j] = 0.0f;
+    if (cfg.kind != ENV_BASE) {
+        for (int i = 0; i < A; ++i) e.applied[i] = 0.0f;
+        for (int i = 0; i < cfg.hist_size * A; ++i) F32(B_HIST)[b * cfg.hist_size * A + i] = 0.0f;
+        if (cfg.has_push) {
+            F32(B_PUSH_FORCE)[b * 3 + 0] = F32(B_PUSH_FORCE)[b * 3 + 1] = F32(B_PUSH_FORCE)[b * 3 + 2] = 0.0f;
+            I32(B_PUSH_REMAIN)[b] = 0;
+        }
+        for (int i = 0; i < 4; ++i) { e.air[i] = 0.0f; e.fc[i] = 0; e.lfc[i] = 0; }
+    }
+    // episode statistics, then clear the sums
+    float ep_s = fmaxf((float)e.ep_len, 1.0f) * dt;
+    out.tracking_per_sec = 0.0f;
+    for (int k = 0; k < cfg.n_rew; ++k) {
+        float s = F32(B_EP_SUMS)[k * bf.B + b];
+        out.ep_stat[k] = cfg.kind == ENV_BASE ? s : s / ep_s;
+        if (cfg.rew_id[k] == R_TRACKING_LIN_VEL || cfg.rew_id[k] == R_TRACKING_ANG_VEL) out.tracking_per_sec += s / ep_s;
+        F32(B_EP_SUMS)[k * bf.B + b] = 0.0f;
+    }
+    e.ep_len = 0;
+    resample_commands(cfg, sp, rng, SLOT_CMD_RESET, cfg.env_offset + b, e.cmd);
+}
+
+// One control tick of env b.  `actions` is batch-first [B][A].
+G2_HDN void env_step(const Go2Model& m, const EnvConfig& cfg, const StepParams& sp, const Buffers& bf, const float* actions, int b,
+                     Phys& p, EnvStepOut& out) {
+    const int A = cfg.num_actions, H = cfg.hist_size;
+    Rng rng;
+    rng.env = (uint32_t)(cfg.env_offset + b); rng.step = sp.step_count; rng.k0 = cfg.seed_lo; rng.k1 = cfg.seed_hi;
+    EnvLocal e;
+    out.reset = 0; out.timeout = 0; out.tracking_per_sec = 0.0f;
+    load_phys(bf, b, p);
+    kinematics(m, sp.mass_shift, sp.com_shift, p);
+    velocities(m, p);
+    for (int i = 0; i < A; ++i) e.last_act[i] = F32(B_LAST_ACTIONS)[b * A + i];
+    for (int j = 0; j < NHINGE; ++j) {
+        e.dof_pos[j] = F32(B_DOF_POS)[b * NHINGE + j];
+        e.dof_vel[j] = F32(B_DOF_VEL)[b * NHINGE + j];
+        e.last_dof_vel[j] = F32(B_LAST_DOF_VEL)[b * NHINGE + j];
+        e.target[j] = 0.0f;
+        e.torque[j] = 0.0f;
+    }
+    for (int i = 0; i < 3; ++i) e.cmd[i] = F32(B_COMMANDS)[b * 3 + i];
+    e.ep_len = I32(B_EP_LEN)[b];
+    for (int i = 0; i < 4; ++i) { e.air[i] = 0.0f; e.fc[i] = 0; e.lfc[i] = 0; }
+    if (cfg.has_foot_tracking) {
+        for (int i = 0; i < 4; ++i) { e.air[i] = F32(B_AIR_TIME)[b * 4 + i]; e.fc[i] = U8(B_FOOT_CONTACT)[b * 4 + i]; }
+    }
+    p.ext_link = -1;
+    p.ext_f = mk3(0, 0, 0);
+    p.ext_t = mk3(0, 0, 0);
+    for (int d = 0; d < NV; ++d) { p.ctrl_force[d] = 0.0f; p.ctrl_pos[d] = 0.0f; }
+
+    if (sp.do_physics) {
+        for (int i = 0; i < A; ++i) e.act[i] = clampf(actions[b * A + i], -cfg.clip_actions, cfg.clip_actions);
+        if (cfg.kind != ENV_BASE) {
+            // ---- action delay ring (shared write index, per-env delay)
+            float* hist = F32(B_HIST) + (size_t)b * H * A;
+            for (int i = 0; i < A; ++i) hist[sp.hist_write_idx * A + i] = e.act[i];
+            int delay = I32(B_DELAY)[b];
+            int rd = ((sp.hist_write_idx - delay) % H + H) % H;
+            for (int i = 0; i < A; ++i) e.applied[i] = hist[rd * A + i];
+            // ---- position targets (+ action noise)
+            float noise[NHINGE];
+            for (int j = 0; j < NHINGE; ++j) noise[j] = 0.0f;
+            if (sp.action_noise_std > 0.0f) {
+                for (int k = 0; k < 3; ++k) {
+                    u4 r = rng4(rng, SLOT_ACT_NOISE + k);
+                    boxmuller(r.a, r.b, noise[4 * k], noise[4 * k + 1]);
+                    boxmuller(r.c, r.d, noise[4 * k + 2], noise[4 * k + 3]);
+                }
+            }
+            for (int j = 0; j < NHINGE; ++j)
+                e.target[j] = e.applied[j] * cfg.action_scale + cfg.default_dof_pos[j] + noise[j] * sp.action_noise_std;
+            if (cfg.ctrl == CTRL_GENESIS_PD) {
+                p.pd_mode = 1; p.pd_kp = sp.kp_genesis; p.pd_kv = sp.kd_genesis;
+                for (int j = 0; j < NHINGE; ++j) p.ctrl_pos[cfg.motors_dof[j]] = e.target[j];
+            } else {
+                p.pd_mode = 0;
+                for (int j = 0; j < NHINGE; ++j) {
+                    float ekp, ekd;
+                    if (cfg.ctrl == CTRL_MANUAL_PLS) {
+                        float kp = clampf(cfg.pls_kp_default + e.applied[cfg.num_pos_actions + j / 3] * cfg.pls_kp_scale, cfg.pls_kp_lo, cfg.pls_kp_hi);
+                        float kd = 0.2f * sqrtf(kp);
+                        ekp = kp * F32(B_KP_FACTORS)[b * NHINGE + j] * F32(B_MOTOR_STRENGTH)[b * NHINGE + j];
+                        ekd = kd * F32(B_KD_FACTORS)[b * NHINGE + j];
+                        F32(B_EFF_KP)[b * NHINGE + j] = ekp;
+                        F32(B_EFF_KD)[b * NHINGE + j] = ekd;
+                    } else {
+                        ekp = F32(B_EFF_KP)[b * NHINGE + j];
+                        ekd = F32(B_EFF_KD)[b * NHINGE + j];
+                    }
+                    float tq = ekp * (e.target[j] - e.dof_pos[j]) - ekd * e.dof_vel[j];
+                    tq = clampf(tq, -cfg.torque_limit[j], cfg.torque_limit[j]);
+                    p.ctrl_force[cfg.motors_dof[j]] = tq;
+                }
+            }
+            // ---- pushes (go2_env_walk.py:872-906): force at the link origin, world frame
+            v3 cur = mk3(0, 0, 0);
+            if (cfg.has_push && sp.push_enable) {
+                if (sp.push_resample) {
+                    u4 r = rng4(rng, SLOT_PUSH);
+                    F32(B_PUSH_FORCE)[b * 3 + 0] = urange(sp.push_lo, sp.push_hi, r.a);
+                    F32(B_PUSH_FORCE)[b * 3 + 1] = urange(sp.push_lo, sp.push_hi, r.b);
+                    F32(B_PUSH_FORCE)[b * 3 + 2] = 0.0f;
+                    I32(B_PUSH_REMAIN)[b] = cfg.push_dur_lo + (int)(r.c % (uint32_t)(cfg.push_dur_hi - cfg.push_dur_lo + 1));
+                }
+                int rem = I32(B_PUSH_REMAIN)[b];
+                float on = rem > 0 ? 1.0f : 0.0f;
+                cur = mk3(F32(B_PUSH_FORCE)[b * 3] * on, F32(B_PUSH_FORCE)[b * 3 + 1] * on, F32(B_PUSH_FORCE)[b * 3 + 2] * on);
+                I32(B_PUSH_REMAIN)[b] = rem - 1 > 0 ? rem - 1 : 0;
+                p.ext_link = cfg.push_link;
+                p.ext_f = cur;
+                p.ext_t = cross(p.lpos[cfg.push_link] - p.root_com, cur);
+            }
+            if (cfg.has_push) { F32(B_CUR_PUSH)[b * 3] = cur.x; F32(B_CUR_PUSH)[b * 3 + 1] = cur.y; F32(B_CUR_PUSH)[b * 3 + 2] = cur.z; }
+        } else {
+            // base env: 1-step latency through last_actions, PD evaluated inside every substep
+            p.pd_mode = 1; p.pd_kp = sp.kp_genesis; p.pd_kv = sp.kd_genesis;
+            for (int j = 0; j < NHINGE; ++j) {
+                float ex = cfg.simulate_action_latency ? e.last_act[j] : e.act[j];
+                e.target[j] = ex * cfg.action_scale + cfg.default_dof_pos[j];
+                p.ctrl_pos[cfg.motors_dof[j]] = e.target[j];
+            }
+        }
+        // ---- physics
+        substep(m, p, sp.friction, sp.mass_shift, sp.com_shift);
+        substep(m, p, sp.friction, sp.mass_shift, sp.com_shift);
+        e.ep_len += 1;
+        // ---- read-back
+        e.base_pos = p.lpos[0];
+        e.base_quat = p.lquat[0];
+        e.euler = quat_to_rpy_deg(qnormalize(qmul(e.base_quat, ld4(cfg.inv_base_init_quat))));
+        q4 inv = qconj(e.base_quat);
+        e.vel_world = link_vel_world(p, 0);
+        e.lin_vel = qrot(e.vel_world, inv);
+        e.ang_vel = qrot(p.cd_a[0], inv);
+        e.proj_g = qrot(mk3(0.0f, 0.0f, -1.0f), inv);
+        for (int j = 0; j < NHINGE; ++j) {
+            e.dof_pos[j] = p.qpos[cfg.motors_dof[j] + 1];
+            e.dof_vel[j] = p.qvel[cfg.motors_dof[j]];
+            e.torque[j] = applied_force(m, p, cfg.motors_dof[j]);
+        }
+        if (cfg.has_foot_tracking) {
+            for (int i = 0; i < 4; ++i) {
+                e.lfc[i] = e.fc[i];
+                e.fc[i] = fabsf(p.cforce[cfg.foot_link[i]].z) > cfg.foot_contact_threshold ? 1 : 0;
+            }
+        }
+        if (e.ep_len % cfg.resample_steps == 0) resample_commands(cfg, sp, rng, SLOT_CMD, cfg.env_offset + b, e.cmd);
+    } else {
+        for (int i = 0; i < A; ++i) { e.act[i] = 0.0f; e.applied[i] = F32(B_APPLIED)[b * A + i]; }
+        e.base_pos = ld3(F32(B_BASE_POS) + b * 3);
+        e.base_quat = ld4(F32(B_BASE_QUAT) + b * 4);
+        e.lin_vel = ld3(F32(B_BASE_LIN_VEL) + b * 3);
+        e.ang_vel = ld3(F32(B_BASE_ANG_VEL) + b * 3);
+        e.proj_g = ld3(F32(B_PROJ_G) + b * 3);
+        e.euler = ld3(F32(B_BASE_EULER) + b * 3);
+        e.vel_world = mk3(0, 0, 0);
+    }
+
+    // ---- termination
+    bool tout = e.ep_len > cfg.max_episode_length;
+    bool rst = tout;
+    if (sp.do_physics) {
+        rst = rst || fabsf(e.euler.y) > cfg.term_pitch || fabsf(e.euler.x) > cfg.term_roll;
+        rst = rst || fabsf(e.lin_vel.z) > cfg.term_zvel || fabsf(e.lin_vel.y) > cfg.term_yvel;
+    }
+    if (sp.force_reset_all) rst = true;
+    // an env whose physics went non-finite is force-reset (stricter than the reference, which raises)
+    if (p.err & (ERR_NAN_ACC | ERR_NAN_FORCE)) rst = true;
+
+    float rew = 0.0f;
+    if (cfg.kind == ENV_BASE) {
+        if (rst) reset_env(m, cfg, sp, bf, b, rng, p, e, out);
+        if (sp.do_physics) {
+            if (rst) {  // live getters see the post-reset state
+                for (int j = 0; j < NHINGE; ++j) e.torque[j] = applied_force(m, p, cfg.motors_dof[j]);
+            }
+            for (int k = 0; k < cfg.n_rew; ++k) {
+                float r = reward_term(cfg.rew_id[k], m, cfg, p, e) * cfg.rew_scale[k];
+                rew += r;
+                F32(B_EP_SUMS)[k * bf.B + b] += r;
+            }
+        }
+    } else {
+        if (sp.do_physics) {
+            for (int k = 0; k < cfg.n_rew; ++k) {
+                float r = reward_term(cfg.rew_id[k], m, cfg, p, e) * cfg.rew_scale[k];
+                rew += r;
+                F32(B_EP_SUMS)[k * bf.B + b] += r;
+            }
+        }
+        if (rst) reset_env(m, cfg, sp, bf, b, rng, p, e, out);
+    }
+    out.reset = rst ? 1 : 0;
+    out.timeout = (rst && tout) ? 1 : 0;
+
+    // ---- observations
+    if (sp.do_physics) {
+        float* obs = F32(B_OBS) + (size_t)b * cfg.num_obs;
+        float o[NOBS_MAX];
+        o[0] = e.ang_vel.x * cfg.obs_scale_ang_vel; o[1] = e.ang_vel.y * cfg.obs_scale_ang_vel; o[2] = e.ang_vel.z * cfg.obs_scale_ang_vel;
+        float go[3] = {0.0f, 0.0f, 0.0f};
+        if (cfg.kind != ENV_BASE) { go[0] = F32(B_GRAV_OFF)[b * 3]; go[1] = F32(B_GRAV_OFF)[b * 3 + 1]; go[2] = F32(B_GRAV_OFF)[b * 3 + 2]; }
+        o[3] = e.proj_g.x + go[0]; o[4] = e.proj_g.y + go[1]; o[5] = e.proj_g.z + go[2];
+        o[6] = e.cmd[0] * cfg.obs_scale_lin_vel; o[7] = e.cmd[1] * cfg.obs_scale_lin_vel; o[8] = e.cmd[2] * cfg.obs_scale_ang_vel;
+        for (int j = 0; j < NHINGE; ++j) {
+            o[9 + j] = (e.dof_pos[j] - cfg.default_dof_pos[j]) * cfg.obs_scale_dof_pos;
+            o[21 + j] = e.dof_vel[j] * cfg.obs_scale_dof_vel;
+        }
+        for (int i = 0; i < A; ++i) o[33 + i] = cfg.kind == ENV_BASE ? e.act[i] : e.applied[i];
+        if (sp.obs_noise_on) {
+            for (int k = 0; k < 9; ++k) {  // entries 0..35 can carry noise (33.. are always zero-std)
+                u4 r = rng4(rng, SLOT_OBS_NOISE + k);
+                float z[4];
+                boxmuller(r.a, r.b, z[0], z[1]);
+                boxmuller(r.c, r.d, z[2], z[3]);
+                for (int j = 0; j < 4; ++j) {
+                    int idx = 4 * k + j;
+                    if (idx < cfg.num_obs) o[idx] += z[j] * sp.obs_noise[idx];
+                }
+            }
+        }
+        for (int i = 0; i < cfg.num_obs; ++i) obs[i] = o[i];
+        if (cfg.num_priv > 0) {  // go2_env_walk.py:1115-1141
+            float* pr = F32(B_PRIV) + (size_t)b * cfg.num_priv;
+            int k = 0;
+            for (int i = 0; i < cfg.num_obs; ++i) pr[k++] = o[i];
+            pr[k++] = e.lin_vel.x * cfg.obs_scale_lin_vel; pr[k++] = e.lin_vel.y * cfg.obs_scale_lin_vel; pr[k++] = e.lin_vel.z * cfg.obs_scale_lin_vel;
+            pr[k++] = sp.friction;
+            for (int j = 0; j < NHINGE; ++j) pr[k++] = F32(B_KP_FACTORS)[b * NHINGE + j];
+            for (int j = 0; j < NHINGE; ++j) pr[k++] = F32(B_KD_FACTORS)[b * NHINGE + j];
+            for (int j = 0; j < NHINGE; ++j) pr[k++] = F32(B_MOTOR_STRENGTH)[b * NHINGE + j];
+            pr[k++] = sp.mass_shift[0];
+            pr[k++] = sp.com_shift[0]; pr[k++] = sp.com_shift[1]; pr[k++] = sp.com_shift[2];
+            // leg mass shifts in cfg order FR, FL, RR, RL = robot links 2, 1, 4, 3
+            pr[k++] = sp.mass_shift[2]; pr[k++] = sp.mass_shift[1]; pr[k++] = sp.mass_shift[4]; pr[k++] = sp.mass_shift[3];
+            pr[k++] = go[0]; pr[k++] = go[1]; pr[k++] = go[2];
+            pr[k++] = F32(B_CUR_PUSH)[b * 3]; pr[k++] = F32(B_CUR_PUSH)[b * 3 + 1]; pr[k++] = F32(B_CUR_PUSH)[b * 3 + 2];
+            pr[k] = cfg.max_delay > 0 ? (float)I32(B_DELAY)[b] / (float)cfg.max_delay : 0.0f;
+        }
+        F32(B_REW)[b] = rew;
+        for (int i = 0; i < A; ++i) e.last_act[i] = e.act[i];
+        for (int j = 0; j < NHINGE; ++j) e.last_dof_vel[j] = e.dof_vel[j];
+    }
+
+    // ---- write back
+    store_phys(bf, b, p);
+    U8(B_RESET)[b] = rst ? 1 : 0;
+    F32(B_TIMEOUT)[b] = tout ? 1.0f : 0.0f;
+    I32(B_EP_LEN)[b] = e.ep_len;
+    I32(B_ERRNO)[b] |= p.err;
+    I32(B_NCONTACT)[b] = p.n_contacts;
+    I32(B_NNEWTON)[b] = p.n_newton;
+    for (int i = 0; i < 3; ++i) F32(B_COMMANDS)[b * 3 + i] = e.cmd[i];
+    for (int i = 0; i < A; ++i) {
+        F32(B_LAST_ACTIONS)[b * A + i] = e.last_act[i];
+        if (cfg.kind != ENV_BASE) F32(B_APPLIED)[b * A + i] = e.applied[i];
+    }
+    for (int j = 0; j < NHINGE; ++j) {
+        F32(B_DOF_POS)[b * NHINGE + j] = e.dof_pos[j];
+        F32(B_DOF_VEL)[b * NHINGE + j] = e.dof_vel[j];
+        F32(B_LAST_DOF_VEL)[b * NHINGE + j] = e.last_dof_vel[j];
+        F32(B_TARGET)[b * NHINGE + j] = e.target[j];
+        F32(B_TORQUE)[b * NHINGE + j] = e.torque[j];
+    }
+    F32(B_BASE_POS)[b * 3] = e.base_pos.x; F32(B_BASE_POS)[b * 3 + 1] = e.base_pos.y; F32(B_BASE_POS)[b * 3 + 2] = e.base_pos.z;
+    F32(B_BASE_QUAT)[b * 4] = e.base_quat.w; F32(B_BASE_QUAT)[b * 4 + 1] = e.base_quat.x; F32(B_BASE_QUAT)[b * 4 + 2] = e.base_quat.y; F32(B_BASE_QUAT)[b * 4 + 3] = e.base_quat.z;
+    F32(B_BASE_LIN_VEL)[b * 3] = e.lin_vel.x; F32(B_BASE_LIN_VEL)[b * 3 + 1] = e.lin_vel.y; F32(B_BASE_LIN_VEL)[b * 3 + 2] = e.lin_vel.z;
+    F32(B_BASE_ANG_VEL)[b * 3] = e.ang_vel.x; F32(B_BASE_ANG_VEL)[b * 3 + 1] = e.ang_vel.y; F32(B_BASE_ANG_VEL)[b * 3 + 2] = e.ang_vel.z;
+    F32(B_PROJ_G)[b * 3] = e.proj_g.x; F32(B_PROJ_G)[b * 3 + 1] = e.proj_g.y; F32(B_PROJ_G)[b * 3 + 2] = e.proj_g.z;
+    F32(B_BASE_EULER)[b * 3] = e.euler.x; F32(B_BASE_EULER)[b * 3 + 1] = e.euler.y; F32(B_BASE_EULER)[b * 3 + 2] = e.euler.z;
+    if (cfg.has_foot_tracking) {
+        for (int i = 0; i < 4; ++i) {
+            F32(B_AIR_TIME)[b * 4 + i] = e.air[i];
+            U8(B_FOOT_CONTACT)[b * 4 + i] = (uint8_t)e.fc[i];
+            U8(B_LAST_FOOT_CONTACT)[b * 4 + i] = (uint8_t)e.lfc[i];
+        }
+    }
+    for (int l = 0; l < NLINK; ++l) {
+        F32(B_CONTACT_FORCE)[(b * NLINK + l) * 3] = p.cforce[l].x;
+        F32(B_CONTACT_FORCE)[(b * NLINK + l) * 3 + 1] = p.cforce[l].y;
+        F32(B_CONTACT_FORCE)[(b * NLINK + l) * 3 + 2] = p.cforce[l].z;
+    }
+}
+
+#undef F32
+#undef I32
+#undef U8
+
+}  // namespace go2

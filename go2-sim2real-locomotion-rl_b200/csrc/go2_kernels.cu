@@ -1,0 +1,200 @@
+// go2_b200 - CUDA kernels + C ABI (include/go2_b200.h) of the fused Go2 env step, sm_100a.
+//
+// Layout v1: one thread per environment.  A thread loads its env's persistent state (SoA, batch-last ->
+// coalesced), runs the whole control tick (torque law, 2 rigid substeps incl. collision + Newton solve,
+// rewards, reset, observations) out of registers / thread-local memory, and writes the state back once.
+// No global-memory round trips between phases, one launch per tick.
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <string>
+#include "../../include/go2_b200.h"
+#include "go2_env.cuh"
+#include "go2_model_host.hpp"
+#include "go2_layout.hpp"
+
+using namespace go2;
+
+struct go2_handle {
+    int device;
+    Go2Model* d_model;
+    EnvConfig* d_cfg;
+    EnvConfig cfg;
+    Buffers bf;
+    int dtype[B_COUNT], rows[B_COUNT], cols[B_COUNT];
+    char* arena;
+    size_t arena_bytes;
+    float* h_stats;  // pinned
+    long long launches;
+    std::string err;
+};
+
+#ifndef GO2_BLOCK
+#define GO2_BLOCK 64
+#endif
+
+__global__ void __launch_bounds__(GO2_BLOCK) go2_step_kernel(const Go2Model* __restrict__ gm, const EnvConfig* __restrict__ gcfg,
+                                                           StepParams sp, Buffers bf, const float* __restrict__ actions) {
+    int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= bf.B) return;
+    Phys p;
+    EnvStepOut out;
+    env_step(*gm, *gcfg, sp, bf, actions, b, p, out);
+    if (out.reset) {
+        float* st = (float*)bf.p[B_STATS];
+        atomicAdd(&st[STATS_RESETS], 1.0f);
+        if (out.timeout) atomicAdd(&st[STATS_TIMEOUTS], 1.0f);
+        atomicAdd(&st[STATS_TRACKING], out.tracking_per_sec);
+        for (int k = 0; k < gcfg->n_rew; ++k) atomicAdd(&st[STATS_REW0 + k], out.ep_stat[k]);
+    }
+    if (p.err) atomicOr((int*)((float*)bf.p[B_STATS] + STATS_ERR), p.err);
+}
+
+__global__ void __launch_bounds__(128) go2_links_kernel(const Go2Model* __restrict__ gm, StepParams sp, Buffers bf) {
+    int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= bf.B) return;
+    Phys p;
+    int B = bf.B;
+    for (int i = 0; i < NQ; ++i) p.qpos[i] = ((float*)bf.p[B_QPOS])[i * B + b];
+    for (int i = 0; i < NV; ++i) p.qvel[i] = ((float*)bf.p[B_QVEL])[i * B + b];
+    kinematics(*gm, sp.mass_shift, sp.com_shift, p);
+    velocities(*gm, p);
+    float* lp = (float*)bf.p[B_LINK_POS] + (size_t)b * NLINK * 3;
+    float* lv = (float*)bf.p[B_LINK_VEL] + (size_t)b * NLINK * 3;
+    for (int l = 0; l < NLINK; ++l) {
+        v3 v = link_vel_world(p, l);
+        lp[l * 3] = p.lpos[l].x; lp[l * 3 + 1] = p.lpos[l].y; lp[l * 3 + 2] = p.lpos[l].z;
+        lv[l * 3] = v.x; lv[l * 3 + 1] = v.y; lv[l * 3 + 2] = v.z;
+    }
+}
+
+static bool ck(go2_handle* h, cudaError_t e, const char* what) {
+    if (e == cudaSuccess) return true;
+    h->err = std::string(what) + ": " + cudaGetErrorString(e);
+    return false;
+}
+
+extern "C" {
+
+void go2_abi_sizes(int* out4) {
+    out4[0] = (int)sizeof(EnvConfig);
+    out4[1] = (int)sizeof(StepParams);
+    out4[2] = (int)B_COUNT;
+    out4[3] = (int)STATS_LEN;
+}
+
+int go2_create(const int32_t* model_iv, int n_iv, const double* model_fv, int n_fv, const void* cfg, int cfg_bytes, int device,
+               go2_handle** out) {
+    *out = nullptr;
+    if (cfg_bytes != (int)sizeof(EnvConfig)) return -2;
+    go2_handle* h = new go2_handle();
+    h->device = device;
+    h->launches = 0;
+    memcpy(&h->cfg, cfg, sizeof(EnvConfig));
+    const EnvConfig& c = h->cfg;
+    Go2Model m;
+    if (!unpack_model(m, model_iv, n_iv, model_fv, n_fv)) { delete h; return -3; }
+    if (c.num_envs <= 0 || c.num_actions > NACT_MAX || c.num_obs > NOBS_MAX || c.hist_size > HIST_MAX || c.n_rew > MAX_REW) { delete h; return -4; }
+    if (cudaSetDevice(device) != cudaSuccess) { delete h; return -5; }
+    compute_layout(c, h->dtype, h->rows, h->cols);
+    size_t offs[B_COUNT];
+    h->arena_bytes = compute_offsets(h->dtype, h->rows, h->cols, offs);
+    if (cudaMalloc(&h->arena, h->arena_bytes) != cudaSuccess) { delete h; return -6; }
+    for (int i = 0; i < B_COUNT; ++i) h->bf.p[i] = h->arena + offs[i];
+    h->bf.B = c.num_envs;
+    cudaMalloc(&h->d_model, sizeof(Go2Model));
+    cudaMalloc(&h->d_cfg, sizeof(EnvConfig));
+    cudaMemcpy(h->d_model, &m, sizeof(Go2Model), cudaMemcpyHostToDevice);
+    cudaMemcpy(h->d_cfg, &h->cfg, sizeof(EnvConfig), cudaMemcpyHostToDevice);
+    cudaMallocHost(&h->h_stats, sizeof(float) * STATS_LEN);
+    std::string init(h->arena_bytes, 0);
+    init_arena(c, offs, &init[0]);
+    cudaMemcpy(h->arena, init.data(), h->arena_bytes, cudaMemcpyHostToDevice);
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) h->err = cudaGetErrorString(e);
+    *out = h;
+    return e == cudaSuccess ? 0 : -7;
+}
+
+void go2_destroy(go2_handle* h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    cudaFree(h->arena);
+    cudaFree(h->d_model);
+    cudaFree(h->d_cfg);
+    cudaFreeHost(h->h_stats);
+    delete h;
+}
+
+const char* go2_last_error(go2_handle* h) { return h ? h->err.c_str() : "null handle"; }
+
+int go2_buffer_info(go2_handle* h, int id, void** ptr, int* dtype, int* rows, int* cols) {
+    if (!h || id < 0 || id >= B_COUNT) return -1;
+    *ptr = h->bf.p[id];
+    *dtype = h->dtype[id];
+    *rows = h->rows[id];
+    *cols = h->cols[id];
+    return 0;
+}
+
+static int launch_step(go2_handle* h, const float* d_actions, const void* params, int params_bytes, cudaStream_t s) {
+    if (params_bytes != (int)sizeof(StepParams)) { h->err = "StepParams size mismatch"; return -2; }
+    StepParams sp;
+    memcpy(&sp, params, sizeof(sp));
+    int B = h->cfg.num_envs;
+    if (!ck(h, cudaMemsetAsync(h->bf.p[B_STATS], 0, sizeof(float) * STATS_LEN, s), "memset stats")) return -1;
+    go2_step_kernel<<<(B + GO2_BLOCK - 1) / GO2_BLOCK, GO2_BLOCK, 0, s>>>(h->d_model, h->d_cfg, sp, h->bf, d_actions);
+    h->launches += 1;
+    return ck(h, cudaGetLastError(), "go2_step_kernel") ? 0 : -1;
+}
+
+int go2_step(go2_handle* h, const float* d_actions, const void* params, int params_bytes, void* stream) {
+    return launch_step(h, d_actions, params, params_bytes, (cudaStream_t)stream);
+}
+
+int go2_reset_all(go2_handle* h, const void* params, int params_bytes, void* stream) {
+    if (params_bytes != (int)sizeof(StepParams)) { h->err = "StepParams size mismatch"; return -2; }
+    StepParams sp;
+    memcpy(&sp, params, sizeof(sp));
+    sp.do_physics = 0;
+    sp.force_reset_all = 1;
+    return launch_step(h, (const float*)h->bf.p[B_ACTIONS_IN], &sp, sizeof(sp), (cudaStream_t)stream);
+}
+
+int go2_step_host(go2_handle* h, const float* h_actions, const void* params, int params_bytes, float* h_obs, float* h_rew,
+                  uint8_t* h_done, float* h_priv, float* h_timeouts, void* stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    const EnvConfig& c = h->cfg;
+    size_t B = c.num_envs;
+    if (!ck(h, cudaMemcpyAsync(h->bf.p[B_ACTIONS_IN], h_actions, B * c.num_actions * 4, cudaMemcpyHostToDevice, s), "H2D actions")) return -1;
+    int r = launch_step(h, (const float*)h->bf.p[B_ACTIONS_IN], params, params_bytes, s);
+    if (r) return r;
+    cudaMemcpyAsync(h_obs, h->bf.p[B_OBS], B * c.num_obs * 4, cudaMemcpyDeviceToHost, s);
+    cudaMemcpyAsync(h_rew, h->bf.p[B_REW], B * 4, cudaMemcpyDeviceToHost, s);
+    cudaMemcpyAsync(h_done, h->bf.p[B_RESET], B, cudaMemcpyDeviceToHost, s);
+    if (h_priv && c.num_priv > 0) cudaMemcpyAsync(h_priv, h->bf.p[B_PRIV], B * c.num_priv * 4, cudaMemcpyDeviceToHost, s);
+    if (h_timeouts) cudaMemcpyAsync(h_timeouts, h->bf.p[B_TIMEOUT], B * 4, cudaMemcpyDeviceToHost, s);
+    return ck(h, cudaStreamSynchronize(s), "step_host sync") ? 0 : -1;
+}
+
+int go2_read_stats(go2_handle* h, float* host_out, int n, void* stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    if (n > STATS_LEN) n = STATS_LEN;
+    if (!ck(h, cudaMemcpyAsync(h->h_stats, h->bf.p[B_STATS], sizeof(float) * n, cudaMemcpyDeviceToHost, s), "D2H stats")) return -1;
+    if (!ck(h, cudaStreamSynchronize(s), "stats sync")) return -1;
+    memcpy(host_out, h->h_stats, sizeof(float) * n);
+    return 0;
+}
+
+int go2_export_links(go2_handle* h, const void* params, int params_bytes, void* stream) {
+    if (params_bytes != (int)sizeof(StepParams)) { h->err = "StepParams size mismatch"; return -2; }
+    StepParams sp;
+    memcpy(&sp, params, sizeof(sp));
+    int B = h->cfg.num_envs;
+    go2_links_kernel<<<(B + 127) / 128, 128, 0, (cudaStream_t)stream>>>(h->d_model, sp, h->bf);
+    h->launches += 1;
+    return ck(h, cudaGetLastError(), "go2_links_kernel") ? 0 : -1;
+}
+
+long long go2_launch_count(go2_handle* h) { return h ? h->launches : 0; }
+
+}  // extern "C"

@@ -1,0 +1,139 @@
+// go2_b200 - shared POD types for the fused Go2 env-step kernel (device + host).
+//
+// Replaces, for the Go2 scenes only, the struct-of-fields zoo of the reference
+// (genesis/utils/array_class.py: LinksInfo/DofsInfo/GeomsInfo/ColliderInfo ...) by one constant table
+// (Go2Model, lives in __constant__ memory) and one per-step parameter block (StepParams, passed by value).
+#pragma once
+#include <stdint.h>
+
+#ifdef __CUDACC__
+#define G2_HD __host__ __device__ __forceinline__
+#define G2_HDN __host__ __device__ __noinline__
+#else
+#define G2_HD inline
+#define G2_HDN
+#endif
+
+namespace go2 {
+
+constexpr int NLINK = 13;   // robot links (robot-local index; ground = -1)
+constexpr int NV = 18;      // dofs: 6 free + 12 hinges
+constexpr int NQ = 19;
+constexpr int NHINGE = 12;
+constexpr int NGEOM = 28;   // geom 0 = ground box, 1..27 robot
+constexpr int MAX_PAIRS_STATIC = 352;
+constexpr int MAX_CPAIRS = 24;   // colliding geom pairs kept per env (contact-normal cache entries)
+constexpr int MAX_CONTACTS = 48; // contacts per env (reference cap: 150; overflow -> errno bit)
+constexpr int MAX_ROWS = 4 * MAX_CONTACTS + NHINGE;
+constexpr int NTRI = NV * (NV + 1) / 2;  // packed lower triangle
+constexpr int MAX_REW = 32;      // reward terms
+constexpr int NACT_MAX = 16;
+constexpr int HIST_MAX = 4;      // action-delay ring slots (max_delay_steps + 1 <= 4)
+constexpr int NOBS_MAX = 49;
+constexpr int SCAN_MAX = 77;
+
+constexpr float EPSF = 1.1920929e-07f;  // gs.EPS for precision="32" (genesis/__init__.py:229)
+constexpr float CCD_EPS = 1e-9f;        // collider/mpr.py:16-20
+constexpr float CCD_TOL = 1e-6f;
+constexpr int CCD_ITERS = 50;
+constexpr float MC_PERTURB = 1e-2f;     // collider/collider.py:78-80
+constexpr float MC_TOL = 1e-2f;
+constexpr int SOLVER_ITERS = 50;        // options/solvers.py:474-519
+constexpr float SOLVER_TOL = 1e-6f;
+constexpr int LS_ITERS = 50;
+constexpr float LS_TOL = 1e-2f;
+
+enum GeomType { GEOM_SPHERE = 1, GEOM_CYLINDER = 3, GEOM_BOX = 5 };
+enum ErrBits { ERR_CPAIR_OVERFLOW = 1, ERR_CONTACT_OVERFLOW = 2, ERR_NAN_FORCE = 4, ERR_NAN_ACC = 8 };
+enum EnvKind { ENV_WALK = 0, ENV_STAIR = 1, ENV_BASE = 2 };
+enum CtrlKind { CTRL_MANUAL_PLS = 0, CTRL_MANUAL_FIXED = 1, CTRL_GENESIS_PD = 2 };
+
+struct Go2Model {
+    int parent[NLINK];
+    float l_pos[NLINK][3], l_quat[NLINK][4];
+    float inertial_pos[NLINK][3], inertial_quat[NLINK][4], inertial_i[NLINK][9], mass[NLINK];
+    float axis[NLINK][3];
+    float limit_lo[NV], limit_hi[NV], frange[NV], armature[NV];
+    float invweight_link[NLINK], invweight_dof[NV];
+    float meaninertia, dt, gravity[3], sol_params[7];
+    int g_link[NGEOM], g_type[NGEOM];
+    float g_pos[NGEOM][3], g_quat[NGEOM][4], g_size[NGEOM][3], g_half[NGEOM][3];
+    int npairs;
+    uint8_t pair_a[MAX_PAIRS_STATIC], pair_b[MAX_PAIRS_STATIC];
+};
+
+// Reward terms (union of the walk / stair / base env zoos).
+enum RewardId {
+    R_TRACKING_LIN_VEL = 0, R_TRACKING_ANG_VEL, R_LIN_VEL_Z, R_BASE_HEIGHT, R_ACTION_RATE, R_SIMILAR_TO_DEFAULT,
+    R_ORIENTATION_PENALTY, R_DOF_ACC, R_DOF_VEL, R_ANG_VEL_XY, R_FEET_AIR_TIME, R_FOOT_SLIP, R_FOOT_CLEARANCE,
+    R_JOINT_TRACKING, R_ENERGY, R_TORQUE_LOAD, R_STAND_STILL, R_STAND_STILL_VEL, R_FEET_STANCE,
+    // base env (crouch / jump)
+    R_JUMP_IMPULSE, R_JUMP_APEX, R_XY_STABILITY, R_ORIENTATION, R_NO_SHAKE, R_CROUCH, R_CROUCH_2, R_GROUND_PENALTY,
+    R_CROUCH_TARGET, R_NO_FALL, R_Y_STABILITY, R_CROUCH_PROGRESS, R_CROUCH_SPEED,
+    // stair
+    R_ORIENTATION_ROLL_ONLY, R_FORWARD_PROGRESS,
+    R_COUNT
+};
+
+// Static env configuration, compiled once from the four cfg dicts (host: go2_b200/config.py).
+struct EnvConfig {
+    int kind;             // EnvKind
+    int ctrl;             // CtrlKind
+    int num_envs, env_offset;  // env_offset = global id of local env 0 (multi-GPU sharding)
+    int num_actions, num_pos_actions, num_obs, num_priv;
+    int max_episode_length, resample_steps;
+    int hist_size;        // delay ring slots
+    int n_rew;            // number of active reward terms, evaluated in this order
+    int rew_id[MAX_REW];
+    float rew_scale[MAX_REW];  // already multiplied by dt, like the reference ctor does
+    int motors_dof[NHINGE];    // dof index of action channel j
+    float default_dof_pos[NHINGE], torque_limit[NHINGE];
+    float action_scale, clip_actions;
+    float kp, kd;         // Genesis PD gains (CTRL_GENESIS_PD) / nominal
+    float pls_kp_default, pls_kp_scale, pls_kp_lo, pls_kp_hi;
+    float term_roll, term_pitch, term_zvel, term_yvel;  // degrees / m/s; <0 => check disabled
+    float base_init_pos[3], base_init_quat[4], inv_base_init_quat[4];
+    float obs_scale_lin_vel, obs_scale_ang_vel, obs_scale_dof_pos, obs_scale_dof_vel;
+    float tracking_sigma, base_height_target, feet_height_target, feet_air_time_target;
+    float foot_contact_threshold;
+    int foot_link[4];     // robot-local link index of each foot (cfg order FR, FL, RR, RL)
+    int has_foot_tracking;
+    int push_link;        // robot-local link the push force is applied to (reference quirk: FL_hip)
+    int push_dur_lo, push_dur_hi;
+    int has_push, has_init_z, has_init_euler, has_kp_factor, has_kd_factor, has_motor_strength, has_gravity_offset,
+        has_delay, compound_commands, n_standing;
+    float init_z_lo, init_z_hi, init_euler_lo, init_euler_hi;  // radians
+    int min_delay, max_delay;
+    int has_kp_range;
+    int simulate_action_latency;  // base env: 1-step latency through last_actions
+    // base-env reward parameters
+    float rp[16];
+    uint32_t seed_lo, seed_hi;
+};
+
+// Per-step parameters: everything the reference keeps as host-side python scalars (curriculum-driven
+// values, global DR values, ring-buffer write index, push schedule).  Passed by value at each launch.
+struct StepParams {
+    uint32_t step_count;       // RNG counter component
+    int hist_write_idx;        // ring slot written this step
+    int push_resample;         // 1 if push_counter % push_interval == 0 at this step
+    int push_enable;
+    float push_lo, push_hi;
+    float action_noise_std;
+    float obs_noise[NOBS_MAX]; // per-entry std (obs_noise_vec); all zero => no noise draws
+    int obs_noise_on;
+    float cmd_lo[3], cmd_hi[3];
+    // reset-time DR ranges, already lerped with this step's t_sample
+    float kpf_lo, kpf_hi, kdf_lo, kdf_hi, ms_lo, ms_hi, go_lo, go_hi;
+    float kp_lo, kp_hi, kd_lo, kd_hi;  // fixed-gain manual PD (non-PLS) base gain ranges
+    int delay_lo, delay_hi;
+    // global physics DR currently in force (Genesis semantics: one value for all envs)
+    float friction;            // applied to every geom (ground + robot)
+    float mass_shift[NLINK];   // base + the four hips used by the envs
+    float com_shift[3];        // base link COM shift
+    float kp_genesis, kd_genesis;  // dofs kp/kv for CTRL_GENESIS_PD
+    int do_physics;            // 0 => reset-only launch
+    int force_reset_all;
+};
+
+}  // namespace go2

@@ -1,0 +1,66 @@
+/* go2_b200 - C ABI of the B200-native batched Go2 environment step.
+ *
+ * This is the drop-in boundary for the hot path `Go2Env.step(actions)` of
+ * saifahmadgit/go2-sim2real-locomotion-rl.  The reference has no FFI for this path: its env classes
+ * call the Genesis scene API in-process (examples/locomotion/final/go2_env_walk.py:985-1109 ->
+ * genesis/engine/scene.py:979 Scene.step -> genesis/engine/solvers/rigid/rigid_solver.py:1116 substep).
+ * Each entry point below names the reference interface it replaces.  Plain pointers and sizes only; no
+ * exceptions cross the boundary (int return codes, 0 = ok, message via go2_last_error).
+ *
+ * Memory: the library owns every device buffer; go2_buffer_info() hands out raw device pointers that the
+ * host side wraps as non-owning views (lifetime = handle).  Threading: one host thread per handle; all
+ * work is enqueued on the stream passed by the caller; distinct handles are independent.
+ */
+#ifndef GO2_B200_H
+#define GO2_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct go2_handle go2_handle;
+
+/* sizeof(EnvConfig), sizeof(StepParams), B_COUNT, STATS_LEN - lets a binding verify its struct mirrors. */
+void go2_abi_sizes(int* out4);
+
+/* Replaces gs.Scene(...) + add_entity(plane, go2) + scene.build(n_envs)  (go2_env_walk.py:211-244,
+ * rigid_solver.py:337 RigidSolver.build).  `model_iv/model_fv` is the flat model table produced by
+ * go2_b200.model.flatten_model; `cfg` points to an EnvConfig (csrc/go2_types.cuh). */
+int go2_create(const int32_t* model_iv, int n_iv, const double* model_fv, int n_fv, const void* cfg, int cfg_bytes,
+               int device, go2_handle** out);
+void go2_destroy(go2_handle* h);
+const char* go2_last_error(go2_handle* h);
+
+/* Buffer table (csrc/go2_buffers.cuh BufId).  dtype: 0 = f32, 1 = i32, 2 = u8.  rows/cols describe the
+ * 2-D shape in memory order. Replaces the qd_to_torch zero-copy views of genesis/utils/misc.py. */
+int go2_buffer_info(go2_handle* h, int buf_id, void** dev_ptr, int* dtype, int* rows, int* cols);
+
+/* One control tick for every env: replaces Go2Env.step (go2_env_walk.py:985-1109 /
+ * go2_env_base.py:123-192) including scene.step() (2 substeps).  `d_actions`: device f32 [B][A].
+ * `params` points to a StepParams.  Asynchronous on `stream` (a cudaStream_t, 0 = default stream). */
+int go2_step(go2_handle* h, const float* d_actions, const void* params, int params_bytes, void* stream);
+
+/* Replaces Go2Env.reset() -> reset_idx(all envs) (go2_env_walk.py:1242-1245). */
+int go2_reset_all(go2_handle* h, const void* params, int params_bytes, void* stream);
+
+/* Same tick with HOST buffers: copies actions H2D, steps, copies obs / rew / done (and, if non-NULL,
+ * privileged obs and time_outs) D2H, and synchronises the stream before returning. */
+int go2_step_host(go2_handle* h, const float* h_actions, const void* params, int params_bytes, float* h_obs, float* h_rew,
+                  uint8_t* h_done, float* h_priv, float* h_timeouts, void* stream);
+
+/* Episode statistics accumulated by the last step's resets (n_resets, n_timeouts, sum tracking/sec,
+ * errno OR, then the per-reward-term sums): replaces the per-key `.mean().item()` host syncs of
+ * reset_idx (go2_env_walk.py:1228-1235) and the curriculum aggregates (:688-729).  Synchronises. */
+int go2_read_stats(go2_handle* h, float* host_out, int n, void* stream);
+
+/* Recompute link poses / velocities of every env into B_LINK_POS / B_LINK_VEL
+ * (replaces RigidEntity.get_links_pos / get_links_vel, rigid_entity.py:2241-2406). */
+int go2_export_links(go2_handle* h, const void* params, int params_bytes, void* stream);
+
+/* Number of kernels this library has launched on the handle since creation. */
+long long go2_launch_count(go2_handle* h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
