@@ -1,0 +1,719 @@
+"""Drop-in `Go2Env` classes backed by the fused CUDA step (walk / base flavours).
+
+Same constructor, attributes and return values as the reference env classes
+(examples/locomotion/final/go2_env_walk.py:154-171,985-1109,1145-1245 and go2_env_base.py), so rsl-rl 2.2.4's
+OnPolicyRunner and the repo's train scripts can use them unchanged.  What the reference does per step with
+~80 torch kernels + ~20 quadrants kernels happens here in ONE kernel launch; the Python side only keeps the
+scalar state machines the reference also keeps on the host (curriculum, global domain randomisation, push
+schedule, delay-ring write index) and turns them into the per-step parameter block.
+"""
+from __future__ import annotations
+
+import math
+
+import numpy as np
+import torch
+
+from . import abi
+from .core import Go2Core
+from .model import load_model, motors_dof_idx
+
+DT = 0.02
+
+
+def _clamp01(x):
+    return float(max(0.0, min(1.0, x)))
+
+
+def _lerp(a, b, t):
+    return a + (b - a) * _clamp01(t)
+
+
+def _lerp_range(a, b, t):
+    return [_lerp(a[0], b[0], t), _lerp(a[1], b[1], t)]
+
+
+class Curriculum:
+    """Metric-gated difficulty level (behaviour of go2_env_walk.py:42-151 CurriculumManager)."""
+
+    def __init__(self, cfg, rng):
+        c = cfg or {}
+        g = c.get
+        self.enabled = bool(g("enabled", False))
+        self.level = float(g("level_init", 0.0))
+        self.level_min, self.level_max = float(g("level_min", 0.0)), float(g("level_max", 1.0))
+        self.alpha = float(g("ema_alpha", 0.05))
+        self.ready = (float(g("ready_timeout_rate", 0.7)), float(g("ready_tracking", 0.6)), float(g("ready_fall_rate", 0.30)))
+        self.ready_need, self.hard_rate, self.hard_need = int(g("ready_streak", 3)), float(g("hard_fall_rate", 0.55)), int(g("hard_streak", 2))
+        self.step_up, self.step_down, self.cooldown_updates = float(g("step_up", 0.02)), float(g("step_down", 0.01)), int(g("cooldown_updates", 1))
+        self.mix = (float(g("mix_prob_current", 0.80)), float(g("mix_level_low", 0.0)), float(g("mix_level_high", 0.6)))
+        self.ema = {"timeout_rate": None, "tracking": None, "fall_rate": None}
+        self._ready_streak = self._hard_streak = self._cooldown = 0
+        self._rng = rng
+
+    def sample_level(self):
+        if not self.enabled:
+            return 1.0
+        if self._rng.random() < self.mix[0]:
+            return _clamp01(self.level)
+        hi = min(self.level, self.mix[2])
+        lo = min(self.mix[1], hi)
+        return _clamp01(lo + (hi - lo) * self._rng.random())
+
+    def update(self, timeout_rate, tracking, fall_rate):
+        if not self.enabled:
+            return False
+        for k, x in (("timeout_rate", timeout_rate), ("tracking", tracking), ("fall_rate", fall_rate)):
+            old = self.ema[k]
+            self.ema[k] = float(x) if old is None else float((1.0 - self.alpha) * old + self.alpha * float(x))
+        if self._cooldown > 0:
+            self._cooldown -= 1
+        ready = self.ema["timeout_rate"] >= self.ready[0] and self.ema["tracking"] >= self.ready[1] and self.ema["fall_rate"] <= self.ready[2]
+        hard = self.ema["fall_rate"] >= self.hard_rate
+        self._ready_streak = self._ready_streak + 1 if ready else 0
+        self._hard_streak = self._hard_streak + 1 if hard else 0
+        old = self.level
+        if self._hard_streak >= self.hard_need:
+            self.level = max(self.level_min, self.level - self.step_down)
+            self._hard_streak = self._ready_streak = 0
+            self._cooldown = self.cooldown_updates
+        elif self._ready_streak >= self.ready_need and self._cooldown == 0:
+            self.level = min(self.level_max, self.level + self.step_up)
+            self._ready_streak = 0
+            self._cooldown = self.cooldown_updates
+        self.level = _clamp01(self.level)
+        return self.level != old
+
+    def state_dict(self):
+        return {"enabled": self.enabled, "level": float(self.level), "timeout_rate_ema": self.ema["timeout_rate"],
+                "tracking_ema": self.ema["tracking"], "fall_rate_ema": self.ema["fall_rate"]}
+
+
+def _inv_quat(q):
+    return [q[0], -q[1], -q[2], -q[3]]
+
+
+def _default_device():
+    try:
+        import genesis as gs  # the shim (or a real install) decides the device, like the reference does
+
+        return gs.device
+    except Exception:
+        return torch.device("cuda:0")
+
+
+class _Go2EnvBase:
+    """State shared by the walk / stair / base flavours: buffers, views, rsl-rl facing attributes."""
+
+    KIND = abi.ENV_WALK
+
+    def __init__(self, num_envs, env_cfg, obs_cfg, reward_cfg, command_cfg, show_viewer=False, *, device=None, seed=1,
+                 env_offset=0, total_envs=None, lib_path=None, stats_sync_interval=1):
+        if show_viewer:
+            raise RuntimeError("show_viewer=True: no graphics stack on this box (viewer unavailable)")
+        self.num_envs = int(num_envs)
+        self.num_obs = obs_cfg["num_obs"]
+        self.num_actions = env_cfg["num_actions"]
+        self.num_commands = command_cfg["num_commands"]
+        self.device = torch.device(device) if device is not None else torch.device(_default_device())
+        self.dt = DT
+        self.max_episode_length = math.ceil(env_cfg["episode_length_s"] / self.dt)
+        self.env_cfg, self.obs_cfg, self.reward_cfg, self.command_cfg = env_cfg, obs_cfg, reward_cfg, command_cfg
+        self.obs_scales = obs_cfg["obs_scales"]
+        self.reward_scales = reward_cfg["reward_scales"]
+        self._model = load_model()
+        self.motors_dof_idx = motors_dof_idx(self._model, env_cfg["joint_names"])
+        self._seed = int(seed)
+        self._np_rng = np.random.default_rng(self._seed)
+        self._env_offset = int(env_offset)
+        self._total_envs = int(total_envs) if total_envs is not None else self.num_envs
+        self._lib_path = lib_path
+        self.stats_sync_interval = int(stats_sync_interval)
+        self._step_count = 0
+        self.extras = {"observations": {}}
+
+    # ---- cfg -> EnvConfig fields common to all flavours
+    def _fill_common(self, c: abi.EnvConfig):
+        e = self.env_cfg
+        c.kind = self.KIND
+        c.num_envs, c.env_offset = self.num_envs, self._env_offset
+        c.num_actions, c.num_obs = self.num_actions, self.num_obs
+        c.max_episode_length = self.max_episode_length
+        c.resample_steps = int(e["resampling_time_s"] / self.dt)
+        names = list(self.reward_scales.keys())
+        c.n_rew = len(names)
+        for k, name in enumerate(names):
+            if name not in abi.REWARD_IDS:
+                raise AttributeError(f"Reward function '_reward_{name}' not found in Go2Env.")
+            self.reward_scales[name] *= self.dt  # the reference mutates the cfg dict in place (go2_env_walk.py:255-265)
+            c.rew_id[k] = abi.REWARD_IDS[name]
+            c.rew_scale[k] = float(self.reward_scales[name])
+        self._reward_names = names
+        for j, d in enumerate(self.motors_dof_idx):
+            c.motors_dof[j] = d
+            c.default_dof_pos[j] = float(e["default_joint_angles"][e["joint_names"][j]])
+        c.action_scale, c.clip_actions = float(e["action_scale"]), float(e["clip_actions"])
+        c.kp, c.kd = float(e["kp"]), float(e["kd"])
+        big = 1e30
+        c.term_roll = float(e.get("termination_if_roll_greater_than", big))
+        c.term_pitch = float(e.get("termination_if_pitch_greater_than", big))
+        c.term_zvel = float(e.get("termination_if_z_vel_greater_than", big))
+        c.term_yvel = float(e.get("termination_if_y_vel_greater_than", big))
+        for j in range(3):
+            c.base_init_pos[j] = float(e["base_init_pos"][j])
+        q = [float(v) for v in e["base_init_quat"]]
+        for j in range(4):
+            c.base_init_quat[j] = q[j]
+            c.inv_base_init_quat[j] = _inv_quat(q)[j]
+        s = self.obs_scales
+        c.obs_scale_lin_vel, c.obs_scale_ang_vel = float(s["lin_vel"]), float(s["ang_vel"])
+        c.obs_scale_dof_pos, c.obs_scale_dof_vel = float(s["dof_pos"]), float(s["dof_vel"])
+        r = self.reward_cfg
+        c.tracking_sigma = float(r.get("tracking_sigma", 0.25))
+        c.base_height_target = float(r.get("base_height_target", 0.3))
+        c.feet_height_target = float(r.get("feet_height_target", 0.075))
+        c.feet_air_time_target = float(r.get("feet_air_time_target", 0.1))
+        c.rp[0] = float(r.get("jump_apex_height", 0.55))
+        c.rp[1] = float(r.get("jump_apex_sigma", 0.05))
+        c.seed_lo = self._seed & 0xFFFFFFFF
+        c.seed_hi = (self._seed >> 32) & 0xFFFFFFFF
+
+    def _bind(self, c: abi.EnvConfig):
+        self.core = Go2Core(c, device=self.device, model=self._model, lib_path=self._lib_path)
+        b = self.core.buf
+        B = self.num_envs
+        self.obs_buf = b["obs"]
+        self.rew_buf = b["rew"].view(-1)
+        self.reset_buf = b["reset"].view(-1).view(torch.bool)
+        self._episode_length_buf = b["ep_len"].view(-1)
+        self.commands = b["commands"]
+        self.last_actions = b["last_actions"]
+        self.dof_pos, self.dof_vel, self.last_dof_vel = b["dof_pos"], b["dof_vel"], b["last_dof_vel"]
+        self.base_pos, self.base_quat = b["base_pos"], b["base_quat"]
+        self.base_lin_vel, self.base_ang_vel = b["base_lin_vel"], b["base_ang_vel"]
+        self.projected_gravity, self.base_euler = b["proj_g"], b["base_euler"]
+        self.actions = torch.zeros((B, self.num_actions), device=self.device, dtype=torch.float32)
+        self.default_dof_pos = torch.tensor([c.default_dof_pos[j] for j in range(12)], device=self.device, dtype=torch.float32)
+        self.base_init_pos = torch.tensor(list(c.base_init_pos), device=self.device)
+        self.base_init_quat = torch.tensor(list(c.base_init_quat), device=self.device)
+        self.inv_base_init_quat = torch.tensor(list(c.inv_base_init_quat), device=self.device)
+        self.commands_scale = torch.tensor([c.obs_scale_lin_vel, c.obs_scale_lin_vel, c.obs_scale_ang_vel], device=self.device)
+        self.global_gravity = torch.tensor([0.0, 0.0, -1.0], device=self.device).repeat(B, 1)
+        self.episode_sums = {name: b["ep_sums"][k] for k, name in enumerate(self._reward_names)}
+        self.extras["time_outs"] = b["timeout"].view(-1)
+        self._ecfg = c
+
+    # rsl-rl rebinds this attribute (`env.episode_length_buf = torch.randint_like(...)`): keep the device buffer in sync
+    @property
+    def episode_length_buf(self):
+        return self._episode_length_buf
+
+    @episode_length_buf.setter
+    def episode_length_buf(self, value):
+        self._episode_length_buf.copy_(torch.as_tensor(value, device=self.device).to(torch.int32))
+
+    def get_observations(self):
+        self.extras["observations"]["critic"] = self._critic_obs()
+        return self.obs_buf, self.extras
+
+    def _critic_obs(self):
+        return self.obs_buf
+
+    def close(self):
+        self.core.close()
+
+    def poll_errno(self):
+        """Raise like Genesis' check_errno (rigid_solver.py:1189-1213) if any env hit an error bit."""
+        err = int(np.frombuffer(self.core.read_stats()[abi.STATS_ERR:abi.STATS_ERR + 1].tobytes(), dtype=np.int32)[0])
+        if err & 2:
+            raise RuntimeError("Exceeding max number of contact pairs. Please increase 'max_collision_pairs'.")
+        if err & 1:
+            raise RuntimeError("Exceeding max number of colliding geom pairs per env.")
+        return err
+
+
+class Go2EnvWalk(_Go2EnvBase):
+    """Walk env (16-dim PLS action, delay ring, manual PD, pushes, curriculum, DR, 49/104-d obs)."""
+
+    KIND = abi.ENV_WALK
+
+    def __init__(self, num_envs, env_cfg, obs_cfg, reward_cfg, command_cfg, show_viewer=False, **kw):
+        super().__init__(num_envs, env_cfg, obs_cfg, reward_cfg, command_cfg, show_viewer, **kw)
+        e = env_cfg
+        self.num_privileged_obs = obs_cfg.get("num_privileged_obs", None)
+        self.num_pos_actions = e.get("num_pos_actions", 12)
+        self.simulate_action_latency = e.get("simulate_action_latency", True)
+        self.pls_enable = bool(e.get("pls_enable", False))
+        self.num_stiffness_actions = 4 if self.pls_enable else 0
+        c = abi.EnvConfig()
+        self._fill_common(c)
+        c.num_pos_actions = self.num_pos_actions
+        c.num_priv = int(self.num_privileged_obs or 0)
+        if self.pls_enable:
+            self.pls_kp_range = e["pls_kp_range"]
+            self.pls_kp_default = float(e["pls_kp_default"])
+            self.pls_kp_action_scale = float(e["pls_kp_action_scale"])
+            c.pls_kp_default, c.pls_kp_scale = self.pls_kp_default, self.pls_kp_action_scale
+            c.pls_kp_lo, c.pls_kp_hi = float(self.pls_kp_range[0]), float(self.pls_kp_range[1])
+        tl = e.get("torque_limits", None) or [23.7] * self.num_pos_actions
+        for j in range(12):
+            c.torque_limit[j] = float(tl[j])
+        self._use_manual_pd = self.pls_enable or ("kp_factor_range" in e)
+        c.ctrl = abi.CTRL_MANUAL_PLS if self.pls_enable else (abi.CTRL_MANUAL_FIXED if self._use_manual_pd else abi.CTRL_GENESIS_PD)
+        # foot contact tracking (go2_env_walk.py:270-276,531-597)
+        link_names = [l["name"] for l in self._model["links"]]
+        self._foot_reward_names = ["feet_air_time", "foot_slip", "foot_clearance", "feet_stance"]
+        self._has_foot_contact_rewards = any(n in self.reward_scales and self.reward_scales[n] != 0.0 for n in self._foot_reward_names)
+        self._foot_link_indices = []
+        if self._has_foot_contact_rewards:
+            foot_names = e.get("foot_names", [])
+            if not foot_names:
+                raise ValueError("env_cfg['foot_names'] is required for feet_air_time/foot_slip/foot_clearance rewards.")
+            for fn in foot_names:
+                if fn not in link_names:
+                    raise RuntimeError(f"Foot link '{fn}' NOT FOUND. Available: {sorted(link_names)}")
+                self._foot_link_indices.append(link_names.index(fn))
+            self._n_feet = len(foot_names)
+            self._has_link_vel = self._has_link_pos = True
+            self._foot_contact_threshold = float(e.get("foot_contact_threshold", 1.0))
+            c.has_foot_tracking = 1
+            c.foot_contact_threshold = self._foot_contact_threshold
+            for i in range(4):
+                c.foot_link[i] = self._foot_link_indices[i]
+        self._has_leg_mass_dr = "leg_mass_shift_range" in e
+        self._hip_link_indices = [link_names.index(n) for n in ("FR_hip", "FL_hip", "RR_hip", "RL_hip")] if self._has_leg_mass_dr else []
+        # DR maxima
+        self.obs_noise_components = e.get("obs_noise", None)
+        self.obs_noise_level_max = float(e.get("obs_noise_level", 0.0)) if self.obs_noise_components else 0.0
+        self.action_noise_std_max = float(e.get("action_noise_std", 0.0)) if ("action_noise_std" in e) else 0.0
+        self.push_interval_s_hard = float(e.get("push_interval_s", 5.0))
+        self.push_force_range_hard = e.get("push_force_range", None)
+        self._push_counter = 0
+        if self.push_force_range_hard is not None:
+            self._base_link_idx = 2  # reference quirk: robot.links[1].idx == global link 2 == FL_hip (go2_env_walk.py:339-342)
+            c.has_push, c.push_link = 1, 1
+            dur = e.get("push_duration_s", [0.05, 0.15])
+            self._push_duration_steps = [max(1, int(dur[0] / self.dt)), max(1, int(dur[1] / self.dt))]
+            c.push_dur_lo, c.push_dur_hi = self._push_duration_steps
+        # commands
+        self._cmd_curriculum = bool(command_cfg.get("cmd_curriculum", False))
+        self._cmd_start_frac = float(command_cfg.get("cmd_curriculum_start_frac", 0.1))
+        self._rel_standing_envs = float(command_cfg.get("rel_standing_envs", 0.0))
+        self._compound_commands = bool(command_cfg.get("compound_commands", True))
+        self._cmd_full_ranges = {k: list(command_cfg[k + "_range"]) for k in ("lin_vel_x", "lin_vel_y", "ang_vel")}
+        self._cmd_cur_ranges = {k: list(v) for k, v in self._cmd_full_ranges.items()}
+        c.compound_commands = int(self._compound_commands)
+        c.n_standing = int(self._rel_standing_envs * self._total_envs)  # by GLOBAL env index
+        # delay ring
+        self._min_delay_steps = int(e.get("min_delay_steps", 0))
+        self._max_delay_steps = int(e.get("max_delay_steps", 2))
+        self._delay_buf_size = self._max_delay_steps + 1
+        self._action_history_write_idx = 0
+        c.hist_size, c.min_delay, c.max_delay = self._delay_buf_size, self._min_delay_steps, self._max_delay_steps
+        # per-episode DR switches
+        c.has_kp_factor, c.has_kd_factor = int("kp_factor_range" in e), int("kd_factor_range" in e)
+        c.has_kp_range = int((not self.pls_enable) and "kp_range" in e)
+        c.has_motor_strength, c.has_gravity_offset = int("motor_strength_range" in e), int("gravity_offset_range" in e)
+        c.has_delay = 1
+        if "init_pos_z_range" in e:
+            c.has_init_z, c.init_z_lo, c.init_z_hi = 1, float(e["init_pos_z_range"][0]), float(e["init_pos_z_range"][1])
+        if "init_euler_range" in e:
+            c.has_init_euler = 1
+            c.init_euler_lo, c.init_euler_hi = math.radians(e["init_euler_range"][0]), math.radians(e["init_euler_range"][1])
+        self._bind(c)
+        b = self.core.buf
+        self.privileged_obs_buf = b["priv"] if self.num_privileged_obs else self.obs_buf
+        self._applied_actions = b["applied"]
+        self._action_history = b["hist"].view(self.num_envs, self._delay_buf_size, self.num_actions)
+        self._delay_steps = b["delay"].view(-1)
+        self._kp_factors, self._kd_factors, self._motor_strength = b["kp_factors"], b["kd_factors"], b["motor_strength"]
+        self._effective_kp, self._effective_kd = b["eff_kp"], b["eff_kd"]
+        self._gravity_offset, self._current_push_force = b["grav_off"], b["cur_push"]
+        self._push_stored_force, self._push_remaining = b["push_force"], b["push_remain"].view(-1)
+        self._target_dof_pos = b["target"]
+        if self._has_foot_contact_rewards:
+            self._foot_contact = b["foot_contact"].view(torch.bool)
+            self._last_foot_contact = b["last_foot_contact"].view(torch.bool)
+            self._feet_air_time = b["air_time"]
+        # curriculum + DR ranges (go2_env_walk.py:457-514)
+        self.curr_cfg = e.get("curriculum", {}) or {}
+        cc = self.curr_cfg
+        self.curriculum = Curriculum(cc, self._np_rng)
+        self._curr_ep_total, self._curr_timeout_total, self._curr_tracking_sum, self._curr_tracking_n = 0, 0.0, 0.0, 0
+        self.curr_update_every_episodes = int(cc.get("update_every_episodes", 2048))
+        kp_nom, kd_nom = float(e.get("kp", 60.0)), float(e.get("kd", 2.0))
+        self.friction_easy = cc.get("friction_easy", [0.6, 0.9]); self.friction_hard = e.get("friction_range", self.friction_easy)
+        self.kp_easy = cc.get("kp_easy", [0.9 * kp_nom, 1.1 * kp_nom]); self.kp_hard = e.get("kp_range", self.kp_easy)
+        self.kd_easy = cc.get("kd_easy", [0.75 * kd_nom, 1.25 * kd_nom]); self.kd_hard = e.get("kd_range", self.kd_easy)
+        self.kp_factor_easy = cc.get("kp_factor_easy", [0.95, 1.05]); self.kp_factor_hard = e.get("kp_factor_range", self.kp_factor_easy)
+        self.kd_factor_easy = cc.get("kd_factor_easy", [0.85, 1.15]); self.kd_factor_hard = e.get("kd_factor_range", self.kd_factor_easy)
+        self.mass_easy = cc.get("mass_shift_easy", [-0.2, 0.5]); self.mass_hard = e.get("mass_shift_range", self.mass_easy)
+        self.com_easy = cc.get("com_shift_easy", [-0.005, 0.005]); self.com_hard = e.get("com_shift_range", self.com_easy)
+        self.gravity_offset_easy = cc.get("gravity_offset_easy", [-0.2, 0.2]); self.gravity_offset_hard = e.get("gravity_offset_range", self.gravity_offset_easy)
+        self.motor_strength_easy = cc.get("motor_strength_easy", [0.97, 1.03]); self.motor_strength_hard = e.get("motor_strength_range", self.motor_strength_easy)
+        self.leg_mass_easy = cc.get("leg_mass_shift_easy", [-0.1, 0.1]); self.leg_mass_hard = e.get("leg_mass_shift_range", self.leg_mass_easy)
+        self.delay_easy_max = int(cc.get("delay_easy_max_steps", 1))
+        self.push_start = float(cc.get("push_start", 0.30))
+        self.push_interval_s_easy = float(cc.get("push_interval_easy_s", 6.0))
+        self._global_dr_update_interval = int(cc.get("global_dr_update_interval", 200))
+        self._global_dr_reset_counter = 0
+        # global physics DR currently in force (Genesis semantics: one value for every env)
+        self._friction = 1.0
+        self._mass_shift = np.zeros(abi.NLINK, dtype=np.float32)
+        self._com_shift = np.zeros(3, dtype=np.float32)
+        self._kp_genesis, self._kd_genesis = (0.0, 0.0) if self._use_manual_pd else (kp_nom, kd_nom)
+        self._obs_noise_level_cur = self._action_noise_std_cur = 0.0
+        self._push_enable_cur = False
+        self._push_interval = int(self.push_interval_s_easy / self.dt) if self.push_force_range_hard is not None else 1
+        self._push_force_range_cur = [0.0, 0.0]
+        self._delay_max_cur = self.delay_easy_max
+        self.obs_noise_vec = None
+        self._apply_curriculum_level(force=True)
+        self.robot = _RobotFacade(self)
+        self.ground = _GroundFacade(self)
+        self.scene = _SceneFacade(self)
+
+    # ---- curriculum-driven runtime values (go2_env_walk.py:611-686)
+    def _rebuild_obs_noise_vec(self, level):
+        if self.obs_noise_components is None or self.obs_noise_level_max <= 0.0:
+            self.obs_noise_vec = None
+            return
+        nl = _lerp(0.0, self.obs_noise_level_max, level)
+        nc, s = self.obs_noise_components, self.obs_scales
+        nv = np.zeros(self.num_obs, dtype=np.float32)
+        nv[0:3] = nc.get("ang_vel", 0.0) * s["ang_vel"] * nl
+        nv[3:6] = nc.get("gravity", 0.0) * nl
+        nv[9:21] = nc.get("dof_pos", 0.0) * s["dof_pos"] * nl
+        nv[21:33] = nc.get("dof_vel", 0.0) * s["dof_vel"] * nl
+        self.obs_noise_vec = nv
+
+    def _apply_curriculum_level(self, force=False):
+        if not self.curriculum.enabled and not force:
+            return
+        lvl = float(self.curriculum.level) if self.curriculum.enabled else 1.0
+        self._obs_noise_level_cur = _lerp(0.0, self.obs_noise_level_max, lvl)
+        self._action_noise_std_cur = _lerp(0.0, self.action_noise_std_max, lvl)
+        self._rebuild_obs_noise_vec(lvl)
+        if self.push_force_range_hard is None:
+            self._push_enable_cur, self._push_force_range_cur, self._push_interval = False, [0.0, 0.0], 10**9
+        elif lvl < self.push_start:
+            self._push_enable_cur, self._push_force_range_cur = False, [0.0, 0.0]
+            self._push_interval = int(self.push_interval_s_easy / self.dt)
+        else:
+            s = _clamp01((lvl - self.push_start) / max(1e-6, (1.0 - self.push_start)))
+            lo, hi = float(self.push_force_range_hard[0]), float(self.push_force_range_hard[1])
+            self._push_force_range_cur = [lo * s, hi * s]
+            self._push_interval = max(1, int(_lerp(self.push_interval_s_easy, self.push_interval_s_hard, s) / self.dt))
+            self._push_enable_cur = True
+        self._delay_max_cur = int(round(_lerp(float(self.delay_easy_max), float(self._max_delay_steps), lvl)))
+        if self._cmd_curriculum:
+            frac = _lerp(self._cmd_start_frac, 1.0, lvl)
+            for k, fr in self._cmd_full_ranges.items():
+                ctr, half = (fr[0] + fr[1]) / 2.0, (fr[1] - fr[0]) / 2.0
+                self._cmd_cur_ranges[k] = [ctr - half * frac, ctr + half * frac]
+        else:
+            self._cmd_cur_ranges = {k: list(v) for k, v in self._cmd_full_ranges.items()}
+        cur = self.extras.setdefault("curriculum", {})
+        cur.update(self.curriculum.state_dict())
+        cur.update({"obs_noise_level_cur": float(self._obs_noise_level_cur), "action_noise_std_cur": float(self._action_noise_std_cur),
+                    "push_enable": bool(self._push_enable_cur), "push_force_range_cur": list(self._push_force_range_cur),
+                    "push_interval_steps": int(self._push_interval), "delay_max_cur": int(self._delay_max_cur),
+                    "cmd_ranges": {k: list(v) for k, v in self._cmd_cur_ranges.items()}})
+
+    # ---- per-step parameter block
+    def _make_params(self, physics=True):
+        sp = abi.StepParams()
+        sp.step_count = self._step_count & 0xFFFFFFFF
+        sp.do_physics = 1 if physics else 0
+        sp.hist_write_idx = self._action_history_write_idx
+        if physics:
+            self._action_history_write_idx = (self._action_history_write_idx + 1) % self._delay_buf_size
+        sp.push_enable = int(self.push_force_range_hard is not None and self._push_enable_cur)
+        if physics and sp.push_enable:
+            sp.push_resample = int(self._push_counter % self._push_interval == 0)
+            self._push_counter += 1
+        sp.push_lo, sp.push_hi = float(self._push_force_range_cur[0]), float(self._push_force_range_cur[1])
+        sp.action_noise_std = float(self._action_noise_std_cur)
+        if self.obs_noise_vec is not None:
+            sp.obs_noise_on = 1
+            for i in range(self.num_obs):
+                sp.obs_noise[i] = float(self.obs_noise_vec[i])
+        for i, k in enumerate(("lin_vel_x", "lin_vel_y", "ang_vel")):
+            sp.cmd_lo[i], sp.cmd_hi[i] = float(self._cmd_cur_ranges[k][0]), float(self._cmd_cur_ranges[k][1])
+        t = self._t_sample = self.curriculum.sample_level()
+        sp.kpf_lo, sp.kpf_hi = _lerp_range(self.kp_factor_easy, self.kp_factor_hard, t)
+        sp.kdf_lo, sp.kdf_hi = _lerp_range(self.kd_factor_easy, self.kd_factor_hard, t)
+        sp.kp_lo, sp.kp_hi = _lerp_range(self.kp_easy, self.kp_hard, t)
+        sp.kd_lo, sp.kd_hi = _lerp_range(self.kd_easy, self.kd_hard, t)
+        sp.ms_lo, sp.ms_hi = _lerp_range(self.motor_strength_easy, self.motor_strength_hard, t)
+        sp.go_lo, sp.go_hi = _lerp_range(self.gravity_offset_easy, self.gravity_offset_hard, t)
+        sp.delay_lo = self._min_delay_steps
+        sp.delay_hi = max(self._min_delay_steps, min(self._delay_max_cur, self._max_delay_steps))
+        sp.friction = float(self._friction)
+        for l in range(abi.NLINK):
+            sp.mass_shift[l] = float(self._mass_shift[l])
+        for j in range(3):
+            sp.com_shift[j] = float(self._com_shift[j])
+        sp.kp_genesis, sp.kd_genesis = float(self._kp_genesis), float(self._kd_genesis)
+        self._step_count += 1
+        return sp
+
+    # ---- host side of reset_idx: curriculum aggregates, global DR, episode log (go2_env_walk.py:688-756,803-848,1228-1235)
+    def _after_resets(self, stats):
+        n = int(round(float(stats[abi.STATS_RESETS])))
+        if n <= 0:
+            return
+        if self.curriculum.enabled:
+            self._curr_ep_total += n
+            self._curr_timeout_total += float(stats[abi.STATS_TIMEOUTS])
+            self._curr_tracking_sum += float(stats[abi.STATS_TRACKING])
+            self._curr_tracking_n += n
+            if self._curr_ep_total >= self.curr_update_every_episodes:
+                tr = float(self._curr_timeout_total / max(1, self._curr_ep_total))
+                if self.curriculum.update(tr, float(self._curr_tracking_sum / max(1, self._curr_tracking_n)), float(1.0 - tr)):
+                    self._apply_curriculum_level()
+                self._curr_ep_total, self._curr_timeout_total, self._curr_tracking_sum, self._curr_tracking_n = 0, 0.0, 0.0, 0
+        t, e, rng = self._t_sample, self.env_cfg, self._np_rng
+        dr = self.extras.setdefault("domain_randomization", {})
+        if "friction_range" in e:
+            self._global_dr_reset_counter += n
+            if self._global_dr_reset_counter >= self._global_dr_update_interval:
+                self._global_dr_reset_counter = 0
+                lo, hi = _lerp_range(self.friction_easy, self.friction_hard, t)
+                self._friction = float((hi - lo) * rng.random() + lo)
+                dr["friction"] = self._friction
+        if "mass_shift_range" in e:
+            lo, hi = _lerp_range(self.mass_easy, self.mass_hard, t)
+            self._mass_shift[0] = (hi - lo) * rng.random() + lo
+            dr["mass_shift"] = float(self._mass_shift[0])
+        if "com_shift_range" in e:
+            lo, hi = _lerp_range(self.com_easy, self.com_hard, t)
+            self._com_shift[:] = [(hi - lo) * rng.random() + lo for _ in range(3)]
+        if self._has_leg_mass_dr:
+            lo, hi = _lerp_range(self.leg_mass_easy, self.leg_mass_hard, t)
+            for l in self._hip_link_indices:
+                self._mass_shift[l] = (hi - lo) * rng.random() + lo
+        self.extras["episode"] = {"rew_" + name: float(stats[abi.STATS_REW0 + k]) / n for k, name in enumerate(self._reward_names)}
+
+    def _critic_obs(self):
+        return self.privileged_obs_buf if self.num_privileged_obs else self.obs_buf
+
+    def get_privileged_observations(self):
+        return self.privileged_obs_buf if self.num_privileged_obs is not None else None
+
+    def step(self, actions):
+        sp = self._make_params(physics=True)
+        self.core.step(actions, sp)
+        self.actions = self.last_actions  # after the tick last_actions holds the clipped policy output
+        if self.stats_sync_interval > 0 and self._step_count % self.stats_sync_interval == 0:
+            self._after_resets(self.core.read_stats())
+        self.extras["observations"]["critic"] = self._critic_obs()
+        return self.obs_buf, self.rew_buf, self.reset_buf, self.extras
+
+    def reset(self):
+        sp = self._make_params(physics=False)
+        self.core.reset_all(sp)
+        self._after_resets(self.core.read_stats())
+        return self.obs_buf, None
+
+
+class Go2EnvBaseFlavour(_Go2EnvBase):
+    """Genesis stock Go2 env used by the crouch / jump scripts (go2_env_base.py): 12-dim action, 1-step
+    latency through last_actions, solver-side PD, reset BEFORE rewards, 45-d obs, no privileged obs."""
+
+    KIND = abi.ENV_BASE
+
+    def __init__(self, num_envs, env_cfg, obs_cfg, reward_cfg, command_cfg, show_viewer=False, **kw):
+        super().__init__(num_envs, env_cfg, obs_cfg, reward_cfg, command_cfg, show_viewer, **kw)
+        self.num_privileged_obs = None
+        self.simulate_action_latency = True
+        c = abi.EnvConfig()
+        self._fill_common(c)
+        c.num_pos_actions, c.num_priv, c.ctrl = 12, 0, abi.CTRL_GENESIS_PD
+        c.simulate_action_latency = 1
+        c.hist_size = 1
+        c.compound_commands = 1
+        for j in range(12):
+            c.torque_limit[j] = 1e30
+        self._bind(c)
+        self._kp_genesis, self._kd_genesis = float(env_cfg["kp"]), float(env_cfg["kd"])
+        self._friction = 1.0
+        self._mass_shift = np.zeros(abi.NLINK, dtype=np.float32)
+        self._com_shift = np.zeros(3, dtype=np.float32)
+        self.robot = _RobotFacade(self)
+        self.scene = _SceneFacade(self)
+
+    def _make_params(self, physics=True):
+        sp = abi.StepParams()
+        sp.step_count = self._step_count & 0xFFFFFFFF
+        sp.do_physics = 1 if physics else 0
+        cc = self.command_cfg
+        for i, k in enumerate(("lin_vel_x_range", "lin_vel_y_range", "ang_vel_range")):
+            sp.cmd_lo[i], sp.cmd_hi[i] = float(cc[k][0]), float(cc[k][1])
+        sp.friction = float(self._friction)
+        for l in range(abi.NLINK):
+            sp.mass_shift[l] = float(self._mass_shift[l])
+        for j in range(3):
+            sp.com_shift[j] = float(self._com_shift[j])
+        sp.kp_genesis, sp.kd_genesis = float(self._kp_genesis), float(self._kd_genesis)
+        sp.delay_lo = sp.delay_hi = 0
+        self._step_count += 1
+        return sp
+
+    def _after_resets(self, stats):
+        n = int(round(float(stats[abi.STATS_RESETS])))
+        if n <= 0:
+            return
+        ep_s = float(self.env_cfg["episode_length_s"])  # go2_env_base.py:231-236: mean(sum) / episode_length_s
+        self.extras["episode"] = {"rew_" + name: float(stats[abi.STATS_REW0 + k]) / n / ep_s for k, name in enumerate(self._reward_names)}
+
+    def get_privileged_observations(self):
+        return None
+
+    def step(self, actions):
+        sp = self._make_params(physics=True)
+        self.core.step(actions, sp)
+        self.actions = self.last_actions
+        if self.stats_sync_interval > 0 and self._step_count % self.stats_sync_interval == 0:
+            self._after_resets(self.core.read_stats())
+        self.extras["observations"]["critic"] = self.obs_buf
+        return self.obs_buf, self.rew_buf, self.reset_buf, self.extras
+
+    def reset(self):
+        sp = self._make_params(physics=False)
+        self.core.reset_all(sp)
+        self._after_resets(self.core.read_stats())
+        return self.obs_buf, None
+
+
+# ---------------------------------------------------------------------------------------------------
+# Facades for the scene-level attribute surface the eval scripts poke: env.robot.*,
+# env.ground.set_friction, env.scene.sim.rigid_solver.apply_links_external_force.  They edit the same
+# device buffers / host scalars the step kernel reads.
+# ---------------------------------------------------------------------------------------------------
+class _Link:
+    def __init__(self, name, idx):
+        self.name, self.idx = name, idx
+
+
+class _Joint:
+    def __init__(self, name, dof_start):
+        self.name, self.dof_start = name, dof_start
+
+
+class _RobotFacade:
+    def __init__(self, env):
+        self._env = env
+        self.links = [_Link(l["name"], i + 1) for i, l in enumerate(env._model["links"])]  # .idx is global (ground = 0)
+        self._joints = {l["joint_name"]: _Joint(l["joint_name"], l["dof_start"]) for l in env._model["links"]}
+
+    def get_joint(self, name):
+        return self._joints[name]
+
+    def _idx(self, envs_idx):
+        e = self._env
+        return torch.arange(e.num_envs, device=e.device) if envs_idx is None else torch.as_tensor(envs_idx, device=e.device).long()
+
+    def zero_all_dofs_velocity(self, envs_idx=None):
+        self._env.core.buf["qvel"][:, self._idx(envs_idx)] = 0.0
+
+    def set_dofs_position(self, position, dofs_idx_local=None, zero_velocity=True, envs_idx=None):
+        ii = self._idx(envs_idx)
+        dofs = list(range(18)) if dofs_idx_local is None else list(dofs_idx_local)
+        pos = torch.as_tensor(position, device=self._env.device, dtype=torch.float32).reshape(len(ii), len(dofs))
+        q = self._env.core.buf["qpos"]
+        for k, d in enumerate(dofs):
+            q[d + 1, ii] = pos[:, k]
+        if zero_velocity:
+            self.zero_all_dofs_velocity(envs_idx)
+
+    def set_pos(self, pos, zero_velocity=True, envs_idx=None):
+        ii = self._idx(envs_idx)
+        p = torch.as_tensor(pos, device=self._env.device, dtype=torch.float32).reshape(len(ii), 3)
+        self._env.core.buf["qpos"][0:3, ii] = p.t()
+        if zero_velocity:
+            self.zero_all_dofs_velocity(envs_idx)
+
+    def set_quat(self, quat, zero_velocity=True, envs_idx=None):
+        ii = self._idx(envs_idx)
+        q = torch.as_tensor(quat, device=self._env.device, dtype=torch.float32).reshape(len(ii), 4)
+        self._env.core.buf["qpos"][3:7, ii] = q.t()
+        if zero_velocity:
+            self.zero_all_dofs_velocity(envs_idx)
+
+    def get_pos(self):
+        return self._env.core.buf["qpos"][0:3].t().contiguous()
+
+    def get_quat(self):
+        q = self._env.core.buf["qpos"][3:7].t()
+        return q / q.norm(dim=1, keepdim=True)
+
+    def get_dofs_position(self, dofs=None):
+        q = self._env.core.buf["qpos"]
+        return torch.stack([q[d + 1] for d in (dofs if dofs is not None else range(6, 18))], dim=1)
+
+    def get_dofs_velocity(self, dofs=None):
+        v = self._env.core.buf["qvel"]
+        return torch.stack([v[d] for d in (dofs if dofs is not None else range(18))], dim=1)
+
+    def get_dofs_control_force(self, dofs=None):
+        return self._env.core.buf["torque"]
+
+    def _links(self):
+        self._env.core.export_links(self._env._make_params(physics=False))
+        self._env._step_count -= 1
+
+    def get_links_pos(self):
+        self._links()
+        return self._env.core.buf["link_pos"].view(self._env.num_envs, 13, 3)
+
+    def get_links_vel(self):
+        self._links()
+        return self._env.core.buf["link_vel"].view(self._env.num_envs, 13, 3)
+
+    def get_vel(self):
+        return self.get_links_vel()[:, 0]
+
+    def get_links_net_contact_force(self):
+        return self._env.core.buf["contact_force"].view(self._env.num_envs, 13, 3)
+
+    def set_friction(self, mu):
+        self._env._friction = float(mu)
+
+    def set_mass_shift(self, shifts, links_idx_local):
+        for s, l in zip(shifts, links_idx_local):
+            self._env._mass_shift[int(l)] = float(s)
+
+    def set_COM_shift(self, shifts, links_idx_local):
+        for s, l in zip(shifts, links_idx_local):
+            if int(l) != 0:
+                raise NotImplementedError("COM shift is supported for the base link only (all the envs use)")
+            self._env._com_shift[:] = np.asarray(torch.as_tensor(s).cpu(), dtype=np.float32)
+
+    def set_dofs_kp(self, kp, dofs=None):
+        self._env._kp_genesis = float(kp[0])
+
+    def set_dofs_kv(self, kv, dofs=None):
+        self._env._kd_genesis = float(kv[0])
+
+
+class _GroundFacade:
+    def __init__(self, env):
+        self._env = env
+
+    def set_friction(self, mu):
+        self._env._friction = float(mu)
+
+
+class _SceneFacade:
+    def __init__(self, env):
+        import types
+
+        self.sim = types.SimpleNamespace(rigid_solver=self)
+        self._env = env
+
+    def apply_links_external_force(self, force, links_idx, envs_idx=None):
+        raise NotImplementedError("external forces are applied inside the fused step (env_cfg['push_force_range'])")
+
+    def step(self):
+        raise NotImplementedError("scene.step() is fused into Go2Env.step()")

@@ -1,0 +1,66 @@
+"""Parity of the fused step against golden vectors produced by the UNMODIFIED reference env classes running
+on the CPU oracle (oracle/gen_golden.py).  Two regimes:
+  * teacher-forced: every step starts from the fixture's pre-step state -> one-step outputs must agree within
+    fp32 tolerance, integer / boolean outputs bit-exactly (except at numerically borderline thresholds);
+  * free-running: the first steps of the trajectory agree tightly (contact-mode switches make both fp32
+    implementations diverge chaotically later - SURVEY.md 8(d) parity acceptance).
+Backends: `hostemu` = the kernel source compiled for the CPU (runs in the build container), `cuda` = the
+real library on a B200 (marked gpu).  Tolerance: |d| <= 2e-4 + 2e-3 |x|.
+"""
+import numpy as np
+import pytest
+import torch
+
+from util import close, force_state, load_golden, make_env, np_
+
+ATOL, RTOL = 2e-4, 2e-3
+BACKENDS = ["hostemu", pytest.param("cuda", marks=pytest.mark.gpu)]
+CASES = [("walk_det", "walk"), ("walk_short", "walk"), ("crouch", "base"), ("jump", "base")]
+
+
+def _frac_ok(a, b):
+    return float(close(a, b, ATOL, RTOL).mean())
+
+
+@pytest.mark.parametrize("backend", BACKENDS)
+@pytest.mark.parametrize("name,kind", CASES)
+def test_teacher_forced(name, kind, backend, hostemu_lib):
+    g, cfgs = load_golden(name)
+    T, B = g["actions"].shape[:2]
+    env = make_env(kind, cfgs, B, backend, hostemu_lib)
+    env.reset()
+    n_bad_reset = n_bad_float = n_checked = 0
+    for t in range(T):
+        force_state(env, g, t, kind)
+        obs, rew, done, extras = env.step(torch.as_tensor(g["actions"][t], device=env.device))
+        done_np = np_(done).astype(np.uint8)
+        n_bad_reset += int((done_np != g["o_reset"][t]).sum())
+        same = done_np == g["o_reset"][t]
+        assert np.array_equal(np_(extras["time_outs"])[same], g["o_timeout"][t][same])
+        assert np.array_equal(np_(env.episode_length_buf)[same], g["o_ep_len"][t][same])
+        ok = close(np_(obs), g["o_obs"][t], ATOL, RTOL).all(1) & close(np_(rew), g["o_rew"][t], ATOL, RTOL)
+        ok &= close(np_(env.core.buf["qpos"]).T, g["o_qpos"][t], ATOL, RTOL).all(1)
+        ok &= close(np_(env.core.buf["qvel"]).T, g["o_qvel"][t], 10 * ATOL, RTOL).all(1)
+        if kind == "walk":
+            ok &= close(np_(extras["observations"]["critic"]), g["o_priv"][t], ATOL, RTOL).all(1)
+            ok &= (np_(env._foot_contact) == g["o_foot_contact"][t]).all(1)
+        n_bad_float += int((~ok[same]).sum())
+        n_checked += int(same.sum())
+    # integer outputs must match; allow a vanishing number of threshold-borderline disagreements
+    assert n_bad_reset <= max(1, T * B // 500), f"{n_bad_reset} reset mismatches"
+    assert n_bad_float <= max(2, n_checked // 100), f"{n_bad_float}/{n_checked} env-steps outside tolerance"
+
+
+@pytest.mark.parametrize("backend", BACKENDS)
+@pytest.mark.parametrize("name,kind,horizon", [("walk_det", "walk", 30), ("jump", "base", 12)])
+def test_free_running_prefix(name, kind, horizon, backend, hostemu_lib):
+    g, cfgs = load_golden(name)
+    T, B = g["actions"].shape[:2]
+    env = make_env(kind, cfgs, B, backend, hostemu_lib)
+    env.reset()
+    for t in range(horizon):
+        obs, rew, done, extras = env.step(torch.as_tensor(g["actions"][t], device=env.device))
+        assert np.array_equal(np_(done).astype(np.uint8), g["o_reset"][t]), f"reset mismatch at step {t}"
+        assert _frac_ok(np_(env.core.buf["qpos"]).T, g["o_qpos"][t]) == 1.0, f"qpos diverged at step {t}"
+        assert _frac_ok(np_(rew), g["o_rew"][t]) == 1.0, f"reward diverged at step {t}"
+        assert _frac_ok(np_(obs), g["o_obs"][t]) >= 0.99
