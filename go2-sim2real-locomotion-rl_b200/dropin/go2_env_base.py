@@ -1,0 +1,6 @@
+"""Drop-in replacement for examples/locomotion/final/go2_env_base.py: `from go2_env_base import Go2Env`."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from go2_b200.envs import Go2EnvBaseFlavour as Go2Env  # noqa: E402,F401

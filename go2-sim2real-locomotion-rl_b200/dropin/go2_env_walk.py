@@ -1,0 +1,7 @@
+"""Drop-in replacement for examples/locomotion/final/go2_env_walk.py: `from go2_env_walk import Go2Env`."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from go2_b200.envs import Curriculum as CurriculumManager  # noqa: E402,F401
+from go2_b200.envs import Go2EnvWalk as Go2Env  # noqa: E402,F401
