@@ -1,22 +1,21 @@
 // go2_b200 - device buffer table.  The library owns one arena; the Python side wraps each entry as a
-// non-owning torch view (see go2_b200/env.py).  Two layouts:
-//   * physics state: SoA, batch LAST  ([K][B], thread-per-env loads are fully coalesced);
-//   * env-level tensors the reference exposes as torch attributes: batch FIRST ([B][K]) so that the
-//     views have the reference's shapes and can be indexed / assigned by user code.
+// non-owning torch view (see go2_b200/core.py).
+// every buffer is env-major ([B][K]): with one warp per env the lanes read one env's row contiguously, and
+// the env-level tensors the reference exposes as torch attributes get the reference's shapes.
 #pragma once
 #include "go2_types.cuh"
 
 namespace go2 {
 
 enum BufId {
-    // ---- physics state, batch last
-    B_QPOS = 0,      // f32 [19][B]
-    B_QVEL,          // f32 [18][B]
-    B_QACC_WS,       // f32 [18][B]
+    // ---- physics state, env-major (one warp loads one env's rows with coalesced lane accesses)
+    B_QPOS = 0,      // f32 [B][19]
+    B_QVEL,          // f32 [B][18]
+    B_QACC_WS,       // f32 [B][18]
     B_WARM,          // i32 [B]
     B_NCACHE,        // i32 [B]
-    B_CACHE_PAIR,    // i32 [MAX_CPAIRS][B]
-    B_CACHE_N,       // f32 [MAX_CPAIRS*3][B]
+    B_CACHE_PAIR,    // i32 [B][MAX_CPAIRS]
+    B_CACHE_N,       // f32 [B][MAX_CPAIRS*3]
     // ---- env tensors, batch first
     B_ACTIONS_IN,    // f32 [B][A]   (staging copy of the policy output for host-buffer calls)
     B_OBS,           // f32 [B][num_obs]
@@ -52,7 +51,7 @@ enum BufId {
     B_FOOT_CONTACT,  // u8  [B][4]
     B_LAST_FOOT_CONTACT, // u8 [B][4]
     B_AIR_TIME,      // f32 [B][4]
-    B_EP_SUMS,       // f32 [n_rew][B]   (batch last: one torch view per reward name)
+    B_EP_SUMS,       // f32 [B][n_rew]
     B_ERRNO,         // i32 [B]
     B_LINK_POS,      // f32 [B][13][3]  robot link origins (get_links_pos)
     B_LINK_VEL,      // f32 [B][13][3]

@@ -19,7 +19,8 @@ struct GeomPose {
     q4 quat;
 };
 
-G2_HD GeomPose geom_pose(const Go2Model& m, const Phys& p, int g) {
+template <class P>
+G2_HD GeomPose geom_pose(const Go2Model& m, const P& p, int g) {
     GeomPose r;
     int l = m.g_link[g];
     if (l < 0) {

@@ -8,7 +8,7 @@
 // reset -> obs.  Base: termination -> reset -> rewards -> obs.
 #pragma once
 #include "go2_buffers.cuh"
-#include "go2_solve.cuh"
+#include "go2_warp.cuh"
 
 namespace go2 {
 
@@ -46,42 +46,8 @@ G2_HD v3 quat_to_rpy_deg(q4 q) {
     return mk3(r * k, pch * k, y * k);
 }
 
-G2_HD void load_phys(const Buffers& bf, int b, Phys& p) {
-    int B = bf.B;
-    for (int i = 0; i < NQ; ++i) p.qpos[i] = F32(B_QPOS)[i * B + b];
-    for (int i = 0; i < NV; ++i) p.qvel[i] = F32(B_QVEL)[i * B + b];
-    for (int i = 0; i < NV; ++i) p.qacc_ws[i] = F32(B_QACC_WS)[i * B + b];
-    p.warm = I32(B_WARM)[b];
-    int nc = I32(B_NCACHE)[b];
-    p.n_cache = nc;
-    for (int k = 0; k < nc; ++k) {
-        p.cache_pair[k] = I32(B_CACHE_PAIR)[k * B + b];
-        p.cache_n[k] = mk3(F32(B_CACHE_N)[(3 * k) * B + b], F32(B_CACHE_N)[(3 * k + 1) * B + b], F32(B_CACHE_N)[(3 * k + 2) * B + b]);
-    }
-    p.err = 0;
-    p.cost = 0.0f;
-    p.pd_mode = 0; p.pd_kp = 0.0f; p.pd_kv = 0.0f;
-    for (int l = 0; l < NLINK; ++l) p.cforce[l] = mk3(0, 0, 0);
-    p.n_contacts = 0;
-    p.n_rows = 0;
-    p.n_newton = 0;
-}
-G2_HD void store_phys(const Buffers& bf, int b, const Phys& p) {
-    int B = bf.B;
-    for (int i = 0; i < NQ; ++i) F32(B_QPOS)[i * B + b] = p.qpos[i];
-    for (int i = 0; i < NV; ++i) F32(B_QVEL)[i * B + b] = p.qvel[i];
-    for (int i = 0; i < NV; ++i) F32(B_QACC_WS)[i * B + b] = p.qacc_ws[i];
-    I32(B_WARM)[b] = p.warm;
-    I32(B_NCACHE)[b] = p.n_cache;
-    for (int k = 0; k < p.n_cache; ++k) {
-        I32(B_CACHE_PAIR)[k * B + b] = p.cache_pair[k];
-        F32(B_CACHE_N)[(3 * k) * B + b] = p.cache_n[k].x;
-        F32(B_CACHE_N)[(3 * k + 1) * B + b] = p.cache_n[k].y;
-        F32(B_CACHE_N)[(3 * k + 2) * B + b] = p.cache_n[k].z;
-    }
-}
-
-G2_HD v3 link_vel_world(const Phys& p, int l) { return p.cd_v[l] + cross(p.cd_a[l], p.lpos[l] - p.root_com); }
+template <class P>
+G2_HD v3 link_vel_world(const P& p, int l) { return p.cd_v[l] + cross(p.cd_a[l], p.lpos[l] - p.root_com); }
 
 G2_HD void resample_commands(const EnvConfig& cfg, const StepParams& sp, const Rng& rng, uint32_t slot, int gid, float* cmd) {
     u4 r = rng4(rng, slot);
@@ -110,7 +76,8 @@ struct EnvLocal {
     int ep_len;
 };
 
-G2_HDN float reward_term(int id, const Go2Model& m, const EnvConfig& cfg, const Phys& p, EnvLocal& e) {
+template <class P>
+G2_HDN float reward_term(int id, const Go2Model& m, const EnvConfig& cfg, const P& p, EnvLocal& e) {
     const float dt = 0.02f;
     switch (id) {
         case R_TRACKING_LIN_VEL: {
@@ -227,8 +194,9 @@ G2_HDN float reward_term(int id, const Go2Model& m, const EnvConfig& cfg, const 
 }
 
 // Reset of one env (walk: go2_env_walk.py:1156-1240; base: go2_env_base.py:201-238).
+template <class P>
 G2_HDN void reset_env(const Go2Model& m, const EnvConfig& cfg, const StepParams& sp, const Buffers& bf, int b, const Rng& rng,
-                      Phys& p, EnvLocal& e, EnvStepOut& out) {
+                      P& p, EnvLocal& e, EnvStepOut& out) {
     const float dt = 0.02f;
     int A = cfg.num_actions;
     if (cfg.kind != ENV_BASE) {
@@ -302,26 +270,25 @@ G2_HDN void reset_env(const Go2Model& m, const EnvConfig& cfg, const StepParams&
     float ep_s = fmaxf((float)e.ep_len, 1.0f) * dt;
     out.tracking_per_sec = 0.0f;
     for (int k = 0; k < cfg.n_rew; ++k) {
-        float s = F32(B_EP_SUMS)[k * bf.B + b];
+        float s = F32(B_EP_SUMS)[b * cfg.n_rew + k];
         out.ep_stat[k] = cfg.kind == ENV_BASE ? s : s / ep_s;
         if (cfg.rew_id[k] == R_TRACKING_LIN_VEL || cfg.rew_id[k] == R_TRACKING_ANG_VEL) out.tracking_per_sec += s / ep_s;
-        F32(B_EP_SUMS)[k * bf.B + b] = 0.0f;
+        F32(B_EP_SUMS)[b * cfg.n_rew + k] = 0.0f;
     }
     e.ep_len = 0;
     resample_commands(cfg, sp, rng, SLOT_CMD_RESET, cfg.env_offset + b, e.cmd);
 }
 
-// One control tick of env b.  `actions` is batch-first [B][A].
-G2_HDN void env_step(const Go2Model& m, const EnvConfig& cfg, const StepParams& sp, const Buffers& bf, const float* actions, int b,
-                     Phys& p, EnvStepOut& out) {
+// Scalar part of the tick BEFORE the physics (executed by one lane): loads the env-level buffers, turns the
+// action into joint torques / PD targets and sets up the push force.  `p` must hold fresh kinematics.
+template <class P>
+G2_HDN void env_pre(const Go2Model& m, const EnvConfig& cfg, const StepParams& sp, const Buffers& bf, const float* actions, int b,
+                    P& p, EnvLocal& e, EnvStepOut& out) {
     const int A = cfg.num_actions, H = cfg.hist_size;
     Rng rng;
     rng.env = (uint32_t)(cfg.env_offset + b); rng.step = sp.step_count; rng.k0 = cfg.seed_lo; rng.k1 = cfg.seed_hi;
-    EnvLocal e;
     out.reset = 0; out.timeout = 0; out.tracking_per_sec = 0.0f;
-    load_phys(bf, b, p);
-    kinematics(m, sp.mass_shift, sp.com_shift, p);
-    velocities(m, p);
+    p.pd_mode = 0; p.pd_kp = 0.0f; p.pd_kv = 0.0f;
     for (int i = 0; i < A; ++i) e.last_act[i] = F32(B_LAST_ACTIONS)[b * A + i];
     for (int j = 0; j < NHINGE; ++j) {
         e.dof_pos[j] = F32(B_DOF_POS)[b * NHINGE + j];
@@ -413,9 +380,18 @@ G2_HDN void env_step(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
                 p.ctrl_pos[cfg.motors_dof[j]] = e.target[j];
             }
         }
-        // ---- physics
-        substep(m, p, sp.friction, sp.mass_shift, sp.com_shift);
-        substep(m, p, sp.friction, sp.mass_shift, sp.com_shift);
+    }
+}
+
+// Scalar part of the tick AFTER the physics: read-back, foot contacts, command resampling, termination,
+// rewards, reset (+ DR draws), observations, write-back of the env-level buffers.
+template <class P>
+G2_HDN void env_post(const Go2Model& m, const EnvConfig& cfg, const StepParams& sp, const Buffers& bf, int b, P& p, EnvLocal& e,
+                     EnvStepOut& out) {
+    const int A = cfg.num_actions;
+    Rng rng;
+    rng.env = (uint32_t)(cfg.env_offset + b); rng.step = sp.step_count; rng.k0 = cfg.seed_lo; rng.k1 = cfg.seed_hi;
+    if (sp.do_physics) {
         e.ep_len += 1;
         // ---- read-back
         e.base_pos = p.lpos[0];
@@ -429,7 +405,7 @@ G2_HDN void env_step(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
         for (int j = 0; j < NHINGE; ++j) {
             e.dof_pos[j] = p.qpos[cfg.motors_dof[j] + 1];
             e.dof_vel[j] = p.qvel[cfg.motors_dof[j]];
-            e.torque[j] = applied_force(m, p, cfg.motors_dof[j]);
+            e.torque[j] = w_applied_force(m, p, cfg.motors_dof[j]);
         }
         if (cfg.has_foot_tracking) {
             for (int i = 0; i < 4; ++i) {
@@ -465,12 +441,12 @@ G2_HDN void env_step(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
         if (rst) reset_env(m, cfg, sp, bf, b, rng, p, e, out);
         if (sp.do_physics) {
             if (rst) {  // live getters see the post-reset state
-                for (int j = 0; j < NHINGE; ++j) e.torque[j] = applied_force(m, p, cfg.motors_dof[j]);
+                for (int j = 0; j < NHINGE; ++j) e.torque[j] = w_applied_force(m, p, cfg.motors_dof[j]);
             }
             for (int k = 0; k < cfg.n_rew; ++k) {
                 float r = reward_term(cfg.rew_id[k], m, cfg, p, e) * cfg.rew_scale[k];
                 rew += r;
-                F32(B_EP_SUMS)[k * bf.B + b] += r;
+                F32(B_EP_SUMS)[b * cfg.n_rew + k] += r;
             }
         }
     } else {
@@ -478,7 +454,7 @@ G2_HDN void env_step(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
             for (int k = 0; k < cfg.n_rew; ++k) {
                 float r = reward_term(cfg.rew_id[k], m, cfg, p, e) * cfg.rew_scale[k];
                 rew += r;
-                F32(B_EP_SUMS)[k * bf.B + b] += r;
+                F32(B_EP_SUMS)[b * cfg.n_rew + k] += r;
             }
         }
         if (rst) reset_env(m, cfg, sp, bf, b, rng, p, e, out);
@@ -536,7 +512,6 @@ G2_HDN void env_step(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
     }
 
     // ---- write back
-    store_phys(bf, b, p);
     U8(B_RESET)[b] = rst ? 1 : 0;
     F32(B_TIMEOUT)[b] = tout ? 1.0f : 0.0f;
     I32(B_EP_LEN)[b] = e.ep_len;
@@ -573,6 +548,81 @@ G2_HDN void env_step(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
         F32(B_CONTACT_FORCE)[(b * NLINK + l) * 3 + 1] = p.cforce[l].y;
         F32(B_CONTACT_FORCE)[(b * NLINK + l) * 3 + 2] = p.cforce[l].z;
     }
+}
+
+// Per-warp shared working set: physics + the scalar env-level locals that must survive the physics phases.
+struct WarpS {
+    EnvS s;
+    EnvLocal e;
+    EnvStepOut out;
+};
+
+// One control tick of env b by one warp.  `actions` is batch-first [B][A]; physics state is env-major.
+G2_HD void w_env_step(const Go2Model& m, const EnvConfig& cfg, const StepParams& sp, const Buffers& bf, const float* actions, int b,
+                      WarpS& w) {
+    EnvS& s = w.s;
+    LANES(l) {
+        if (l < NQ) s.qpos[l] = F32(B_QPOS)[b * NQ + l];
+        if (l < NV) {
+            s.qvel[l] = F32(B_QVEL)[b * NV + l];
+            s.qacc_ws[l] = F32(B_QACC_WS)[b * NV + l];
+            s.ctrl_force[l] = 0.0f;
+            s.ctrl_pos[l] = 0.0f;
+        }
+        if (l < NLINK) s.cforce[l] = mk3(0, 0, 0);
+        int nc = I32(B_NCACHE)[b];
+        if (l < nc) {
+            s.cache_pair[l] = I32(B_CACHE_PAIR)[b * MAX_CPAIRS + l];
+            const float* cn = F32(B_CACHE_N) + (size_t)b * MAX_CPAIRS * 3 + 3 * l;
+            s.cache_n[l] = mk3(cn[0], cn[1], cn[2]);
+        }
+        if (l == 0) {
+            s.warm = I32(B_WARM)[b];
+            s.n_cache = nc;
+            s.err = 0;
+            s.cost = 0.0f;
+            s.prev_cost = 0.0f;
+            s.n_contacts = 0;
+            s.n_rows = 0;
+            s.n_newton = 0;
+            s.ext_link = -1;
+            s.ext_f = mk3(0, 0, 0);
+            s.ext_t = mk3(0, 0, 0);
+        }
+        for (int r = l; r < W_MAXR; r += 32) s.act[r] = 0;
+    }
+    WSYNC();
+    w_kinematics(m, sp.mass_shift, sp.com_shift, s);
+    w_velocities(m, s);
+    LANES(l) {
+        if (l == 0) env_pre(m, cfg, sp, bf, actions, b, s, w.e, w.out);
+    }
+    WSYNC();
+    if (sp.do_physics) {
+        w_substep(m, s, sp.friction, sp.mass_shift, sp.com_shift);
+        w_substep(m, s, sp.friction, sp.mass_shift, sp.com_shift);
+    }
+    LANES(l) {
+        if (l == 0) env_post(m, cfg, sp, bf, b, s, w.e, w.out);
+    }
+    WSYNC();
+    LANES(l) {
+        if (l < NQ) F32(B_QPOS)[b * NQ + l] = s.qpos[l];
+        if (l < NV) {
+            F32(B_QVEL)[b * NV + l] = s.qvel[l];
+            F32(B_QACC_WS)[b * NV + l] = s.qacc_ws[l];
+        }
+        if (l < s.n_cache) {
+            I32(B_CACHE_PAIR)[b * MAX_CPAIRS + l] = s.cache_pair[l];
+            float* cn = F32(B_CACHE_N) + (size_t)b * MAX_CPAIRS * 3 + 3 * l;
+            cn[0] = s.cache_n[l].x; cn[1] = s.cache_n[l].y; cn[2] = s.cache_n[l].z;
+        }
+        if (l == 0) {
+            I32(B_WARM)[b] = s.warm;
+            I32(B_NCACHE)[b] = s.n_cache;
+        }
+    }
+    WSYNC();
 }
 
 #undef F32

@@ -1,8 +1,8 @@
 // go2_b200 - CUDA kernels + C ABI (include/go2_b200.h) of the fused Go2 env step, sm_100a.
 //
-// Layout v1: one thread per environment.  A thread loads its env's persistent state (SoA, batch-last ->
-// coalesced), runs the whole control tick (torque law, 2 rigid substeps incl. collision + Newton solve,
-// rewards, reset, observations) out of registers / thread-local memory, and writes the state back once.
+// Layout v2: one WARP per environment (csrc/go2_warp.cuh).  A warp loads its env's persistent state (env-major
+// rows -> coalesced lane accesses), runs the whole control tick (torque law, 2 rigid substeps incl. collision +
+// Newton solve, rewards, reset, observations) out of shared memory, and writes the state back once.
 // No global-memory round trips between phases, one launch per tick.
 #include <cuda_runtime.h>
 #include <stdio.h>
@@ -28,42 +28,49 @@ struct go2_handle {
     std::string err;
 };
 
-#ifndef GO2_BLOCK
-#define GO2_BLOCK 64
+#ifndef GO2_WARPS
+#define GO2_WARPS 4  // envs (warps) per block
 #endif
 
-__global__ void __launch_bounds__(GO2_BLOCK) go2_step_kernel(const Go2Model* __restrict__ gm, const EnvConfig* __restrict__ gcfg,
-                                                           StepParams sp, Buffers bf, const float* __restrict__ actions) {
-    int b = blockIdx.x * blockDim.x + threadIdx.x;
+// one warp per env; the per-env working set (WarpS) lives in dynamic shared memory
+__global__ void __launch_bounds__(GO2_WARPS * 32) go2_step_kernel(const Go2Model* __restrict__ gm, const EnvConfig* __restrict__ gcfg,
+                                                                  StepParams sp, Buffers bf, const float* __restrict__ actions) {
+    extern __shared__ __align__(16) unsigned char g2_smem[];
+    int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    int b = blockIdx.x * GO2_WARPS + warp;
     if (b >= bf.B) return;
-    Phys p;
-    EnvStepOut out;
-    env_step(*gm, *gcfg, sp, bf, actions, b, p, out);
-    if (out.reset) {
+    WarpS& w = reinterpret_cast<WarpS*>(g2_smem)[warp];
+    w_env_step(*gm, *gcfg, sp, bf, actions, b, w);
+    if (lane == 0) {
+        const EnvStepOut& out = w.out;
         float* st = (float*)bf.p[B_STATS];
-        atomicAdd(&st[STATS_RESETS], 1.0f);
-        if (out.timeout) atomicAdd(&st[STATS_TIMEOUTS], 1.0f);
-        atomicAdd(&st[STATS_TRACKING], out.tracking_per_sec);
-        for (int k = 0; k < gcfg->n_rew; ++k) atomicAdd(&st[STATS_REW0 + k], out.ep_stat[k]);
+        if (out.reset) {
+            atomicAdd(&st[STATS_RESETS], 1.0f);
+            if (out.timeout) atomicAdd(&st[STATS_TIMEOUTS], 1.0f);
+            atomicAdd(&st[STATS_TRACKING], out.tracking_per_sec);
+            for (int k = 0; k < gcfg->n_rew; ++k) atomicAdd(&st[STATS_REW0 + k], out.ep_stat[k]);
+        }
+        if (w.s.err) atomicAdd(&st[STATS_ERR], 1.0f);  // number of envs that raised an errno bit this tick
     }
-    if (p.err) atomicAdd((float*)bf.p[B_STATS] + STATS_ERR, 1.0f);  // number of envs that raised an errno bit this tick
 }
 
-__global__ void __launch_bounds__(128) go2_links_kernel(const Go2Model* __restrict__ gm, StepParams sp, Buffers bf) {
-    int b = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(GO2_WARPS * 32) go2_links_kernel(const Go2Model* __restrict__ gm, StepParams sp, Buffers bf) {
+    extern __shared__ __align__(16) unsigned char g2_smem[];
+    int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    int b = blockIdx.x * GO2_WARPS + warp;
     if (b >= bf.B) return;
-    Phys p;
-    int B = bf.B;
-    for (int i = 0; i < NQ; ++i) p.qpos[i] = ((float*)bf.p[B_QPOS])[i * B + b];
-    for (int i = 0; i < NV; ++i) p.qvel[i] = ((float*)bf.p[B_QVEL])[i * B + b];
-    kinematics(*gm, sp.mass_shift, sp.com_shift, p);
-    velocities(*gm, p);
-    float* lp = (float*)bf.p[B_LINK_POS] + (size_t)b * NLINK * 3;
-    float* lv = (float*)bf.p[B_LINK_VEL] + (size_t)b * NLINK * 3;
-    for (int l = 0; l < NLINK; ++l) {
-        v3 v = link_vel_world(p, l);
-        lp[l * 3] = p.lpos[l].x; lp[l * 3 + 1] = p.lpos[l].y; lp[l * 3 + 2] = p.lpos[l].z;
-        lv[l * 3] = v.x; lv[l * 3 + 1] = v.y; lv[l * 3 + 2] = v.z;
+    EnvS& s = reinterpret_cast<WarpS*>(g2_smem)[warp].s;
+    if (lane < NQ) s.qpos[lane] = ((float*)bf.p[B_QPOS])[b * NQ + lane];
+    if (lane < NV) s.qvel[lane] = ((float*)bf.p[B_QVEL])[b * NV + lane];
+    __syncwarp();
+    w_kinematics(*gm, sp.mass_shift, sp.com_shift, s);
+    w_velocities(*gm, s);
+    if (lane < NLINK) {
+        float* lp = (float*)bf.p[B_LINK_POS] + ((size_t)b * NLINK + lane) * 3;
+        float* lv = (float*)bf.p[B_LINK_VEL] + ((size_t)b * NLINK + lane) * 3;
+        v3 v = link_vel_world(s, lane);
+        lp[0] = s.lpos[lane].x; lp[1] = s.lpos[lane].y; lp[2] = s.lpos[lane].z;
+        lv[0] = v.x; lv[1] = v.y; lv[2] = v.z;
     }
 }
 
@@ -106,6 +113,8 @@ int go2_create(const int32_t* model_iv, int n_iv, const double* model_fv, int n_
     cudaMemcpy(h->d_model, &m, sizeof(Go2Model), cudaMemcpyHostToDevice);
     cudaMemcpy(h->d_cfg, &h->cfg, sizeof(EnvConfig), cudaMemcpyHostToDevice);
     cudaMallocHost(&h->h_stats, sizeof(float) * STATS_LEN);
+    cudaFuncSetAttribute(go2_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(GO2_WARPS * sizeof(WarpS)));
+    cudaFuncSetAttribute(go2_links_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(GO2_WARPS * sizeof(WarpS)));
     std::string init(h->arena_bytes, 0);
     init_arena(c, offs, &init[0]);
     cudaMemcpy(h->arena, init.data(), h->arena_bytes, cudaMemcpyHostToDevice);
@@ -142,7 +151,7 @@ static int launch_step(go2_handle* h, const float* d_actions, const void* params
     memcpy(&sp, params, sizeof(sp));
     int B = h->cfg.num_envs;
     if (!ck(h, cudaMemsetAsync(h->bf.p[B_STATS], 0, sizeof(float) * STATS_LEN, s), "memset stats")) return -1;
-    go2_step_kernel<<<(B + GO2_BLOCK - 1) / GO2_BLOCK, GO2_BLOCK, 0, s>>>(h->d_model, h->d_cfg, sp, h->bf, d_actions);
+    go2_step_kernel<<<(B + GO2_WARPS - 1) / GO2_WARPS, GO2_WARPS * 32, GO2_WARPS * sizeof(WarpS), s>>>(h->d_model, h->d_cfg, sp, h->bf, d_actions);
     h->launches += 1;
     return ck(h, cudaGetLastError(), "go2_step_kernel") ? 0 : -1;
 }
@@ -190,7 +199,7 @@ int go2_export_links(go2_handle* h, const void* params, int params_bytes, void* 
     StepParams sp;
     memcpy(&sp, params, sizeof(sp));
     int B = h->cfg.num_envs;
-    go2_links_kernel<<<(B + 127) / 128, 128, 0, (cudaStream_t)stream>>>(h->d_model, sp, h->bf);
+    go2_links_kernel<<<(B + GO2_WARPS - 1) / GO2_WARPS, GO2_WARPS * 32, GO2_WARPS * sizeof(WarpS), (cudaStream_t)stream>>>(h->d_model, sp, h->bf);
     h->launches += 1;
     return ck(h, cudaGetLastError(), "go2_links_kernel") ? 0 : -1;
 }

@@ -9,8 +9,8 @@ namespace go2 {
 inline void compute_layout(const EnvConfig& c, int* dtype, int* rows, int* cols) {
     int B = c.num_envs, A = c.num_actions;
     auto set = [&](int id, int dt, int r, int cc) { dtype[id] = dt; rows[id] = r; cols[id] = cc; };
-    set(B_QPOS, 0, NQ, B); set(B_QVEL, 0, NV, B); set(B_QACC_WS, 0, NV, B); set(B_WARM, 1, 1, B); set(B_NCACHE, 1, 1, B);
-    set(B_CACHE_PAIR, 1, MAX_CPAIRS, B); set(B_CACHE_N, 0, MAX_CPAIRS * 3, B);
+    set(B_QPOS, 0, B, NQ); set(B_QVEL, 0, B, NV); set(B_QACC_WS, 0, B, NV); set(B_WARM, 1, B, 1); set(B_NCACHE, 1, B, 1);
+    set(B_CACHE_PAIR, 1, B, MAX_CPAIRS); set(B_CACHE_N, 0, B, MAX_CPAIRS * 3);
     set(B_ACTIONS_IN, 0, B, A); set(B_OBS, 0, B, c.num_obs); set(B_PRIV, 0, B, c.num_priv > 0 ? c.num_priv : 1);
     set(B_REW, 0, B, 1); set(B_RESET, 2, B, 1); set(B_TIMEOUT, 0, B, 1); set(B_EP_LEN, 1, B, 1); set(B_COMMANDS, 0, B, 3);
     set(B_LAST_ACTIONS, 0, B, A); set(B_APPLIED, 0, B, A); set(B_HIST, 0, B, c.hist_size * A);
@@ -21,7 +21,7 @@ inline void compute_layout(const EnvConfig& c, int* dtype, int* rows, int* cols)
     set(B_EFF_KP, 0, B, NHINGE); set(B_EFF_KD, 0, B, NHINGE); set(B_GRAV_OFF, 0, B, 3); set(B_PUSH_FORCE, 0, B, 3);
     set(B_CUR_PUSH, 0, B, 3); set(B_PUSH_REMAIN, 1, B, 1); set(B_DELAY, 1, B, 1);
     set(B_FOOT_CONTACT, 2, B, 4); set(B_LAST_FOOT_CONTACT, 2, B, 4); set(B_AIR_TIME, 0, B, 4);
-    set(B_EP_SUMS, 0, c.n_rew > 0 ? c.n_rew : 1, B); set(B_ERRNO, 1, B, 1);
+    set(B_EP_SUMS, 0, B, c.n_rew > 0 ? c.n_rew : 1); set(B_ERRNO, 1, B, 1);
     set(B_LINK_POS, 0, B, NLINK * 3); set(B_LINK_VEL, 0, B, NLINK * 3); set(B_CONTACT_FORCE, 0, B, NLINK * 3);
     set(B_TORQUE, 0, B, NHINGE); set(B_STATS, 0, 1, STATS_LEN); set(B_NCONTACT, 1, B, 1); set(B_NNEWTON, 1, B, 1);
 }
@@ -41,8 +41,8 @@ inline void init_arena(const EnvConfig& c, const size_t* offs, char* a) {
     int B = c.num_envs;
     float* q = (float*)(a + offs[B_QPOS]);
     for (int b = 0; b < B; ++b) {
-        for (int j = 0; j < 3; ++j) q[j * B + b] = c.base_init_pos[j];
-        for (int j = 0; j < 4; ++j) q[(3 + j) * B + b] = c.base_init_quat[j];
+        for (int j = 0; j < 3; ++j) q[b * NQ + j] = c.base_init_pos[j];
+        for (int j = 0; j < 4; ++j) q[b * NQ + 3 + j] = c.base_init_quat[j];
     }
     const int ones[3] = {B_KP_FACTORS, B_KD_FACTORS, B_MOTOR_STRENGTH};
     for (int t = 0; t < 3; ++t) {

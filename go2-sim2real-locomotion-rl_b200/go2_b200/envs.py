@@ -200,7 +200,7 @@ class _Go2EnvBase:
         self.inv_base_init_quat = torch.tensor(list(c.inv_base_init_quat), device=self.device)
         self.commands_scale = torch.tensor([c.obs_scale_lin_vel, c.obs_scale_lin_vel, c.obs_scale_ang_vel], device=self.device)
         self.global_gravity = torch.tensor([0.0, 0.0, -1.0], device=self.device).repeat(B, 1)
-        self.episode_sums = {name: b["ep_sums"][k] for k, name in enumerate(self._reward_names)}
+        self.episode_sums = {name: b["ep_sums"][:, k] for k, name in enumerate(self._reward_names)}
         self.extras["time_outs"] = b["timeout"].view(-1)
         self._ecfg = c
 
@@ -637,7 +637,7 @@ class _RobotFacade:
         return torch.arange(e.num_envs, device=e.device) if envs_idx is None else torch.as_tensor(envs_idx, device=e.device).long()
 
     def zero_all_dofs_velocity(self, envs_idx=None):
-        self._env.core.buf["qvel"][:, self._idx(envs_idx)] = 0.0
+        self._env.core.buf["qvel"][self._idx(envs_idx)] = 0.0
 
     def set_dofs_position(self, position, dofs_idx_local=None, zero_velocity=True, envs_idx=None):
         ii = self._idx(envs_idx)
@@ -645,38 +645,38 @@ class _RobotFacade:
         pos = torch.as_tensor(position, device=self._env.device, dtype=torch.float32).reshape(len(ii), len(dofs))
         q = self._env.core.buf["qpos"]
         for k, d in enumerate(dofs):
-            q[d + 1, ii] = pos[:, k]
+            q[ii, d + 1] = pos[:, k]
         if zero_velocity:
             self.zero_all_dofs_velocity(envs_idx)
 
     def set_pos(self, pos, zero_velocity=True, envs_idx=None):
         ii = self._idx(envs_idx)
         p = torch.as_tensor(pos, device=self._env.device, dtype=torch.float32).reshape(len(ii), 3)
-        self._env.core.buf["qpos"][0:3, ii] = p.t()
+        self._env.core.buf["qpos"][ii, 0:3] = p
         if zero_velocity:
             self.zero_all_dofs_velocity(envs_idx)
 
     def set_quat(self, quat, zero_velocity=True, envs_idx=None):
         ii = self._idx(envs_idx)
         q = torch.as_tensor(quat, device=self._env.device, dtype=torch.float32).reshape(len(ii), 4)
-        self._env.core.buf["qpos"][3:7, ii] = q.t()
+        self._env.core.buf["qpos"][ii, 3:7] = q
         if zero_velocity:
             self.zero_all_dofs_velocity(envs_idx)
 
     def get_pos(self):
-        return self._env.core.buf["qpos"][0:3].t().contiguous()
+        return self._env.core.buf["qpos"][:, 0:3].contiguous()
 
     def get_quat(self):
-        q = self._env.core.buf["qpos"][3:7].t()
+        q = self._env.core.buf["qpos"][:, 3:7]
         return q / q.norm(dim=1, keepdim=True)
 
     def get_dofs_position(self, dofs=None):
         q = self._env.core.buf["qpos"]
-        return torch.stack([q[d + 1] for d in (dofs if dofs is not None else range(6, 18))], dim=1)
+        return torch.stack([q[:, d + 1] for d in (dofs if dofs is not None else range(6, 18))], dim=1)
 
     def get_dofs_velocity(self, dofs=None):
         v = self._env.core.buf["qvel"]
-        return torch.stack([v[d] for d in (dofs if dofs is not None else range(18))], dim=1)
+        return torch.stack([v[:, d] for d in (dofs if dofs is not None else range(18))], dim=1)
 
     def get_dofs_control_force(self, dofs=None):
         return self._env.core.buf["torque"]

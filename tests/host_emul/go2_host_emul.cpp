@@ -1,5 +1,5 @@
-// TEST INFRASTRUCTURE ONLY - compiles the kernel source (csrc/go2_env.cuh, the exact per-thread code the
-// CUDA kernel runs) with the host compiler and runs it env-by-env on host memory.  It exists because the
+// TEST INFRASTRUCTURE ONLY - compiles the kernel source (csrc/go2_env.cuh, the exact per-warp code the
+// CUDA kernel runs, lane loops executed serially) with the host compiler and runs it env-by-env on host memory.  It exists because the
 // build container has no GPU: it lets the CPU test-suite exercise the kernel *source* against the oracle.
 // It is never loaded by the go2_b200 package (which hard-fails without the CUDA library); only
 // tests/ loads it, by explicit path.
@@ -62,19 +62,19 @@ int go2_buffer_info(go2_handle* h, int id, void** ptr, int* dtype, int* rows, in
 static int run(go2_handle* h, const float* actions, const StepParams& sp) {
     float* st = (float*)h->bf.p[B_STATS];
     memset(st, 0, sizeof(float) * STATS_LEN);
-    Phys* p = new Phys();
+    WarpS* w = new WarpS();
     for (int b = 0; b < h->cfg.num_envs; ++b) {
-        EnvStepOut out;
-        env_step(h->model, h->cfg, sp, h->bf, actions, b, *p, out);
+        w_env_step(h->model, h->cfg, sp, h->bf, actions, b, *w);
+        const EnvStepOut& out = w->out;
         if (out.reset) {
             st[STATS_RESETS] += 1.0f;
             if (out.timeout) st[STATS_TIMEOUTS] += 1.0f;
             st[STATS_TRACKING] += out.tracking_per_sec;
             for (int k = 0; k < h->cfg.n_rew; ++k) st[STATS_REW0 + k] += out.ep_stat[k];
         }
-        if (p->err) st[STATS_ERR] += 1.0f;
+        if (w->s.err) st[STATS_ERR] += 1.0f;
     }
-    delete p;
+    delete w;
     h->launches += 1;
     return 0;
 }
@@ -119,22 +119,23 @@ int go2_export_links(go2_handle* h, const void* params, int params_bytes, void* 
     if (params_bytes != (int)sizeof(StepParams)) return -2;
     StepParams sp;
     memcpy(&sp, params, sizeof(sp));
-    Phys* p = new Phys();
+    WarpS* w = new WarpS();
     int B = h->bf.B;
     for (int b = 0; b < B; ++b) {
-        for (int i = 0; i < NQ; ++i) p->qpos[i] = ((float*)h->bf.p[B_QPOS])[i * B + b];
-        for (int i = 0; i < NV; ++i) p->qvel[i] = ((float*)h->bf.p[B_QVEL])[i * B + b];
-        kinematics(h->model, sp.mass_shift, sp.com_shift, *p);
-        velocities(h->model, *p);
+        EnvS& es = w->s;
+        for (int i = 0; i < NQ; ++i) es.qpos[i] = ((float*)h->bf.p[B_QPOS])[b * NQ + i];
+        for (int i = 0; i < NV; ++i) es.qvel[i] = ((float*)h->bf.p[B_QVEL])[b * NV + i];
+        w_kinematics(h->model, sp.mass_shift, sp.com_shift, es);
+        w_velocities(h->model, es);
         float* lp = (float*)h->bf.p[B_LINK_POS] + (size_t)b * NLINK * 3;
         float* lv = (float*)h->bf.p[B_LINK_VEL] + (size_t)b * NLINK * 3;
         for (int l = 0; l < NLINK; ++l) {
-            v3 v = link_vel_world(*p, l);
-            lp[l * 3] = p->lpos[l].x; lp[l * 3 + 1] = p->lpos[l].y; lp[l * 3 + 2] = p->lpos[l].z;
+            v3 v = link_vel_world(es, l);
+            lp[l * 3] = es.lpos[l].x; lp[l * 3 + 1] = es.lpos[l].y; lp[l * 3 + 2] = es.lpos[l].z;
             lv[l * 3] = v.x; lv[l * 3 + 1] = v.y; lv[l * 3 + 2] = v.z;
         }
     }
-    delete p;
+    delete w;
     h->launches += 1;
     return 0;
 }

@@ -39,8 +39,8 @@ def test_teacher_forced(name, kind, backend, hostemu_lib):
         assert np.array_equal(np_(extras["time_outs"])[same], g["o_timeout"][t][same])
         assert np.array_equal(np_(env.episode_length_buf)[same], g["o_ep_len"][t][same])
         ok = close(np_(obs), g["o_obs"][t], ATOL, RTOL).all(1) & close(np_(rew), g["o_rew"][t], ATOL, RTOL)
-        ok &= close(np_(env.core.buf["qpos"]).T, g["o_qpos"][t], ATOL, RTOL).all(1)
-        ok &= close(np_(env.core.buf["qvel"]).T, g["o_qvel"][t], 10 * ATOL, RTOL).all(1)
+        ok &= close(np_(env.core.buf["qpos"]), g["o_qpos"][t], ATOL, RTOL).all(1)
+        ok &= close(np_(env.core.buf["qvel"]), g["o_qvel"][t], 10 * ATOL, RTOL).all(1)
         if kind == "walk":
             ok &= close(np_(extras["observations"]["critic"]), g["o_priv"][t], ATOL, RTOL).all(1)
             ok &= (np_(env._foot_contact) == g["o_foot_contact"][t]).all(1)
@@ -61,6 +61,6 @@ def test_free_running_prefix(name, kind, horizon, backend, hostemu_lib):
     for t in range(horizon):
         obs, rew, done, extras = env.step(torch.as_tensor(g["actions"][t], device=env.device))
         assert np.array_equal(np_(done).astype(np.uint8), g["o_reset"][t]), f"reset mismatch at step {t}"
-        assert _frac_ok(np_(env.core.buf["qpos"]).T, g["o_qpos"][t]) == 1.0, f"qpos diverged at step {t}"
+        assert _frac_ok(np_(env.core.buf["qpos"]), g["o_qpos"][t]) == 1.0, f"qpos diverged at step {t}"
         assert _frac_ok(np_(rew), g["o_rew"][t]) == 1.0, f"reward diverged at step {t}"
         assert _frac_ok(np_(obs), g["o_obs"][t]) >= 0.99

@@ -34,20 +34,20 @@ def force_state(env, g, t, kind):
     """Overwrite the env's persistent state with the fixture's pre-step state at step t."""
     b = env.core.buf
     B = env.num_envs
-    b["qpos"].copy_(_t(env, g["qpos"][t].T))
-    b["qvel"].copy_(_t(env, g["qvel"][t].T))
-    b["qacc_ws"].copy_(_t(env, g["qacc_ws"][t].T))
-    b["warm"].copy_(_t(env, g["warm"][t][None], torch.int32))
+    b["qpos"].copy_(_t(env, g["qpos"][t]))
+    b["qvel"].copy_(_t(env, g["qvel"][t]))
+    b["qacc_ws"].copy_(_t(env, g["qacc_ws"][t]))
+    b["warm"].copy_(_t(env, g["warm"][t][:, None], torch.int32))
     cache = g["cache"][t]  # [B, npairs, 3]
-    ncache = np.zeros((1, B), dtype=np.int32)
+    ncache = np.zeros((B, 1), dtype=np.int32)
     cpair = np.zeros(tuple(b["cache_pair"].shape), dtype=np.int32)
     cn = np.zeros(tuple(b["cache_n"].shape), dtype=np.float32)
     for e in range(B):
         nz = np.nonzero(np.abs(cache[e]).sum(1) > 0)[0]
-        ncache[0, e] = len(nz)
+        ncache[e, 0] = len(nz)
         for k, p in enumerate(nz):
-            cpair[k, e] = p
-            cn[3 * k:3 * k + 3, e] = cache[e, p]
+            cpair[e, k] = p
+            cn[e, 3 * k:3 * k + 3] = cache[e, p]
     b["ncache"].copy_(_t(env, ncache, torch.int32))
     b["cache_pair"].copy_(_t(env, cpair, torch.int32))
     b["cache_n"].copy_(_t(env, cn))
@@ -57,7 +57,7 @@ def force_state(env, g, t, kind):
         b[name].copy_(_t(env, g[key][t]))
     b["ep_len"].copy_(_t(env, g["ep_len"][t][:, None], torch.int32))
     if g["ep_sums"].shape[1] > 0:
-        b["ep_sums"].copy_(_t(env, g["ep_sums"][t]))
+        b["ep_sums"].copy_(_t(env, g["ep_sums"][t].T))
     if kind == "walk":
         b["hist"].copy_(_t(env, g["hist"][t].reshape(B, -1)))
         env._action_history_write_idx = int(g["hist_idx"][t])
