@@ -9,6 +9,7 @@
 #pragma once
 #include "go2_buffers.cuh"
 #include "go2_warp.cuh"
+#include "go2_solve.cuh"
 
 namespace go2 {
 
@@ -45,6 +46,8 @@ G2_HD v3 quat_to_rpy_deg(q4 q) {
     const float k = 57.29577951308232f;
     return mk3(r * k, pch * k, y * k);
 }
+
+G2_HD float w_applied_force(const Go2Model& m, const Phys& p, int d) { return applied_force(m, p, d); }
 
 template <class P>
 G2_HD v3 link_vel_world(const P& p, int l) { return p.cd_v[l] + cross(p.cd_a[l], p.lpos[l] - p.root_com); }
@@ -623,6 +626,57 @@ G2_HD void w_env_step(const Go2Model& m, const EnvConfig& cfg, const StepParams&
         }
     }
     WSYNC();
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Layout v3: one THREAD per env.  The whole control tick of env b runs in this thread; `p` is the thread's
+// private working set (registers + thread-local memory).  Persistent physics state is env-major in HBM.
+// ---------------------------------------------------------------------------------------------------
+G2_HD void load_phys(const Buffers& bf, int b, Phys& p) {
+    for (int i = 0; i < NQ; ++i) p.qpos[i] = F32(B_QPOS)[b * NQ + i];
+    for (int i = 0; i < NV; ++i) p.qvel[i] = F32(B_QVEL)[b * NV + i];
+    for (int i = 0; i < NV; ++i) p.qacc_ws[i] = F32(B_QACC_WS)[b * NV + i];
+    p.warm = I32(B_WARM)[b];
+    int nc = I32(B_NCACHE)[b];
+    p.n_cache = nc;
+    for (int k = 0; k < nc; ++k) {
+        p.cache_pair[k] = I32(B_CACHE_PAIR)[b * MAX_CPAIRS + k];
+        const float* cn = F32(B_CACHE_N) + (size_t)b * MAX_CPAIRS * 3 + 3 * k;
+        p.cache_n[k] = mk3(cn[0], cn[1], cn[2]);
+    }
+    p.err = 0;
+    p.cost = 0.0f;
+    p.prev_cost = 0.0f;
+    p.pd_mode = 0; p.pd_kp = 0.0f; p.pd_kv = 0.0f;
+    for (int l = 0; l < NLINK; ++l) p.cforce[l] = mk3(0, 0, 0);
+    p.n_contacts = 0;
+    p.n_rows = 0;
+    p.n_newton = 0;
+}
+G2_HD void store_phys(const Buffers& bf, int b, const Phys& p) {
+    for (int i = 0; i < NQ; ++i) F32(B_QPOS)[b * NQ + i] = p.qpos[i];
+    for (int i = 0; i < NV; ++i) F32(B_QVEL)[b * NV + i] = p.qvel[i];
+    for (int i = 0; i < NV; ++i) F32(B_QACC_WS)[b * NV + i] = p.qacc_ws[i];
+    I32(B_WARM)[b] = p.warm;
+    I32(B_NCACHE)[b] = p.n_cache;
+    for (int k = 0; k < p.n_cache; ++k) {
+        I32(B_CACHE_PAIR)[b * MAX_CPAIRS + k] = p.cache_pair[k];
+        float* cn = F32(B_CACHE_N) + (size_t)b * MAX_CPAIRS * 3 + 3 * k;
+        cn[0] = p.cache_n[k].x; cn[1] = p.cache_n[k].y; cn[2] = p.cache_n[k].z;
+    }
+}
+
+G2_HD void t_env_step(const Go2Model& m, const EnvConfig& cfg, const StepParams& sp, const Buffers& bf, const float* actions, int b,
+                      Phys& p, EnvLocal& e, EnvStepOut& out) {
+    load_phys(bf, b, p);
+    kinematics(m, sp.mass_shift, sp.com_shift, p);
+    velocities(m, p);
+    env_pre(m, cfg, sp, bf, actions, b, p, e, out);
+    if (sp.do_physics) {
+        for (int s = 0; s < 2; ++s) substep(m, p, sp.friction, sp.mass_shift, sp.com_shift);
+    }
+    env_post(m, cfg, sp, bf, b, p, e, out);
+    store_phys(bf, b, p);
 }
 
 #undef F32

@@ -1,11 +1,15 @@
 // go2_b200 - CUDA kernels + C ABI (include/go2_b200.h) of the fused Go2 env step, sm_100a.
 //
-// Layout v2: one WARP per environment (csrc/go2_warp.cuh).  A warp loads its env's persistent state (env-major
-// rows -> coalesced lane accesses), runs the whole control tick (torque law, 2 rigid substeps incl. collision +
-// Newton solve, rewards, reset, observations) out of shared memory, and writes the state back once.
-// No global-memory round trips between phases, one launch per tick.
+// Layout v3 (default): one THREAD per environment (go2_env.cuh: t_env_step).  A thread loads its env's persistent
+// state, runs the whole control tick (torque law, 2 rigid substeps incl. collision + Newton solve, rewards,
+// reset, observations) in registers / thread-local memory and writes the state back once: one launch per tick,
+// no global-memory round trips between phases.
+// Layout v2 (GO2_B200_LAYOUT=warp, kept for ablation; measured 5x slower): one WARP per env with
+// the working set in shared memory (go2_warp.cuh).
 #include <cuda_runtime.h>
 #include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
 #include <string>
 #include "../../include/go2_b200.h"
 #include "go2_env.cuh"
@@ -25,6 +29,7 @@ struct go2_handle {
     size_t arena_bytes;
     float* h_stats;  // pinned
     long long launches;
+    int layout;  // 0 = thread per env (default), 1 = warp per env
     std::string err;
 };
 
@@ -32,8 +37,35 @@ struct go2_handle {
 #define GO2_WARPS 4  // envs (warps) per block
 #endif
 
+#ifndef GO2_TPB
+#define GO2_TPB 64  // envs (threads) per block, thread-per-env layout
+#endif
+
+__device__ __forceinline__ void accumulate_stats(const EnvConfig* gcfg, const Buffers& bf, const EnvStepOut& out, int err) {
+    float* st = (float*)bf.p[B_STATS];
+    if (out.reset) {
+        atomicAdd(&st[STATS_RESETS], 1.0f);
+        if (out.timeout) atomicAdd(&st[STATS_TIMEOUTS], 1.0f);
+        atomicAdd(&st[STATS_TRACKING], out.tracking_per_sec);
+        for (int k = 0; k < gcfg->n_rew; ++k) atomicAdd(&st[STATS_REW0 + k], out.ep_stat[k]);
+    }
+    if (err) atomicAdd(&st[STATS_ERR], 1.0f);  // number of envs that raised an errno bit this tick
+}
+
+// one thread per env
+__global__ void __launch_bounds__(GO2_TPB) go2_step_kernel(const Go2Model* __restrict__ gm, const EnvConfig* __restrict__ gcfg,
+                                                           StepParams sp, Buffers bf, const float* __restrict__ actions) {
+    int b = blockIdx.x * GO2_TPB + threadIdx.x;
+    if (b >= bf.B) return;
+    Phys p;
+    EnvLocal e;
+    EnvStepOut out;
+    t_env_step(*gm, *gcfg, sp, bf, actions, b, p, e, out);
+    accumulate_stats(gcfg, bf, out, p.err);
+}
+
 // one warp per env; the per-env working set (WarpS) lives in dynamic shared memory
-__global__ void __launch_bounds__(GO2_WARPS * 32) go2_step_kernel(const Go2Model* __restrict__ gm, const EnvConfig* __restrict__ gcfg,
+__global__ void __launch_bounds__(GO2_WARPS * 32) go2_step_warp_kernel(const Go2Model* __restrict__ gm, const EnvConfig* __restrict__ gcfg,
                                                                   StepParams sp, Buffers bf, const float* __restrict__ actions) {
     extern __shared__ __align__(16) unsigned char g2_smem[];
     int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -41,17 +73,7 @@ __global__ void __launch_bounds__(GO2_WARPS * 32) go2_step_kernel(const Go2Model
     if (b >= bf.B) return;
     WarpS& w = reinterpret_cast<WarpS*>(g2_smem)[warp];
     w_env_step(*gm, *gcfg, sp, bf, actions, b, w);
-    if (lane == 0) {
-        const EnvStepOut& out = w.out;
-        float* st = (float*)bf.p[B_STATS];
-        if (out.reset) {
-            atomicAdd(&st[STATS_RESETS], 1.0f);
-            if (out.timeout) atomicAdd(&st[STATS_TIMEOUTS], 1.0f);
-            atomicAdd(&st[STATS_TRACKING], out.tracking_per_sec);
-            for (int k = 0; k < gcfg->n_rew; ++k) atomicAdd(&st[STATS_REW0 + k], out.ep_stat[k]);
-        }
-        if (w.s.err) atomicAdd(&st[STATS_ERR], 1.0f);  // number of envs that raised an errno bit this tick
-    }
+    if (lane == 0) accumulate_stats(gcfg, bf, w.out, w.s.err);
 }
 
 __global__ void __launch_bounds__(GO2_WARPS * 32) go2_links_kernel(const Go2Model* __restrict__ gm, StepParams sp, Buffers bf) {
@@ -96,6 +118,8 @@ int go2_create(const int32_t* model_iv, int n_iv, const double* model_fv, int n_
     go2_handle* h = new go2_handle();
     h->device = device;
     h->launches = 0;
+    const char* lay = getenv("GO2_B200_LAYOUT");
+    h->layout = (lay && !strcmp(lay, "warp")) ? 1 : 0;
     memcpy(&h->cfg, cfg, sizeof(EnvConfig));
     const EnvConfig& c = h->cfg;
     Go2Model m;
@@ -113,7 +137,8 @@ int go2_create(const int32_t* model_iv, int n_iv, const double* model_fv, int n_
     cudaMemcpy(h->d_model, &m, sizeof(Go2Model), cudaMemcpyHostToDevice);
     cudaMemcpy(h->d_cfg, &h->cfg, sizeof(EnvConfig), cudaMemcpyHostToDevice);
     cudaMallocHost(&h->h_stats, sizeof(float) * STATS_LEN);
-    cudaFuncSetAttribute(go2_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(GO2_WARPS * sizeof(WarpS)));
+    cudaFuncSetAttribute(go2_step_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(GO2_WARPS * sizeof(WarpS)));
+    cudaFuncSetAttribute(go2_step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 0);  // all of L1 for thread-local data
     cudaFuncSetAttribute(go2_links_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(GO2_WARPS * sizeof(WarpS)));
     std::string init(h->arena_bytes, 0);
     init_arena(c, offs, &init[0]);
@@ -151,7 +176,10 @@ static int launch_step(go2_handle* h, const float* d_actions, const void* params
     memcpy(&sp, params, sizeof(sp));
     int B = h->cfg.num_envs;
     if (!ck(h, cudaMemsetAsync(h->bf.p[B_STATS], 0, sizeof(float) * STATS_LEN, s), "memset stats")) return -1;
-    go2_step_kernel<<<(B + GO2_WARPS - 1) / GO2_WARPS, GO2_WARPS * 32, GO2_WARPS * sizeof(WarpS), s>>>(h->d_model, h->d_cfg, sp, h->bf, d_actions);
+    if (h->layout == 1)
+        go2_step_warp_kernel<<<(B + GO2_WARPS - 1) / GO2_WARPS, GO2_WARPS * 32, GO2_WARPS * sizeof(WarpS), s>>>(h->d_model, h->d_cfg, sp, h->bf, d_actions);
+    else
+        go2_step_kernel<<<(B + GO2_TPB - 1) / GO2_TPB, GO2_TPB, 0, s>>>(h->d_model, h->d_cfg, sp, h->bf, d_actions);
     h->launches += 1;
     return ck(h, cudaGetLastError(), "go2_step_kernel") ? 0 : -1;
 }

@@ -54,11 +54,9 @@ struct Phys {
     Contact con[MAX_CONTACTS];
     float J[MAX_ROWS][NV];
     float Dd[MAX_ROWS], aref[MAX_ROWS], Jaref[MAX_ROWS], jv[MAX_ROWS], efc[MAX_ROWS];
-    uint8_t act[MAX_ROWS], pact[MAX_ROWS];
-    float H[NTRI];
-    float qacc[NV], Ma[NV], grad[NV], Mgrad[NV], search[NV], mv[NV], qfc[NV];
-    float cost, prev_cost, gauss, qg0, qg1, qg2;
-    int ls_it;
+    uint8_t act[MAX_ROWS];
+    float H[NTRI];  // Cholesky factor of the Newton Hessian
+    float cost, prev_cost, gauss;
     v3 cforce[NLINK];  // net contact force per link
     int err;
     int n_newton;

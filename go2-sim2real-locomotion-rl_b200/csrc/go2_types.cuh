@@ -23,7 +23,7 @@ constexpr int NHINGE = 12;
 constexpr int NGEOM = 28;   // geom 0 = ground box, 1..27 robot
 constexpr int MAX_PAIRS_STATIC = 352;
 constexpr int MAX_CPAIRS = 24;   // colliding geom pairs kept per env (contact-normal cache entries)
-constexpr int MAX_CONTACTS = 48; // contacts per env (reference cap: 150; overflow -> errno bit)
+constexpr int MAX_CONTACTS = 16; // contacts per env kept for the solve (reference cap: 150; overflow -> errno bit)
 constexpr int MAX_ROWS = 4 * MAX_CONTACTS + NHINGE;
 constexpr int NTRI = NV * (NV + 1) / 2;  // packed lower triangle
 constexpr int MAX_REW = 32;      // reward terms

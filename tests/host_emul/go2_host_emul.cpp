@@ -63,8 +63,12 @@ static int run(go2_handle* h, const float* actions, const StepParams& sp) {
     float* st = (float*)h->bf.p[B_STATS];
     memset(st, 0, sizeof(float) * STATS_LEN);
     WarpS* w = new WarpS();
+    Phys* p = new Phys();
+    const char* lay = getenv("GO2_B200_LAYOUT");
+    bool warp = lay && !strcmp(lay, "warp");
     for (int b = 0; b < h->cfg.num_envs; ++b) {
-        w_env_step(h->model, h->cfg, sp, h->bf, actions, b, *w);
+        if (warp) w_env_step(h->model, h->cfg, sp, h->bf, actions, b, *w);
+        else { t_env_step(h->model, h->cfg, sp, h->bf, actions, b, *p, w->e, w->out); w->s.err = p->err; }
         const EnvStepOut& out = w->out;
         if (out.reset) {
             st[STATS_RESETS] += 1.0f;
@@ -75,6 +79,7 @@ static int run(go2_handle* h, const float* actions, const StepParams& sp) {
         if (w->s.err) st[STATS_ERR] += 1.0f;
     }
     delete w;
+    delete p;
     h->launches += 1;
     return 0;
 }
