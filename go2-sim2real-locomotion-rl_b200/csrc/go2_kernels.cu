@@ -30,6 +30,7 @@ struct go2_handle {
     float* h_stats;  // pinned
     long long launches;
     int layout;  // 0 = thread per env (default), 1 = warp per env
+    int tpb, nblocks;  // launch shape of the thread-per-env kernel
     std::string err;
 };
 
@@ -38,7 +39,7 @@ struct go2_handle {
 #endif
 
 #ifndef GO2_TPB
-#define GO2_TPB 64  // envs (threads) per block, thread-per-env layout
+#define GO2_TPB 512  // max envs (threads) per block, thread-per-env layout; the launch picks blockDim <= GO2_TPB
 #endif
 
 __device__ __forceinline__ void accumulate_stats(const EnvConfig* gcfg, const Buffers& bf, const EnvStepOut& out, int err) {
@@ -55,13 +56,13 @@ __device__ __forceinline__ void accumulate_stats(const EnvConfig* gcfg, const Bu
 // one thread per env
 __global__ void __launch_bounds__(GO2_TPB) go2_step_kernel(const Go2Model* __restrict__ gm, const EnvConfig* __restrict__ gcfg,
                                                            StepParams sp, Buffers bf, const float* __restrict__ actions) {
-    int b = blockIdx.x * GO2_TPB + threadIdx.x;
-    if (b >= bf.B) return;
+    int b = blockIdx.x * blockDim.x + threadIdx.x;
+    bool valid = b < bf.B;
     Phys p;
     EnvLocal e;
     EnvStepOut out;
-    t_env_step(*gm, *gcfg, sp, bf, actions, b, p, e, out);
-    accumulate_stats(gcfg, bf, out, p.err);
+    t_env_step(*gm, *gcfg, sp, bf, actions, b, valid, p, e, out);
+    if (valid) accumulate_stats(gcfg, bf, out, p.err);
 }
 
 // one warp per env; the per-env working set (WarpS) lives in dynamic shared memory
@@ -121,6 +122,22 @@ int go2_create(const int32_t* model_iv, int n_iv, const double* model_fv, int n_
     const char* lay = getenv("GO2_B200_LAYOUT");
     h->layout = (lay && !strcmp(lay, "warp")) ? 1 : 0;
     memcpy(&h->cfg, cfg, sizeof(EnvConfig));
+    {
+        // One block per SM per wave, as large as allowed: the warps of a block run phase-locked (barriers in
+        // t_env_step / solve_constraints) and share instruction fetches, so big blocks win; the block size is
+        // the smallest multiple of 32 that covers the envs with k * n_SM blocks.
+        int n_sm = 148;
+        cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, device);
+        int B = h->cfg.num_envs, tpb = GO2_TPB;
+        for (int k = 1; k <= 64; ++k) {
+            int t = ((B + n_sm * k - 1) / (n_sm * k) + 31) / 32 * 32;
+            if (t <= GO2_TPB) { tpb = t; break; }
+        }
+        const char* tp = getenv("GO2_B200_TPB");
+        if (tp && atoi(tp) >= 32 && atoi(tp) <= GO2_TPB) tpb = atoi(tp) / 32 * 32;
+        h->tpb = tpb;
+        h->nblocks = (B + tpb - 1) / tpb;
+    }
     const EnvConfig& c = h->cfg;
     Go2Model m;
     if (!unpack_model(m, model_iv, n_iv, model_fv, n_fv)) { delete h; return -3; }
@@ -179,7 +196,7 @@ static int launch_step(go2_handle* h, const float* d_actions, const void* params
     if (h->layout == 1)
         go2_step_warp_kernel<<<(B + GO2_WARPS - 1) / GO2_WARPS, GO2_WARPS * 32, GO2_WARPS * sizeof(WarpS), s>>>(h->d_model, h->d_cfg, sp, h->bf, d_actions);
     else
-        go2_step_kernel<<<(B + GO2_TPB - 1) / GO2_TPB, GO2_TPB, 0, s>>>(h->d_model, h->d_cfg, sp, h->bf, d_actions);
+        go2_step_kernel<<<h->nblocks, h->tpb, 0, s>>>(h->d_model, h->d_cfg, sp, h->bf, d_actions);
     h->launches += 1;
     return ck(h, cudaGetLastError(), "go2_step_kernel") ? 0 : -1;
 }

@@ -38,25 +38,39 @@ struct Phys {
     v3 lpos[NLINK];
     q4 lquat[NLINK];
     v3 root_com;
-    float cin_I[NLINK][6];  // symmetric inertia about root COM: xx,xy,xz,yy,yz,zz
-    v3 cin_h[NLINK];        // mass * (link COM - root COM)
-    float cin_m[NLINK];
     v3 cdof_a[NV], cdof_v[NV];
-    v3 cdofd_a[NV], cdofd_v[NV];
     v3 cd_a[NLINK], cd_v[NLINK];
     // dynamics
-    float M[NTRI], L[NTRI], Dinv[NV];
-    float force[NV], qf_smooth[NV], acc_smooth[NV], acc[NV];
-    // geoms
-    v3 g_c[NGEOM], g_h[NGEOM];  // world AABB centre / half extents
-    // contacts + constraints
+    float M[NTRI];
+    float force[NV], acc_smooth[NV], acc[NV];
+    // contacts
     int n_contacts, n_rows;
     Contact con[MAX_CONTACTS];
-    float J[MAX_ROWS][NV];
-    float Dd[MAX_ROWS], aref[MAX_ROWS], Jaref[MAX_ROWS], jv[MAX_ROWS], efc[MAX_ROWS];
-    uint8_t act[MAX_ROWS];
-    float H[NTRI];  // Cholesky factor of the Newton Hessian
     float cost, prev_cost, gauss;
+    // Phase-private scratch sharing one address range (thread-local memory is cached per touched word, so
+    // overlapping the phases keeps the per-thread cache footprint at max(phase) instead of sum(phase)):
+    //   kin -> smooth : inertias about the root COM, cdof time derivatives (written by kinematics()/velocities()
+    //                   at the end of a substep, read by the next smooth_dynamics()), LtDL factor of M
+    //   collide       : geom AABBs
+    //   solve         : Cholesky factor of the Newton Hessian, constraint rows, Jacobian
+    union {
+        struct {
+            float cin_I[NLINK][6];  // symmetric inertia about root COM: xx,xy,xz,yy,yz,zz
+            v3 cin_h[NLINK];        // mass * (link COM - root COM)
+            float cin_m[NLINK];
+            v3 cdofd_a[NV], cdofd_v[NV];
+            float L[NTRI], Dinv[NV];
+        };
+        struct {
+            v3 g_c[NGEOM], g_h[NGEOM];  // world AABB centre / half extents
+        };
+        struct {
+            float H[NTRI];
+            uint8_t act[MAX_ROWS];
+            float Dd[MAX_ROWS], aref[MAX_ROWS], Jaref[MAX_ROWS], jv[MAX_ROWS], efc[MAX_ROWS];
+            float J[MAX_ROWS][NV];
+        };
+    };
     v3 cforce[NLINK];  // net contact force per link
     int err;
     int n_newton;
@@ -294,7 +308,6 @@ G2_HDN void smooth_dynamics(const Go2Model& m, Phys& p) {
         float bias = dot(p.cdof_a[d], fa[l]) + dot(p.cdof_v[d], fv[l]);
         float ap = d < 6 ? 0.0f : applied_force(m, p, d);
         p.force[d] = ap - bias;
-        p.qf_smooth[d] = p.force[d];
     }
     solve_mass(p, p.force, p.acc_smooth);
     for (int d = 0; d < NV; ++d) p.acc[d] = p.acc_smooth[d];

@@ -20,10 +20,17 @@
 
 namespace go2 {
 
-#if defined(__CUDACC__)
+#if defined(__CUDACC__) && defined(G2_ROLLED)
+#define G2_UNROLL _Pragma("unroll 1")
+#elif defined(__CUDACC__)
 #define G2_UNROLL _Pragma("unroll")
 #else
 #define G2_UNROLL
+#endif
+#if defined(__CUDACC__) && defined(G2_ROLLED) && !defined(G2_ROLLED_ALL)
+#define G2_UNROLL_H _Pragma("unroll")
+#else
+#define G2_UNROLL_H G2_UNROLL
 #endif
 
 // M[i][j] is structurally nonzero iff one of the dofs is a base dof or both hinges belong to the same leg
@@ -151,7 +158,7 @@ G2_HD void update_constraint(Phys& p, const float* qacc, const float* Ma, float*
 // L written to p.H once.
 G2_HDN void hessian_factor(Phys& p) {
     float H[NTRI];
-    G2_UNROLL
+    G2_UNROLL_H
     for (int k = 0; k < NTRI; ++k) H[k] = p.M[k];
     int n = p.n_rows;
     for (int c = 0; c < n; ++c) {
@@ -159,32 +166,32 @@ G2_HDN void hessian_factor(Phys& p) {
         const float* Jr = p.J[c];
         float D = p.Dd[c];
         float jr[NV];
-        G2_UNROLL
+        G2_UNROLL_H
         for (int i = 0; i < NV; ++i) jr[i] = Jr[i];
-        G2_UNROLL
+        G2_UNROLL_H
         for (int i = 0; i < NV; ++i) {
             float s = jr[i] * D;
-            G2_UNROLL
+            G2_UNROLL_H
             for (int j = 0; j <= i; ++j) H[tri(i, j)] += jr[j] * s;
         }
     }
-    G2_UNROLL
+    G2_UNROLL_H
     for (int i = 0; i < NV; ++i) {
         float t = H[tri(i, i)];
-        G2_UNROLL
+        G2_UNROLL_H
         for (int j = 0; j < i; ++j) t -= H[tri(i, j)] * H[tri(i, j)];
         float lii = sqrtf(fmaxf(t, EPSF));
         H[tri(i, i)] = lii;
         float inv = 1.0f / lii;
-        G2_UNROLL
+        G2_UNROLL_H
         for (int j = i + 1; j < NV; ++j) {
             float dt = 0.0f;
-            G2_UNROLL
+            G2_UNROLL_H
             for (int k = 0; k < i; ++k) dt += H[tri(j, k)] * H[tri(i, k)];
             H[tri(j, i)] = (H[tri(j, i)] - dt) * inv;
         }
     }
-    G2_UNROLL
+    G2_UNROLL_H
     for (int k = 0; k < NTRI; ++k) p.H[k] = H[k];
 }
 
@@ -238,6 +245,14 @@ G2_HD void update_gradient(Phys& p, const float* Ma, const float* qfc, float* gr
     }
 }
 
+#if defined(GO2_LS_STATS) && !defined(__CUDA_ARCH__)
+// host-only debugging counters of the line search (tests/host_emul with -DGO2_LS_STATS)
+static long g_ls_calls = 0, g_lsA[64] = {0}, g_lsB[64] = {0}, g_lsend[4] = {0};
+#define G2_LS_COUNT(nA, nB, k) (g_ls_calls++, g_lsA[nA]++, g_lsB[nB]++, g_lsend[k]++)
+#else
+#define G2_LS_COUNT(nA, nB, k)
+#endif
+constexpr int LS_REG = 16;  // rows of the line search kept in registers (4 contacts)
 struct LsPt {
     float alpha, cost, d0, d1;
 };
@@ -273,7 +288,23 @@ G2_HD float linesearch(const Go2Model& m, Phys& p, const float* search, const fl
     if (sn < EPSF) return 0.0f;
     mul_M(p.M, search, mv);
     int n = p.n_rows;
-    for (int c = 0; c < n; ++c) {
+    // the first LS_REG rows are cached in registers for the evaluations (rows >= n contribute exact zeros);
+    // any further rows (more than 4 contacts) are streamed from thread-local memory
+    float rja[LS_REG], rjv[LS_REG], rD[LS_REG];
+    G2_UNROLL
+    for (int c = 0; c < LS_REG; ++c) {
+        float s = 0.0f, ja = 0.0f, D = 0.0f;
+        if (c < n) {
+            const float* Jr = p.J[c];
+            G2_UNROLL
+            for (int d = 0; d < NV; ++d) s += Jr[d] * search[d];
+            p.jv[c] = s;
+            ja = p.Jaref[c];
+            D = p.Dd[c];
+        }
+        rja[c] = ja; rjv[c] = s; rD[c] = D;
+    }
+    for (int c = LS_REG; c < n; ++c) {
         const float* Jr = p.J[c];
         float s = 0.0f;
         G2_UNROLL
@@ -297,7 +328,16 @@ G2_HD float linesearch(const Go2Model& m, Phys& p, const float* search, const fl
     int stage = 0;
     for (;;) {
         float q0 = g0, q1 = g1, q2 = g2;
-        for (int c = 0; c < n; ++c) {
+        G2_UNROLL
+        for (int c = 0; c < LS_REG; ++c) {
+            float ja = rja[c], jv = rjv[c], D = rD[c];
+            if (ja + alpha * jv < 0.0f) {
+                q0 += D * (0.5f * ja * ja);
+                q1 += D * (jv * ja);
+                q2 += D * (0.5f * jv * jv);
+            }
+        }
+        for (int c = LS_REG; c < n; ++c) {
             float ja = p.Jaref[c], jv = p.jv[c], D = p.Dd[c];
             if (ja + alpha * jv < 0.0f) {
                 q0 += D * (0.5f * ja * ja);
@@ -348,11 +388,23 @@ G2_HD float linesearch(const Go2Model& m, Phys& p, const float* search, const fl
     }
     // ---- loop B: three-point refinement of the bracket [p1, p2]
     float a[3] = {p1.alpha - p1.d0 / p1.d1, p1.alpha, (p1.alpha + p2.alpha) * 0.5f};
+    int nA = ls_it, nB = 0, endk = finished ? 0 : 3;
+    (void)nA; (void)nB; (void)endk;
     while (!finished && ls_it < LS_ITERS) {
+        nB++;
         float t[3][3];
         G2_UNROLL
         for (int k = 0; k < 3; ++k) { t[k][0] = g0; t[k][1] = g1; t[k][2] = g2; }
-        for (int c = 0; c < n; ++c) {
+        G2_UNROLL
+        for (int c = 0; c < LS_REG; ++c) {
+            float ja = rja[c], jv = rjv[c], D = rD[c];
+            float f0 = D * (0.5f * ja * ja), f1 = D * (jv * ja), f2 = D * (0.5f * jv * jv);
+            G2_UNROLL
+            for (int k = 0; k < 3; ++k) {
+                if (ja + a[k] * jv < 0.0f) { t[k][0] += f0; t[k][1] += f1; t[k][2] += f2; }
+            }
+        }
+        for (int c = LS_REG; c < n; ++c) {
             float ja = p.Jaref[c], jv = p.jv[c], D = p.Dd[c];
             float f0 = D * (0.5f * ja * ja), f1 = D * (jv * ja), f2 = D * (0.5f * jv * jv);
             G2_UNROLL
@@ -373,6 +425,7 @@ G2_HD float linesearch(const Go2Model& m, Phys& p, const float* search, const fl
         if (found) {
             result = ba;
             finished = true;
+            endk = 1;
         } else {
             float n1, n2;
             int b1 = bracket_update(p1, cand, n1);
@@ -380,11 +433,13 @@ G2_HD float linesearch(const Go2Model& m, Phys& p, const float* search, const fl
             if (b1 == 0 && b2 == 0) {
                 result = a[2];
                 finished = true;
+                endk = 2;
             } else {
                 a[0] = n1; a[1] = n2; a[2] = (p1.alpha + p2.alpha) * 0.5f;
             }
         }
     }
+    G2_LS_COUNT(nA, nB, endk);
     if (!finished) {
         if (p1.cost <= p2.cost && p1.cost < p0.cost) result = p1.alpha;
         else if (p2.cost <= p1.cost && p2.cost < p0.cost) result = p2.alpha;
@@ -395,62 +450,83 @@ G2_HD float linesearch(const Go2Model& m, Phys& p, const float* search, const fl
 
 constexpr int MAX_RANK1 = 6;  // more flips than this in one Newton iteration -> assemble + factor from scratch
 
+// Block-wide "does any thread still iterate": keeps the warps of a block in the same Newton iteration so that
+// they share instruction fetches (the solver body is ~60 KB of straight-line code).  Host: a single env.
+#ifdef __CUDA_ARCH__
+#define G2_BLOCK_ANY(x) (__syncthreads_or((x) ? 1 : 0) != 0)
+#else
+#define G2_BLOCK_ANY(x) (x)
+#endif
+
 // Newton solve for the constrained acceleration; writes p.acc, warm start, per-link contact forces.
-G2_HDN void solve_constraints(const Go2Model& m, Phys& p) {
-    const int n = p.n_rows;
+// Called by EVERY thread of the block (`valid` = the thread owns an env) because the iteration loop contains
+// block barriers.  Trip 0 of the loop is the initial evaluation (active set, Hessian factorisation, gradient);
+// trips >= 1 are the Newton iterations of constraint/solver.py:2862-2938, each helper having ONE call site.
+G2_HDN void solve_constraints(const Go2Model& m, Phys& p, bool valid) {
+    const int n = valid ? p.n_rows : 0;
     float qacc[NV], Ma[NV], qfc[NV], grad[NV], Mgrad[NV], search[NV], mv[NV];
-    bool ws = n > 0 && p.warm;
-    G2_UNROLL
-    for (int d = 0; d < NV; ++d) qacc[d] = ws ? p.qacc_ws[d] : p.acc_smooth[d];
-    mul_M(p.M, qacc, Ma);
-    for (int c = 0; c < n; ++c) {
-        const float* Jr = p.J[c];
-        float s = -p.aref[c];
+    if (valid) {
+        bool ws = n > 0 && p.warm;
         G2_UNROLL
-        for (int d = 0; d < NV; ++d) s += Jr[d] * qacc[d];
-        p.Jaref[c] = s;
-        p.act[c] = 0;
+        for (int d = 0; d < NV; ++d) qacc[d] = ws ? p.qacc_ws[d] : p.acc_smooth[d];
+        if (n > 0) mul_M(p.M, qacc, Ma);
+        for (int c = 0; c < n; ++c) {
+            const float* Jr = p.J[c];
+            float s = -p.aref[c];
+            G2_UNROLL
+            for (int d = 0; d < NV; ++d) s += Jr[d] * qacc[d];
+            p.Jaref[c] = s;
+            p.act[c] = 0;
+        }
+        p.cost = 0.0f;
     }
-    unsigned long long flist;
-    int nfl;
-    p.cost = 0.0f;
-    update_constraint(p, qacc, Ma, qfc, flist, nfl);
     int n_newton = 0;
-    if (n > 0) {
-        hessian_factor(p);
-        update_gradient(p, Ma, qfc, grad, Mgrad);
-        G2_UNROLL
-        for (int d = 0; d < NV; ++d) search[d] = -Mgrad[d];
-        const float tol = m.meaninertia * (float)NV * SOLVER_TOL;
-        for (int it = 0; it < SOLVER_ITERS; ++it) {
-            n_newton++;
-            float alpha = linesearch(m, p, search, Ma, mv);
-            if (fabsf(alpha) < EPSF) break;
-            G2_UNROLL
-            for (int d = 0; d < NV; ++d) {
-                qacc[d] += search[d] * alpha;
-                Ma[d] += mv[d] * alpha;
+    bool active = n > 0;
+    const float tol = m.meaninertia * (float)NV * SOLVER_TOL;
+    for (int it = 0; it <= SOLVER_ITERS; ++it) {
+        if (!G2_BLOCK_ANY(active)) break;
+        if (active) {
+            bool first = it == 0;
+            if (!first) {
+                n_newton++;
+                float alpha = linesearch(m, p, search, Ma, mv);
+                if (fabsf(alpha) < EPSF) {
+                    active = false;
+                } else {
+                    G2_UNROLL
+                    for (int d = 0; d < NV; ++d) {
+                        qacc[d] += search[d] * alpha;
+                        Ma[d] += mv[d] * alpha;
+                    }
+                    for (int c = 0; c < n; ++c) p.Jaref[c] += p.jv[c] * alpha;
+                }
             }
-            for (int c = 0; c < n; ++c) p.Jaref[c] += p.jv[c] * alpha;
-            update_constraint(p, qacc, Ma, qfc, flist, nfl);
-            // active-set changes: k-th flip of every lane together, oldest first (row order, like the reference)
-            bool refactor = nfl > MAX_RANK1;
-            for (int k = nfl - 1; k >= 0 && !refactor; --k) {
-                int c = (int)((flist >> (8 * k)) & 0xffull);
-                if (!hessian_rank1(p, c, p.act[c] ? 1.0f : -1.0f)) refactor = true;
+            if (active) {
+                unsigned long long flist;
+                int nfl;
+                update_constraint(p, qacc, Ma, qfc, flist, nfl);
+                // active-set changes: k-th flip of every lane together, oldest first (row order, like the reference)
+                bool refactor = first || nfl > MAX_RANK1;
+                for (int k = nfl - 1; k >= 0 && !refactor; --k) {
+                    int c = (int)((flist >> (8 * k)) & 0xffull);
+                    if (!hessian_rank1(p, c, p.act[c] ? 1.0f : -1.0f)) refactor = true;
+                }
+                if (refactor) hessian_factor(p);
+                update_gradient(p, Ma, qfc, grad, Mgrad);
+                if (!first) {
+                    float gn = 0.0f;
+                    G2_UNROLL
+                    for (int d = 0; d < NV; ++d) gn += grad[d] * grad[d];
+                    gn = sqrtf(gn);
+                    bool improved = gn > tol && (p.prev_cost - p.cost) > tol;
+                    if (!improved || it == SOLVER_ITERS) active = false;
+                }
+                G2_UNROLL
+                for (int d = 0; d < NV; ++d) search[d] = -Mgrad[d];
             }
-            if (refactor) hessian_factor(p);
-            update_gradient(p, Ma, qfc, grad, Mgrad);
-            float gn = 0.0f;
-            G2_UNROLL
-            for (int d = 0; d < NV; ++d) gn += grad[d] * grad[d];
-            gn = sqrtf(gn);
-            bool improved = gn > tol && (p.prev_cost - p.cost) > tol;
-            if (!improved) break;
-            G2_UNROLL
-            for (int d = 0; d < NV; ++d) search[d] = -Mgrad[d];
         }
     }
+    if (!valid) return;
     p.n_newton = n_newton;
     bool bad = false;
     G2_UNROLL
@@ -475,17 +551,6 @@ G2_HDN void solve_constraints(const Go2Model& m, Phys& p) {
         if (c.la >= 0) p.cforce[c.la] = p.cforce[c.la] - f;
         if (c.lb >= 0) p.cforce[c.lb] = p.cforce[c.lb] + f;
     }
-}
-
-// One rigid substep: smooth dynamics -> collision -> constraints -> integrate -> refresh kinematics.
-G2_HDN void substep(const Go2Model& m, Phys& p, float friction, const float* mass_shift, const float* com_shift) {
-    smooth_dynamics(m, p);
-    detect_collisions(m, p, friction);
-    assemble_constraints(m, p);
-    solve_constraints(m, p);
-    integrate(m, p);
-    kinematics(m, mass_shift, com_shift, p);
-    velocities(m, p);
 }
 
 }  // namespace go2

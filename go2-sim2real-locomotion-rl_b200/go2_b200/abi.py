@@ -15,7 +15,8 @@ NLINK, NV, NQ, NHINGE = 13, 18, 19, 12
 MAX_REW, NOBS_MAX, MAX_CPAIRS = 32, 49, 24
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-CUDA_LIB_PATH = os.path.join(_HERE, "libgo2_b200.so")
+# GO2_B200_LIB overrides the in-tree library (kernel-variant experiments: other block sizes / register caps)
+CUDA_LIB_PATH = os.environ.get("GO2_B200_LIB") or os.path.join(_HERE, "libgo2_b200.so")
 
 ENV_WALK, ENV_STAIR, ENV_BASE = 0, 1, 2
 CTRL_MANUAL_PLS, CTRL_MANUAL_FIXED, CTRL_GENESIS_PD = 0, 1, 2

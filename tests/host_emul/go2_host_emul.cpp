@@ -68,7 +68,7 @@ static int run(go2_handle* h, const float* actions, const StepParams& sp) {
     bool warp = lay && !strcmp(lay, "warp");
     for (int b = 0; b < h->cfg.num_envs; ++b) {
         if (warp) w_env_step(h->model, h->cfg, sp, h->bf, actions, b, *w);
-        else { t_env_step(h->model, h->cfg, sp, h->bf, actions, b, *p, w->e, w->out); w->s.err = p->err; }
+        else { t_env_step(h->model, h->cfg, sp, h->bf, actions, b, true, *p, w->e, w->out); w->s.err = p->err; }
         const EnvStepOut& out = w->out;
         if (out.reset) {
             st[STATS_RESETS] += 1.0f;
@@ -145,4 +145,11 @@ int go2_export_links(go2_handle* h, const void* params, int params_bytes, void* 
     return 0;
 }
 long long go2_launch_count(go2_handle* h) { return h ? h->launches : 0; }
+#ifdef GO2_LS_STATS
+void go2_ls_stats(long* out) {  // [calls, A[64], B[64], end[4]]
+    out[0] = g_ls_calls;
+    for (int i = 0; i < 64; ++i) { out[1 + i] = g_lsA[i]; out[65 + i] = g_lsB[i]; }
+    for (int i = 0; i < 4; ++i) out[129 + i] = g_lsend[i];
+}
+#endif
 }
