@@ -134,7 +134,7 @@ def run_gpu(args):
     import numpy as np
     import torch
     import torch.distributed as dist
-    from go2_b200.envs import Go2EnvWalk
+    from go2_b200.envs import Go2EnvStair, Go2EnvWalk
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -144,7 +144,8 @@ def run_gpu(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     B = args.envs
-    env = Go2EnvWalk(B, *load_cfgs("walk"), device=dev, seed=1, env_offset=rank * B, total_envs=world * B)
+    env_cls = Go2EnvStair if args.workload == "stair" else Go2EnvWalk
+    env = env_cls(B, *load_cfgs(args.workload), device=dev, seed=1, env_offset=rank * B, total_envs=world * B)
     env.reset()
     g = torch.Generator(device=dev).manual_seed(1234 + rank)
     n_act = 8
@@ -220,7 +221,7 @@ def run_gpu(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": f"Go2 walk (go2_train_walk cfg, full DR + curriculum), {B} envs/GPU, random actions on device",
+            "config": {"workload": f"Go2 {args.workload} (go2_train_{args.workload} cfg, full DR + curriculum), {B} envs/GPU, random actions on device",
                        "envs_per_gpu": B, "l2": "per-step state + thread-local working set exceed the 126 MB L2 at this batch (inputs larger than L2)",
                        "stats_sync_interval": env.stats_sync_interval},
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": B * env.num_actions * 4, "d2h_bytes_per_step": B * (env.num_obs * 4 + 4 + 1),
@@ -246,6 +247,7 @@ def main():
     ap.add_argument("--envs", type=int, default=65536, help="envs per GPU")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="walk", choices=["walk", "stair"], help="walk = headline metric; stair = BASELINE configs[2]")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -60,6 +60,8 @@ enum BufId {
     B_STATS,         // f32 [STATS_LEN] per-step episode statistics (device-side reduction)
     B_NCONTACT,      // i32 [B]  diagnostics: contacts in the last substep
     B_NNEWTON,       // i32 [B]  diagnostics: Newton iterations in the last substep
+    B_TERRAIN_ROW,   // i32 [B]  stair: difficulty row of the env
+    B_LAST_X,        // f32 [B]  stair: base x at the previous tick (forward_progress)
     B_COUNT
 };
 

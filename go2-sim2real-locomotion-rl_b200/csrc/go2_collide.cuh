@@ -36,6 +36,12 @@ G2_HD GeomPose geom_pose(const Go2Model& m, const P& p, int g) {
 // World AABBs from the oriented local box: centre +- |R| h  (== min/max over the 8 rotated corners).
 G2_HDN void geom_aabbs(const Go2Model& m, Phys& p) {
     for (int g = 0; g < NGEOM; ++g) {
+        if (g == 0 && m.terrain_on) {  // whole field; the terrain narrow phase repeats the exact extent test
+            v3 h = mk3(0.5f * m.terrain_r * m.terrain_sh, 0.5f * m.terrain_c * m.terrain_sh, 0.5f * (m.terrain_zmax - m.terrain_zbot));
+            p.g_c[0] = ld3(m.terrain_org) + mk3(h.x, h.y, m.terrain_zbot + h.z);
+            p.g_h[0] = h;
+            continue;
+        }
         GeomPose gp = geom_pose(m, p, g);
         m3 R = qmat(gp.quat);
         v3 h = ld3(m.g_half[g]);
@@ -76,14 +82,27 @@ struct PairCtx {
     int ga, gb;
     v3 pa, pb;
     m3 Ra, Rb;
+    const v3* prism;  // non-null: geom b is the current terrain prism (6 vertices, bottom 0..2, top 3..5)
 };
 struct Portal {
     v3 v[4], v1[4], v2[4];
 };
 
+// support point of the terrain prism (collider/support_field.py:265-282): top or bottom triangle by the sign of d.z
+G2_HD v3 prism_support(const v3* prism, v3 d) {
+    int i0 = d.z < 0.0f ? 0 : 3;
+    v3 best = prism[i0];
+    float bd = dot(best, d);
+    for (int i = 1; i < 3; ++i) {
+        float t = dot(prism[i0 + i], d);
+        if (t > bd) { bd = t; best = prism[i0 + i]; }
+    }
+    return best;
+}
+
 G2_HD void mink_support(const Go2Model& m, const PairCtx& c, v3 d, v3& v, v3& v1, v3& v2) {
     v1 = support(m, c.ga, c.pa, c.Ra, d);
-    v2 = support(m, c.gb, c.pb, c.Rb, -d);
+    v2 = c.prism ? prism_support(c.prism, -d) : support(m, c.gb, c.pb, c.Rb, -d);
     v = v1 - v2;
 }
 G2_HD v3 portal_dir(const Portal& s) { return normalize3(cross(s.v[2] - s.v[1], s.v[3] - s.v[1])); }
@@ -227,7 +246,7 @@ G2_HDN bool pair_contacts(const Go2Model& m, Phys& p, int ga, int gb, v3 nws, bo
     float tol = 0.5f * MC_TOL * fminf(aabb_diag(m, ga), aabb_diag(m, gb));
     GeomPose A = geom_pose(m, p, ga), B = geom_pose(m, p, gb);
     PairCtx c;
-    c.ga = ga; c.gb = gb; c.pa = A.pos; c.pb = B.pos; c.Ra = qmat(A.quat); c.Rb = qmat(B.quat);
+    c.ga = ga; c.gb = gb; c.pa = A.pos; c.pb = B.pos; c.Ra = qmat(A.quat); c.Rb = qmat(B.quat); c.prism = nullptr;
     v3 ca, cb, n0, pos0;
     float pen0;
     seed_centres(m, c, nws, have, ca, cb);
@@ -302,6 +321,73 @@ G2_HDN bool pair_contacts(const Go2Model& m, Phys& p, int ga, int gb, v3 nws, bo
     return true;
 }
 
+// Geom g against the heightfield terrain (collider/narrowphase.py:346-512 func_contact_mpr_terrain): the cells under
+// the geom's extent are swept row by row as a strip of triangular prisms (each new vertex pair forms a prism with
+// the previous two), MPR runs against every prism whose top reaches the geom's lowest point, at most
+// TERRAIN_PAIR_CONTACTS contacts are kept per geom and near-duplicates are dropped.  The terrain frame is the
+// world frame shifted by terrain_org (the reference builds it with an identity quaternion).
+G2_HDN void terrain_contacts(const Go2Model& m, Phys& p, int g, float mu) {
+    GeomPose G = geom_pose(m, p, g);
+    v3 org = ld3(m.terrain_org);
+    PairCtx c;
+    c.ga = g; c.gb = 0; c.pa = G.pos - org; c.pb = mk3(0, 0, 0); c.Ra = qmat(G.quat); c.Rb = c.Ra;
+    v3 prism[6];
+    c.prism = prism;
+    // extent of the geom along the terrain axes from its own support function
+    float hi[3], lo[3];
+    for (int ax = 0; ax < 3; ++ax) {
+        v3 d = mk3(ax == 0 ? 1.0f : 0.0f, ax == 1 ? 1.0f : 0.0f, ax == 2 ? 1.0f : 0.0f);
+        hi[ax] = comp(support(m, g, c.pa, c.Ra, d), ax);
+        lo[ax] = comp(support(m, g, c.pa, c.Ra, -d), ax);
+    }
+    float tmax[3] = {m.terrain_r * m.terrain_sh, m.terrain_c * m.terrain_sh, m.terrain_zmax};
+    float tmin[3] = {0.0f, 0.0f, m.terrain_zbot};
+    for (int i = 0; i < 3; ++i)
+        if (tmax[i] < lo[i] || tmin[i] > hi[i]) return;
+    for (int i = 0; i < 6; ++i) prism[i] = mk3(0.0f, 0.0f, m.terrain_zbot);
+    float sh = m.terrain_sh;
+    int r_min = (int)floorf(lo[0] / sh), r_max = (int)ceilf(hi[0] / sh);
+    int c_min = (int)floorf(lo[1] / sh), c_max = (int)ceilf(hi[1] / sh);
+    r_min = r_min > 0 ? r_min : 0;
+    c_min = c_min > 0 ? c_min : 0;
+    r_max = r_max < m.terrain_r - 1 ? r_max : m.terrain_r - 1;
+    c_max = c_max < m.terrain_c - 1 ? c_max : m.terrain_c - 1;
+    float tol = 0.5f * MC_TOL * aabb_diag(m, g);  // the terrain's own AABB diagonal is never the smaller one
+    int n_con = 0, first = p.n_contacts;
+    for (int r = r_min; r < r_max; ++r) {
+        int nvert = 0;
+        for (int cc = c_min; cc <= c_max; ++cc) {
+            for (int i = 0; i < 2; ++i) {
+                if (n_con >= TERRAIN_PAIR_CONTACTS) continue;
+                nvert++;
+                prism[0] = prism[1]; prism[1] = prism[2]; prism[3] = prism[4]; prism[4] = prism[5];
+                float x = sh * (float)(r + i), y = sh * (float)cc;
+                prism[2].x = x; prism[2].y = y;
+                prism[5] = mk3(x, y, m.terrain_hf[(size_t)(r + i) * m.terrain_c + cc]);
+                if (nvert > 2 && (prism[3].z >= lo[2] || prism[4].z >= lo[2] || prism[5].z >= lo[2])) {
+                    v3 cb = mk3(0, 0, 0);
+                    for (int k = 0; k < 6; ++k) cb = cb + prism[k];
+                    cb = cb * (1.0f / 6.0f);
+                    v3 n, pos;
+                    float pen;
+                    if (mpr(m, c, c.pa, cb, n, pen, pos)) {
+                        pos = pos + org;
+                        bool dup = false;
+                        for (int j = 0; j < n_con && !dup; ++j) {
+                            int idx = p.n_contacts - 1 - j;
+                            if (idx >= first && norm3(pos - p.con[idx].pos) < tol) dup = true;
+                        }
+                        if (!dup) {
+                            push_contact(m, p, g, 0, n, pos, pen, mu);
+                            n_con++;
+                        }
+                    }
+                }
+            }
+        }
+    }
+}
+
 // Full detection for one env: AABBs -> static pair table -> narrow phase; rebuilds the normal cache.
 G2_HDN void detect_collisions(const Go2Model& m, Phys& p, float friction) {
     geom_aabbs(m, p);
@@ -314,6 +400,10 @@ G2_HDN void detect_collisions(const Go2Model& m, Phys& p, float friction) {
         int a = m.pair_a[ip], b = m.pair_b[ip];
         v3 dc = p.g_c[a] - p.g_c[b], hs = p.g_h[a] + p.g_h[b];
         if (!(fabsf(dc.x) < hs.x && fabsf(dc.y) < hs.y && fabsf(dc.z) < hs.z)) continue;
+        if (m.terrain_on && (a == 0 || b == 0)) {  // geom 0 is the terrain: no normal cache, own narrow phase
+            terrain_contacts(m, p, a == 0 ? b : a, mu);
+            continue;
+        }
         // narrow phase wants the lower geom type first (sphere < cylinder < box)
         int ga = a, gb = b;
         if (m.g_type[ga] > m.g_type[gb]) { ga = b; gb = a; }

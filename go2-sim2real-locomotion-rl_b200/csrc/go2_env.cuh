@@ -77,7 +77,18 @@ struct EnvLocal {
     float air[4];
     int fc[4], lfc[4];
     int ep_len;
+    float last_x;     // stair: base x at the previous tick
+    int terrain_row;  // stair: difficulty row
 };
+
+// Terrain height under world (x, y) - go2_env_stair.py:758-770 (truncating index, clamped to the field)
+G2_HD float terrain_height(const Go2Model& m, float x, float y) {
+    if (!m.terrain_on) return 0.0f;
+    int col = (int)((x - m.terrain_org[0]) / m.terrain_sh), row = (int)((y - m.terrain_org[1]) / m.terrain_sh);
+    col = col < 0 ? 0 : (col > m.terrain_r - 1 ? m.terrain_r - 1 : col);
+    row = row < 0 ? 0 : (row > m.terrain_c - 1 ? m.terrain_c - 1 : row);
+    return m.terrain_hf[(size_t)col * m.terrain_c + row];
+}
 
 template <class P>
 G2_HDN float reward_term(int id, const Go2Model& m, const EnvConfig& cfg, const P& p, EnvLocal& e) {
@@ -91,8 +102,16 @@ G2_HDN float reward_term(int id, const Go2Model& m, const EnvConfig& cfg, const 
             float ez = e.cmd[2] - e.ang_vel.z;
             return expf(-(ez * ez) / cfg.tracking_sigma);
         }
-        case R_LIN_VEL_Z: return e.lin_vel.z * e.lin_vel.z;
-        case R_BASE_HEIGHT: { float d = e.base_pos.z - cfg.base_height_target; return d * d; }
+        case R_LIN_VEL_Z: {  // stair: optional dead zone (go2_env_stair.py:1615-1626)
+            if (cfg.lin_vel_z_deadzone > 0.0f) { float x = fmaxf(fabsf(e.lin_vel.z) - cfg.lin_vel_z_deadzone, 0.0f); return x * x; }
+            return e.lin_vel.z * e.lin_vel.z;
+        }
+        case R_BASE_HEIGHT: {  // stair: height above the local terrain (go2_env_stair.py:1634-1648)
+            float h = e.base_pos.z;
+            if (cfg.has_terrain) h = h - terrain_height(m, e.base_pos.x, e.base_pos.y);
+            float d = h - cfg.base_height_target;
+            return d * d;
+        }
         case R_ACTION_RATE: {
             float s = 0.0f;
             for (int i = 0; i < cfg.num_actions; ++i) { float d = e.last_act[i] - e.act[i]; s += d * d; }
@@ -139,7 +158,9 @@ G2_HDN float reward_term(int id, const Go2Model& m, const EnvConfig& cfg, const 
             for (int i = 0; i < 4; ++i) {
                 int l = cfg.foot_link[i];
                 v3 v = link_vel_world(p, l);
-                float he = cfg.feet_height_target - p.lpos[l].z;
+                float fz = p.lpos[l].z;
+                if (cfg.has_terrain) fz = fz - terrain_height(m, p.lpos[l].x, p.lpos[l].y);  // go2_env_stair.py:1745-1750
+                float he = cfg.feet_height_target - fz;
                 s += (e.fc[i] ? 0.0f : 1.0f) * (he * he) * sqrtf(v.x * v.x + v.y * v.y);
             }
             float mv = sqrtf(e.cmd[0] * e.cmd[0] + e.cmd[1] * e.cmd[1]) > 0.1f ? 1.0f : 0.0f;
@@ -192,6 +213,9 @@ G2_HDN float reward_term(int id, const Go2Model& m, const EnvConfig& cfg, const 
         case R_Y_STABILITY: return -(e.vel_world.y * e.vel_world.y);
         case R_CROUCH_PROGRESS: return fmaxf(0.35f - e.base_pos.z, 0.0f);
         case R_CROUCH_SPEED: return -(e.lin_vel.z * e.lin_vel.z);
+        // ---- stair env, go2_env_stair.py:1659-1669, 1763-1772
+        case R_ORIENTATION_ROLL_ONLY: return e.proj_g.y * e.proj_g.y;
+        case R_FORWARD_PROGRESS: { float dx = e.base_pos.x - e.last_x; e.last_x = e.base_pos.x; return dx; }
         default: return 0.0f;
     }
 }
@@ -247,7 +271,31 @@ G2_HDN void reset_env(const Go2Model& m, const EnvConfig& cfg, const StepParams&
     e.base_pos = ld3(cfg.base_init_pos);
     e.base_quat = ld4(cfg.base_init_quat);
     u4 rp = rng4(rng, SLOT_RESET + 10);
-    if (cfg.has_init_z) e.base_pos.z = urange(cfg.init_z_lo, cfg.init_z_hi, rp.a);
+    if (cfg.kind == ENV_STAIR) {
+        if (cfg.has_terrain && cfg.n_terrain_rows > 1 && !sp.lock_terrain_rows) {
+            // frontier-heavy row assignment (go2_env_stair.py:809-854): 40 % on the highest accessible row, 30 % on the
+            // two rows below it, 30 % on the easy rows - drawn per env instead of by exact counts + permutation
+            u4 rr = rng4(rng, SLOT_RESET + 12);
+            int mr = sp.terrain_max_row, row;
+            float u = u01(rr.a);
+            if (u < 0.4f) row = mr;
+            else if (u < 0.7f) {
+                if (mr >= 2) { int lo = mr - 2, hi = mr - 1; row = lo + (int)(rr.b % (uint32_t)(hi - lo + 1)); }
+                else row = mr;
+            } else {
+                int emax = mr >= 3 ? mr - 3 : 0;
+                row = (int)(rr.c % (uint32_t)(emax + 1));
+            }
+            e.terrain_row = row;
+        }
+        if (cfg.has_terrain) {  // spawn at the row centre, robot standing height on top (go2_env_stair.py:856-871)
+            e.base_pos.x = cfg.row_center[e.terrain_row][0];
+            e.base_pos.y = cfg.row_center[e.terrain_row][1];
+            e.base_pos.z = cfg.row_center[e.terrain_row][2] + cfg.base_init_pos[2];
+        }
+        // reference quirk (go2_env_stair.py:1541-1546): the drawn z is ADDED to the spawn height
+        if (cfg.has_init_z) e.base_pos.z = e.base_pos.z + urange(cfg.init_z_lo, cfg.init_z_hi, rp.a) - cfg.base_init_pos[2] + cfg.base_init_pos[2];
+    } else if (cfg.has_init_z) e.base_pos.z = urange(cfg.init_z_lo, cfg.init_z_hi, rp.a);
     if (cfg.has_init_euler) {
         float roll = urange(cfg.init_euler_lo, cfg.init_euler_hi, rp.b), pitch = urange(cfg.init_euler_lo, cfg.init_euler_hi, rp.c);
         float cr = cosf(roll * 0.5f), sr = sinf(roll * 0.5f), cp = cosf(pitch * 0.5f), sp_ = sinf(pitch * 0.5f);
@@ -268,6 +316,7 @@ G2_HDN void reset_env(const Go2Model& m, const EnvConfig& cfg, const StepParams&
             I32(B_PUSH_REMAIN)[b] = 0;
         }
         for (int i = 0; i < 4; ++i) { e.air[i] = 0.0f; e.fc[i] = 0; e.lfc[i] = 0; }
+        e.last_x = e.base_pos.x;  // stair: forward_progress restarts at the spawn (go2_env_stair.py:1568)
     }
     // episode statistics, then clear the sums
     float ep_s = fmaxf((float)e.ep_len, 1.0f) * dt;
@@ -302,6 +351,8 @@ G2_HDN void env_pre(const Go2Model& m, const EnvConfig& cfg, const StepParams& s
     }
     for (int i = 0; i < 3; ++i) e.cmd[i] = F32(B_COMMANDS)[b * 3 + i];
     e.ep_len = I32(B_EP_LEN)[b];
+    e.last_x = F32(B_LAST_X)[b];
+    e.terrain_row = I32(B_TERRAIN_ROW)[b];
     for (int i = 0; i < 4; ++i) { e.air[i] = 0.0f; e.fc[i] = 0; e.lfc[i] = 0; }
     if (cfg.has_foot_tracking) {
         for (int i = 0; i < 4; ++i) { e.air[i] = F32(B_AIR_TIME)[b * 4 + i]; e.fc[i] = U8(B_FOOT_CONTACT)[b * 4 + i]; }
@@ -507,7 +558,27 @@ G2_HDN void env_post(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
             pr[k++] = sp.mass_shift[2]; pr[k++] = sp.mass_shift[1]; pr[k++] = sp.mass_shift[4]; pr[k++] = sp.mass_shift[3];
             pr[k++] = go[0]; pr[k++] = go[1]; pr[k++] = go[2];
             pr[k++] = F32(B_CUR_PUSH)[b * 3]; pr[k++] = F32(B_CUR_PUSH)[b * 3 + 1]; pr[k++] = F32(B_CUR_PUSH)[b * 3 + 2];
-            pr[k] = cfg.max_delay > 0 ? (float)I32(B_DELAY)[b] / (float)cfg.max_delay : 0.0f;
+            pr[k++] = cfg.max_delay > 0 ? (float)I32(B_DELAY)[b] / (float)cfg.max_delay : 0.0f;
+            if (cfg.kind == ENV_STAIR) {  // go2_env_stair.py:1466-1484: terrain difficulty, then the height scan
+                if (k < cfg.num_priv) {
+                    int den = cfg.n_terrain_rows - 1 > 1 ? cfg.n_terrain_rows - 1 : 1;
+                    pr[k++] = cfg.has_terrain ? (float)e.terrain_row / (float)den : 0.0f;
+                }
+                int ns = cfg.scan_nx * cfg.scan_ny;
+                if (ns > 0 && k + ns <= cfg.num_priv) {
+                    q4 q = e.base_quat;
+                    float yaw = atan2f(2.0f * (q.w * q.z + q.x * q.y), 1.0f - 2.0f * (q.y * q.y + q.z * q.z));
+                    float cy = cosf(yaw), sy = sinf(yaw);
+                    for (int ix = 0; ix < cfg.scan_nx; ++ix) {
+                        float lx = cfg.scan_nx > 1 ? cfg.scan_x0 + (cfg.scan_x1 - cfg.scan_x0) * (float)ix / (float)(cfg.scan_nx - 1) : cfg.scan_x0;
+                        for (int iy = 0; iy < cfg.scan_ny; ++iy) {
+                            float ly = cfg.scan_ny > 1 ? cfg.scan_y0 + (cfg.scan_y1 - cfg.scan_y0) * (float)iy / (float)(cfg.scan_ny - 1) : cfg.scan_y0;
+                            float wx = e.base_pos.x + cy * lx - sy * ly, wy = e.base_pos.y + sy * lx + cy * ly;
+                            pr[k++] = cfg.has_terrain ? terrain_height(m, wx, wy) - e.base_pos.z : 0.0f;
+                        }
+                    }
+                }
+            }
         }
         F32(B_REW)[b] = rew;
         for (int i = 0; i < A; ++i) e.last_act[i] = e.act[i];
@@ -518,6 +589,8 @@ G2_HDN void env_post(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
     U8(B_RESET)[b] = rst ? 1 : 0;
     F32(B_TIMEOUT)[b] = tout ? 1.0f : 0.0f;
     I32(B_EP_LEN)[b] = e.ep_len;
+    F32(B_LAST_X)[b] = e.last_x;
+    I32(B_TERRAIN_ROW)[b] = e.terrain_row;
     I32(B_ERRNO)[b] |= p.err;
     I32(B_NCONTACT)[b] = p.n_contacts;
     I32(B_NNEWTON)[b] = p.n_newton;

@@ -21,6 +21,8 @@ using namespace go2;
 struct go2_handle {
     int device;
     Go2Model* d_model;
+    Go2Model model;      // host copy (patched by go2_set_terrain)
+    float* d_hf;         // terrain heightfield (metres), shared by all envs
     EnvConfig* d_cfg;
     EnvConfig cfg;
     Buffers bf;
@@ -139,7 +141,8 @@ int go2_create(const int32_t* model_iv, int n_iv, const double* model_fv, int n_
         h->nblocks = (B + tpb - 1) / tpb;
     }
     const EnvConfig& c = h->cfg;
-    Go2Model m;
+    h->d_hf = nullptr;
+    Go2Model& m = h->model;
     if (!unpack_model(m, model_iv, n_iv, model_fv, n_fv)) { delete h; return -3; }
     if (c.num_envs <= 0 || c.num_actions > NACT_MAX || c.num_obs > NOBS_MAX || c.hist_size > HIST_MAX || c.n_rew > MAX_REW) { delete h; return -4; }
     if (cudaSetDevice(device) != cudaSuccess) { delete h; return -5; }
@@ -171,6 +174,7 @@ void go2_destroy(go2_handle* h) {
     cudaSetDevice(h->device);
     cudaFree(h->arena);
     cudaFree(h->d_model);
+    if (h->d_hf) cudaFree(h->d_hf);
     cudaFree(h->d_cfg);
     cudaFreeHost(h->h_stats);
     delete h;
@@ -247,6 +251,25 @@ int go2_export_links(go2_handle* h, const void* params, int params_bytes, void* 
     go2_links_kernel<<<(B + GO2_WARPS - 1) / GO2_WARPS, GO2_WARPS * 32, GO2_WARPS * sizeof(WarpS), (cudaStream_t)stream>>>(h->d_model, sp, h->bf);
     h->launches += 1;
     return ck(h, cudaGetLastError(), "go2_links_kernel") ? 0 : -1;
+}
+
+int go2_set_terrain(go2_handle* h, const float* hf_m, int rows, int cols, float h_scale, const float* origin3) {
+    if (!h || !hf_m || rows < 2 || cols < 2 || h_scale <= 0.0f) return -1;
+    if (h->layout == 1) { h->err = "terrain is only implemented by the thread-per-env layout"; return -2; }
+    cudaSetDevice(h->device);
+    if (h->d_hf) cudaFree(h->d_hf);
+    size_t n = (size_t)rows * cols;
+    if (!ck(h, cudaMalloc(&h->d_hf, n * sizeof(float)), "terrain alloc")) return -1;
+    if (!ck(h, cudaMemcpy(h->d_hf, hf_m, n * sizeof(float), cudaMemcpyHostToDevice), "terrain upload")) return -1;
+    Go2Model& m = h->model;
+    float zmax = hf_m[0], zmin = hf_m[0];
+    for (size_t i = 1; i < n; ++i) { zmax = hf_m[i] > zmax ? hf_m[i] : zmax; zmin = hf_m[i] < zmin ? hf_m[i] : zmin; }
+    m.terrain_on = 1; m.terrain_r = rows; m.terrain_c = cols; m.terrain_sh = h_scale;
+    for (int j = 0; j < 3; ++j) m.terrain_org[j] = origin3[j];
+    m.terrain_zmax = zmax; m.terrain_zbot = zmin - 1.0f;  // collider.py:386-389 terrain_xyz_maxmin
+    m.terrain_hf = h->d_hf;
+    m.g_type[0] = GEOM_TERRAIN;
+    return ck(h, cudaMemcpy(h->d_model, &m, sizeof(Go2Model), cudaMemcpyHostToDevice), "model upload") ? 0 : -1;
 }
 
 long long go2_launch_count(go2_handle* h) { return h ? h->launches : 0; }

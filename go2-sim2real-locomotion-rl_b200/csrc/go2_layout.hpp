@@ -24,6 +24,7 @@ inline void compute_layout(const EnvConfig& c, int* dtype, int* rows, int* cols)
     set(B_EP_SUMS, 0, B, c.n_rew > 0 ? c.n_rew : 1); set(B_ERRNO, 1, B, 1);
     set(B_LINK_POS, 0, B, NLINK * 3); set(B_LINK_VEL, 0, B, NLINK * 3); set(B_CONTACT_FORCE, 0, B, NLINK * 3);
     set(B_TORQUE, 0, B, NHINGE); set(B_STATS, 0, 1, STATS_LEN); set(B_NCONTACT, 1, B, 1); set(B_NNEWTON, 1, B, 1);
+    set(B_TERRAIN_ROW, 1, B, 1); set(B_LAST_X, 0, B, 1);
 }
 
 inline size_t compute_offsets(const int* dtype, const int* rows, const int* cols, size_t* offs) {

@@ -23,7 +23,7 @@ constexpr int NHINGE = 12;
 constexpr int NGEOM = 28;   // geom 0 = ground box, 1..27 robot
 constexpr int MAX_PAIRS_STATIC = 352;
 constexpr int MAX_CPAIRS = 24;   // colliding geom pairs kept per env (contact-normal cache entries)
-constexpr int MAX_CONTACTS = 16; // contacts per env kept for the solve (reference cap: 150; overflow -> errno bit)
+constexpr int MAX_CONTACTS = 32; // contacts per env kept for the solve (reference cap: 150; overflow -> errno bit)
 constexpr int MAX_ROWS = 4 * MAX_CONTACTS + NHINGE;
 constexpr int NTRI = NV * (NV + 1) / 2;  // packed lower triangle
 constexpr int MAX_REW = 32;      // reward terms
@@ -31,6 +31,8 @@ constexpr int NACT_MAX = 16;
 constexpr int HIST_MAX = 4;      // action-delay ring slots (max_delay_steps + 1 <= 4)
 constexpr int NOBS_MAX = 49;
 constexpr int SCAN_MAX = 77;
+constexpr int MAX_TERRAIN_ROWS = 16;  // difficulty rows of the stair terrain (go2_env_stair.py:61)
+constexpr int TERRAIN_PAIR_CONTACTS = 5;  // n_contacts_per_pair (collider.py)
 
 constexpr float EPSF = 1.1920929e-07f;  // gs.EPS for precision="32" (genesis/__init__.py:229)
 constexpr float CCD_EPS = 1e-9f;        // collider/mpr.py:16-20
@@ -43,7 +45,7 @@ constexpr float SOLVER_TOL = 1e-6f;
 constexpr int LS_ITERS = 50;
 constexpr float LS_TOL = 1e-2f;
 
-enum GeomType { GEOM_SPHERE = 1, GEOM_CYLINDER = 3, GEOM_BOX = 5 };
+enum GeomType { GEOM_SPHERE = 1, GEOM_CYLINDER = 3, GEOM_BOX = 5, GEOM_TERRAIN = 7 };
 enum ErrBits { ERR_CPAIR_OVERFLOW = 1, ERR_CONTACT_OVERFLOW = 2, ERR_NAN_FORCE = 4, ERR_NAN_ACC = 8 };
 enum EnvKind { ENV_WALK = 0, ENV_STAIR = 1, ENV_BASE = 2 };
 enum CtrlKind { CTRL_MANUAL_PLS = 0, CTRL_MANUAL_FIXED = 1, CTRL_GENESIS_PD = 2 };
@@ -60,6 +62,11 @@ struct Go2Model {
     float g_pos[NGEOM][3], g_quat[NGEOM][4], g_size[NGEOM][3], g_half[NGEOM][3];
     int npairs;
     uint8_t pair_a[MAX_PAIRS_STATIC], pair_b[MAX_PAIRS_STATIC];
+    // Heightfield terrain replacing the ground box (stair env; go2_set_terrain).  hf is [terrain_r][terrain_c] metres,
+    // shared by all envs; cell (r, c) sits at terrain_org + (r, c) * terrain_sh  (collider.py:374-394).
+    int terrain_on, terrain_r, terrain_c;
+    float terrain_sh, terrain_org[3], terrain_zmax, terrain_zbot;  // zbot = min(hf) - 1 (prism bottoms)
+    const float* terrain_hf;
 };
 
 // Reward terms (union of the walk / stair / base env zoos).
@@ -109,6 +116,12 @@ struct EnvConfig {
     // base-env reward parameters
     float rp[16];
     uint32_t seed_lo, seed_hi;
+    // stair env (go2_env_stair.py): difficulty rows, height scan of the privileged obs, reward variants
+    int has_terrain, n_terrain_rows;
+    float row_center[MAX_TERRAIN_ROWS][3];
+    int scan_nx, scan_ny;
+    float scan_x0, scan_x1, scan_y0, scan_y1;
+    float lin_vel_z_deadzone;
 };
 
 // Per-step parameters: everything the reference keeps as host-side python scalars (curriculum-driven
@@ -134,6 +147,8 @@ struct StepParams {
     float kp_genesis, kd_genesis;  // dofs kp/kv for CTRL_GENESIS_PD
     int do_physics;            // 0 => reset-only launch
     int force_reset_all;
+    int terrain_max_row;       // stair: int(curriculum_level * (rows - 1))
+    int lock_terrain_rows;     // stair eval: keep each env's row across resets
 };
 
 }  // namespace go2

@@ -570,7 +570,7 @@ G2_HD void w_pair_ctx(const Go2Model& m, const EnvS& s, int ip, int& ga, int& gb
     if (m.g_type[ga] > m.g_type[gb]) { ga = b; gb = a; }
     A = geom_pose(m, s, ga);
     B = geom_pose(m, s, gb);
-    c.ga = ga; c.gb = gb; c.pa = A.pos; c.pb = B.pos; c.Ra = qmat(A.quat); c.Rb = qmat(B.quat);
+    c.ga = ga; c.gb = gb; c.pa = A.pos; c.pb = B.pos; c.Ra = qmat(A.quat); c.Rb = qmat(B.quat); c.prism = nullptr;
 }
 
 G2_HD void w_detect_collisions(const Go2Model& m, EnvS& s, float friction) {

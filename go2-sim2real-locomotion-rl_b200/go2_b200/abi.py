@@ -13,6 +13,7 @@ import numpy as np
 
 NLINK, NV, NQ, NHINGE = 13, 18, 19, 12
 MAX_REW, NOBS_MAX, MAX_CPAIRS = 32, 49, 24
+MAX_TERRAIN_ROWS = 16
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 # GO2_B200_LIB overrides the in-tree library (kernel-variant experiments: other block sizes / register caps)
@@ -41,7 +42,7 @@ BUF_NAMES = [
     "last_dof_vel", "dof_pos", "dof_vel", "target", "base_pos", "base_quat", "base_lin_vel", "base_ang_vel", "proj_g",
     "base_euler", "kp_factors", "kd_factors", "motor_strength", "eff_kp", "eff_kd", "grav_off", "push_force", "cur_push",
     "push_remain", "delay", "foot_contact", "last_foot_contact", "air_time", "ep_sums", "errno", "link_pos", "link_vel",
-    "contact_force", "torque", "stats", "ncontact", "nnewton",
+    "contact_force", "torque", "stats", "ncontact", "nnewton", "terrain_row", "last_x",
 ]
 BUF = {n: i for i, n in enumerate(BUF_NAMES)}
 STATS_RESETS, STATS_TIMEOUTS, STATS_TRACKING, STATS_ERR, STATS_REW0 = 0, 1, 2, 3, 4
@@ -69,6 +70,9 @@ class EnvConfig(C.Structure):
         ("init_z_lo", _f), ("init_z_hi", _f), ("init_euler_lo", _f), ("init_euler_hi", _f),
         ("min_delay", _i), ("max_delay", _i), ("has_kp_range", _i), ("simulate_action_latency", _i),
         ("rp", _f * 16), ("seed_lo", _u), ("seed_hi", _u),
+        ("has_terrain", _i), ("n_terrain_rows", _i), ("row_center", (_f * 3) * MAX_TERRAIN_ROWS),
+        ("scan_nx", _i), ("scan_ny", _i), ("scan_x0", _f), ("scan_x1", _f), ("scan_y0", _f), ("scan_y1", _f),
+        ("lin_vel_z_deadzone", _f),
     ]
 
 
@@ -81,13 +85,13 @@ class StepParams(C.Structure):
         ("kp_lo", _f), ("kp_hi", _f), ("kd_lo", _f), ("kd_hi", _f),
         ("delay_lo", _i), ("delay_hi", _i),
         ("friction", _f), ("mass_shift", _f * NLINK), ("com_shift", _f * 3), ("kp_genesis", _f), ("kd_genesis", _f),
-        ("do_physics", _i), ("force_reset_all", _i),
+        ("do_physics", _i), ("force_reset_all", _i), ("terrain_max_row", _i), ("lock_terrain_rows", _i),
     ]
 
 
 _EXPORTS = [
     "go2_abi_sizes", "go2_create", "go2_destroy", "go2_last_error", "go2_buffer_info", "go2_step", "go2_reset_all",
-    "go2_step_host", "go2_read_stats", "go2_export_links", "go2_launch_count",
+    "go2_step_host", "go2_read_stats", "go2_export_links", "go2_launch_count", "go2_set_terrain",
 ]
 _DTYPES = {0: np.float32, 1: np.int32, 2: np.uint8}
 

@@ -96,5 +96,13 @@ class Go2Core:
     def export_links(self, sp: abi.StepParams):
         self.L.check(self.h, self.lib.go2_export_links(self.h, C.byref(sp), C.sizeof(sp), self._stream()), "go2_export_links")
 
+    def set_terrain(self, hf_m, h_scale, origin):
+        """Heightfield terrain (metres, [rows][cols]) replacing the ground box - go2_set_terrain."""
+        hf = np.ascontiguousarray(hf_m, dtype=np.float32)
+        org = np.asarray(origin, dtype=np.float32)
+        self._terrain_keep = (hf, org)
+        self.L.check(self.h, self.lib.go2_set_terrain(self.h, hf.ctypes.data_as(C.c_void_p), int(hf.shape[0]), int(hf.shape[1]),
+                                                      C.c_float(float(h_scale)), org.ctypes.data_as(C.c_void_p)), "go2_set_terrain")
+
     def launch_count(self):
         return int(self.lib.go2_launch_count(self.h))

@@ -342,7 +342,9 @@ class Go2EnvWalk(_Go2EnvBase):
         if "init_euler_range" in e:
             c.has_init_euler = 1
             c.init_euler_lo, c.init_euler_hi = math.radians(e["init_euler_range"][0]), math.radians(e["init_euler_range"][1])
+        self._fill_flavour(c)
         self._bind(c)
+        self._after_bind()
         b = self.core.buf
         self.privileged_obs_buf = b["priv"] if self.num_privileged_obs else self.obs_buf
         self._applied_actions = b["applied"]
@@ -395,6 +397,16 @@ class Go2EnvWalk(_Go2EnvBase):
         self.ground = _GroundFacade(self)
         self.scene = _SceneFacade(self)
 
+    def _fill_flavour(self, c):
+        """Hook for flavours built on the walk env (stair): extra EnvConfig fields before the handle is created."""
+
+    def _after_bind(self):
+        """Hook: the native handle exists (upload terrain etc.)."""
+
+    def _dr_level(self, lvl):
+        """DR difficulty as a function of the curriculum level (walk: identical)."""
+        return lvl
+
     # ---- curriculum-driven runtime values (go2_env_walk.py:611-686)
     def _rebuild_obs_noise_vec(self, level):
         if self.obs_noise_components is None or self.obs_noise_level_max <= 0.0:
@@ -413,6 +425,8 @@ class Go2EnvWalk(_Go2EnvBase):
         if not self.curriculum.enabled and not force:
             return
         lvl = float(self.curriculum.level) if self.curriculum.enabled else 1.0
+        cmd_lvl = lvl
+        lvl = self._dr_level(lvl)  # stair: two-phase DR schedule; the command curriculum keeps the terrain level
         self._obs_noise_level_cur = _lerp(0.0, self.obs_noise_level_max, lvl)
         self._action_noise_std_cur = _lerp(0.0, self.action_noise_std_max, lvl)
         self._rebuild_obs_noise_vec(lvl)
@@ -429,7 +443,7 @@ class Go2EnvWalk(_Go2EnvBase):
             self._push_enable_cur = True
         self._delay_max_cur = int(round(_lerp(float(self.delay_easy_max), float(self._max_delay_steps), lvl)))
         if self._cmd_curriculum:
-            frac = _lerp(self._cmd_start_frac, 1.0, lvl)
+            frac = _lerp(self._cmd_start_frac, 1.0, cmd_lvl)
             for k, fr in self._cmd_full_ranges.items():
                 ctr, half = (fr[0] + fr[1]) / 2.0, (fr[1] - fr[0]) / 2.0
                 self._cmd_cur_ranges[k] = [ctr - half * frac, ctr + half * frac]
@@ -441,6 +455,14 @@ class Go2EnvWalk(_Go2EnvBase):
                     "push_enable": bool(self._push_enable_cur), "push_force_range_cur": list(self._push_force_range_cur),
                     "push_interval_steps": int(self._push_interval), "delay_max_cur": int(self._delay_max_cur),
                     "cmd_ranges": {k: list(v) for k, v in self._cmd_cur_ranges.items()}})
+        self._curriculum_extras(cur, cmd_lvl, lvl)
+
+    def _curriculum_extras(self, cur, lvl, dr_lvl):
+        """Hook: flavour-specific entries of extras['curriculum']."""
+
+    def _sample_t(self):
+        """DR interpolation parameter of this tick's resets (go2_env_walk.py:1162)."""
+        return self.curriculum.sample_level()
 
     # ---- per-step parameter block
     def _make_params(self, physics=True):
@@ -462,7 +484,7 @@ class Go2EnvWalk(_Go2EnvBase):
                 sp.obs_noise[i] = float(self.obs_noise_vec[i])
         for i, k in enumerate(("lin_vel_x", "lin_vel_y", "ang_vel")):
             sp.cmd_lo[i], sp.cmd_hi[i] = float(self._cmd_cur_ranges[k][0]), float(self._cmd_cur_ranges[k][1])
-        t = self._t_sample = self.curriculum.sample_level()
+        t = self._t_sample = self._sample_t()
         sp.kpf_lo, sp.kpf_hi = _lerp_range(self.kp_factor_easy, self.kp_factor_hard, t)
         sp.kdf_lo, sp.kdf_hi = _lerp_range(self.kd_factor_easy, self.kd_factor_hard, t)
         sp.kp_lo, sp.kp_hi = _lerp_range(self.kp_easy, self.kp_hard, t)
@@ -477,8 +499,12 @@ class Go2EnvWalk(_Go2EnvBase):
         for j in range(3):
             sp.com_shift[j] = float(self._com_shift[j])
         sp.kp_genesis, sp.kd_genesis = float(self._kp_genesis), float(self._kd_genesis)
+        self._flavour_params(sp)
         self._step_count += 1
         return sp
+
+    def _flavour_params(self, sp):
+        """Hook: flavour-specific StepParams fields."""
 
     # ---- host side of reset_idx: curriculum aggregates, global DR, episode log (go2_env_walk.py:688-756,803-848,1228-1235)
     def _after_resets(self, stats):
@@ -537,6 +563,95 @@ class Go2EnvWalk(_Go2EnvBase):
         self.core.reset_all(sp)
         self._after_resets(self._read_stats())
         return self.obs_buf, None
+
+
+class Go2EnvStair(Go2EnvWalk):
+    """Stair env (go2_env_stair.py): the walk env on a stair heightfield - difficulty rows with frontier-heavy
+    assignment, terrain-aware spawn, terrain-relative base-height / foot-clearance rewards, lin_vel_z dead zone,
+    orientation_roll_only, forward_progress, two-phase DR schedule, 182-d privileged obs (terrain row + 11x7 scan)."""
+
+    KIND = abi.ENV_STAIR
+
+    def _fill_flavour(self, c):
+        e = self.env_cfg
+        self._terrain_cfg = e.get("terrain", None)
+        self._use_terrain = self._terrain_cfg is not None and self._terrain_cfg.get("enabled", False)
+        self._lock_terrain_rows = False
+        dr = e.get("dr_schedule", None)
+        self._dr_enabled = dr is not None
+        if dr is not None:
+            self._dr_phase1_level = float(dr.get("phase1_level", 0.15))
+            self._dr_terrain_gate = float(dr.get("terrain_gate", 0.85))
+        c.lin_vel_z_deadzone = float(self.reward_cfg.get("lin_vel_z_deadzone", 0.0))
+        if self._use_terrain:
+            from .terrain import build_stair_terrain
+
+            self._hf, self._terrain_info = build_stair_terrain(self._terrain_cfg)
+            ti = self._terrain_info
+            self._num_terrain_rows = ti["num_difficulty_rows"]
+            if self._num_terrain_rows > abi.MAX_TERRAIN_ROWS:
+                raise ValueError(f"at most {abi.MAX_TERRAIN_ROWS} terrain difficulty rows are supported")
+            self._terrain_row_centers, self._terrain_step_heights = ti["row_centers"], ti["step_heights_m"]
+            self._terrain_origin, self._h_scale, self._v_scale = ti["terrain_origin"], ti["horizontal_scale"], ti["vertical_scale"]
+            hs = self._terrain_cfg.get("height_scan", {})
+            self._scan_nx, self._scan_ny = int(hs.get("num_x", 11)), int(hs.get("num_y", 7))
+            self._scan_n = self._scan_nx * self._scan_ny
+            xr, yr = hs.get("x_range", [-0.5, 0.5]), hs.get("y_range", [-0.3, 0.3])
+            c.has_terrain, c.n_terrain_rows = 1, self._num_terrain_rows
+            for r, ctr in enumerate(self._terrain_row_centers):
+                for j in range(3):
+                    c.row_center[r][j] = float(ctr[j])
+            c.scan_nx, c.scan_ny = self._scan_nx, self._scan_ny
+            c.scan_x0, c.scan_x1, c.scan_y0, c.scan_y1 = float(xr[0]), float(xr[1]), float(yr[0]), float(yr[1])
+        else:
+            self._num_terrain_rows, self._terrain_row_centers, self._scan_n = 1, [(0.0, 0.0, 0.0)], 0
+            c.n_terrain_rows = 1
+
+    def _after_bind(self):
+        b = self.core.buf
+        self._env_terrain_row = b["terrain_row"].view(-1)
+        self._last_base_pos_x = b["last_x"].view(-1)
+        if self._use_terrain:
+            self._hf_heights = torch.tensor(self._hf.astype(np.float32) * np.float32(self._v_scale), device=self.device)
+            self.core.set_terrain(self._hf.astype(np.float32) * np.float32(self._v_scale), self._h_scale, self._terrain_origin)
+
+    # go2_env_stair.py:972-988
+    def _get_dr_level(self, terrain_level):
+        if not self._dr_enabled:
+            return terrain_level
+        if terrain_level < self._dr_terrain_gate:
+            return self._dr_phase1_level
+        prog = _clamp01((terrain_level - self._dr_terrain_gate) / max(1e-6, 1.0 - self._dr_terrain_gate))
+        return _lerp(self._dr_phase1_level, 1.0, prog)
+
+    _dr_level = _get_dr_level
+
+    def _sample_t(self):  # go2_env_stair.py:1506-1511: DR level of the resets follows the two-phase schedule
+        return self._get_dr_level(self.curriculum.level if self.curriculum.enabled else 1.0)
+
+    def _curriculum_extras(self, cur, lvl, dr_lvl):
+        cur["terrain_max_row"] = int(lvl * (self._num_terrain_rows - 1)) if self._use_terrain else 0
+        cur["dr_level"] = float(dr_lvl)
+
+    def _flavour_params(self, sp):
+        lvl = float(self.curriculum.level) if self.curriculum.enabled else 1.0
+        mr = int(lvl * (self._num_terrain_rows - 1))
+        sp.terrain_max_row = max(0, min(mr, self._num_terrain_rows - 1))
+        sp.lock_terrain_rows = int(self._lock_terrain_rows)
+
+    def _after_resets(self, stats):
+        super()._after_resets(stats)
+        if self._use_terrain and int(round(float(stats[abi.STATS_RESETS]))) > 0 and "episode" in self.extras:
+            self.extras["episode"]["terrain_mean_row"] = float(self._env_terrain_row.float().mean())  # over all envs (not only the reset ones)
+
+    # go2_env_stair.py:758-770
+    def _get_terrain_height(self, x, y):
+        if not self._use_terrain:
+            return torch.zeros_like(x)
+        ox, oy, _ = self._terrain_origin
+        col = ((x - ox) / self._h_scale).long().clamp(0, self._hf_heights.shape[0] - 1)
+        row = ((y - oy) / self._h_scale).long().clamp(0, self._hf_heights.shape[1] - 1)
+        return self._hf_heights[col, row]
 
 
 class Go2EnvBaseFlavour(_Go2EnvBase):

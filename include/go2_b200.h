@@ -57,6 +57,12 @@ int go2_read_stats(go2_handle* h, float* host_out, int n, void* stream);
  * (replaces RigidEntity.get_links_pos / get_links_vel, rigid_entity.py:2241-2406). */
 int go2_export_links(go2_handle* h, const void* params, int params_bytes, void* stream);
 
+/* Replace the ground box by a heightfield terrain shared by all envs: replaces
+ * scene.add_entity(gs.morphs.Terrain(height_field, horizontal_scale, vertical_scale, pos))
+ * (go2_env_stair.py:423-433; collider.py:374-394 _init_terrain_state).  `hf_m`: host f32 [rows][cols] heights in
+ * metres (height_field * vertical_scale), cell (r, c) at origin + (r, c) * h_scale.  Call before the first step. */
+int go2_set_terrain(go2_handle* h, const float* hf_m, int rows, int cols, float h_scale, const float* origin3);
+
 /* Number of kernels this library has launched on the handle since creation. */
 long long go2_launch_count(go2_handle* h);
 

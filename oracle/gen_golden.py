@@ -54,6 +54,32 @@ def walk_short_cfgs():
     return env_cfg, obs_cfg, reward_cfg, command_cfg
 
 
+def stair_det_cfgs():
+    """go2_train_stair.get_cfgs() with the random draws removed (terrain, curriculum level and rewards kept)."""
+    env_cfg, obs_cfg, reward_cfg, command_cfg = load_funcs(os.path.join(FINAL, "go2_train_stair.py"), ["get_cfgs"]).get_cfgs()
+    for k in DR_KEYS:
+        env_cfg.pop(k, None)
+    env_cfg.update(episode_length_s=1.6, resampling_time_s=0.6)
+    command_cfg.update(lin_vel_x_range=[0.5, 0.5], lin_vel_y_range=[0.0, 0.0], ang_vel_range=[0.0, 0.0])
+    return env_cfg, obs_cfg, reward_cfg, command_cfg
+
+
+def stair_place(env):
+    """One env per difficulty row (rows locked), robots dropped at staggered x over the first flight of stairs so
+    that feet, calves and the trunk meet step edges of every height."""
+    B = env.num_envs
+    env._env_terrain_row[:] = torch.arange(B) % env._num_terrain_rows
+    env._lock_terrain_rows = True
+    env.reset()
+    pos = env.base_pos.clone()
+    pos[:, 0] = 1.6 + 0.37 * torch.arange(B, dtype=torch.float32)
+    pos[:, 2] = env._get_terrain_height(pos[:, 0], pos[:, 1]) + 0.40
+    idx = torch.arange(B)
+    env.base_pos[:] = pos
+    env.robot.set_pos(pos, zero_velocity=False, envs_idx=idx)
+    env._last_base_pos_x[:] = pos[:, 0]
+
+
 def base_cfgs(script):
     env_cfg, obs_cfg, reward_cfg, command_cfg = load_funcs(os.path.join(FINAL, script), ["get_cfgs"]).get_cfgs()
     return env_cfg, obs_cfg, reward_cfg, command_cfg
@@ -69,10 +95,12 @@ def snapshot(env, kind):
              base_lin_vel=env.base_lin_vel.numpy().copy(), base_ang_vel=env.base_ang_vel.numpy().copy(),
              proj_g=env.projected_gravity.numpy().copy(),
              ep_sums=np.stack([v.numpy().copy() for v in env.episode_sums.values()]) if env.episode_sums else np.zeros((0, env.num_envs)))
-    if kind == "walk":
+    if kind in ("walk", "stair"):
         s.update(hist=env._action_history.numpy().copy(), hist_idx=np.array(env._action_history_write_idx),
                  applied=env._applied_actions.numpy().copy(), delay=env._delay_steps.numpy().copy(),
                  air_time=env._feet_air_time.numpy().copy(), foot_contact=env._foot_contact.numpy().copy())
+    if kind == "stair":
+        s.update(terrain_row=env._env_terrain_row.numpy().astype(np.int32), last_x=env._last_base_pos_x.numpy().copy())
     return s
 
 
@@ -82,18 +110,20 @@ def outputs(env, obs, rew, done, extras, kind):
              o_timeout=extras["time_outs"].numpy().copy(), o_qpos=r.get_qpos(), o_qvel=r.get_qvel(),
              o_base_pos=env.base_pos.numpy().copy(), o_commands=env.commands.numpy().copy(), o_ep_len=env.episode_length_buf.numpy().copy(),
              o_ncon=r.get_solver_stats()[:, 0].copy())
-    if kind == "walk":
+    if kind in ("walk", "stair"):
         o.update(o_priv=extras["observations"]["critic"].numpy().copy(), o_foot_contact=env._foot_contact.numpy().copy(),
                  o_air_time=env._feet_air_time.numpy().copy())
     return o
 
 
-def run(env_cls, cfgs, kind, B, T, act_std, seed, act_dim, episode_len_override=None):
+def run(env_cls, cfgs, kind, B, T, act_std, seed, act_dim, after_reset=None):
     cfgs_json = json.loads(json.dumps(cfgs))  # pristine copy (the ctor multiplies reward scales by dt in place)
     torch.manual_seed(1)
     with contextlib.redirect_stdout(io.StringIO()):
         env = env_cls(B, *cfgs)
     env.reset()
+    if after_reset is not None:
+        after_reset(env)
     g = torch.Generator().manual_seed(seed)
     rec = {}
     for t in range(T):
@@ -111,15 +141,20 @@ def main():
     os.makedirs(OUT, exist_ok=True)
     from go2_env_walk import Go2Env as WalkEnv
     from go2_env_base import Go2Env as BaseEnv
+    from go2_env_stair import Go2Env as StairEnv
 
     jobs = [
         ("walk_det", WalkEnv, walk_det_cfgs(), "walk", 12, 200, 0.5, 1234, 16),
         ("walk_short", WalkEnv, walk_short_cfgs(), "walk", 8, 160, 0.8, 99, 16),
         ("crouch", BaseEnv, base_cfgs("go2_train_crouch.py"), "base", 8, 160, 0.6, 1234, 12),
         ("jump", BaseEnv, base_cfgs("go2_train_jump.py"), "base", 8, 160, 0.6, 4321, 12),
+        ("stair_det", StairEnv, stair_det_cfgs(), "stair", 13, 120, 0.5, 77, 16, stair_place),
     ]
-    for name, cls, cfgs, kind, B, T, std, seed, ad in jobs:
-        out, cj = run(cls, cfgs, kind, B, T, std, seed, ad)
+    only = sys.argv[1:]
+    for name, cls, cfgs, kind, B, T, std, seed, ad, *hook in jobs:
+        if only and name not in only:
+            continue
+        out, cj = run(cls, cfgs, kind, B, T, std, seed, ad, hook[0] if hook else None)
         np.savez_compressed(os.path.join(OUT, name + ".npz"), **out)
         with open(os.path.join(OUT, name + "_cfg.json"), "w") as f:
             json.dump(cj, f)

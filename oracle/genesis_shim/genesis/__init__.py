@@ -54,7 +54,11 @@ class _URDF(_Opt):
     pass
 
 
-morphs = types.SimpleNamespace(URDF=_URDF)
+class _Terrain(_Opt):
+    pass
+
+
+morphs = types.SimpleNamespace(URDF=_URDF, Terrain=_Terrain)
 
 
 def _np(x):
@@ -196,12 +200,16 @@ class Scene:
         self._rigid = None
         self._model = None
         self._robot_morph = None
+        self._terrain_morph = None
         self.sim = types.SimpleNamespace(rigid_solver=_RigidSolverView(self))
 
     def add_entity(self, morph, **kw):
         from go2_b200.model import load_model
 
-        if "plane" in morph.file:
+        if isinstance(morph, _Terrain):  # heightfield terrain in place of the plane (go2_env_stair.py:423-433)
+            self._terrain_morph = morph
+            ent = _Ground(self)
+        elif "plane" in morph.file:
             ent = _Ground(self)
         else:
             self._model = load_model()
@@ -214,6 +222,10 @@ class Scene:
         m = self._robot_morph
         self._rigid = OracleRigid(n_envs, self._model, kind=ORACLE_KIND, base_pos=tuple(np.asarray(m.pos, dtype=float)),
                                   base_quat=tuple(np.asarray(m.quat, dtype=float)))
+        t = self._terrain_morph
+        if t is not None:
+            hf = np.asarray(t.height_field, dtype=np.float64) * float(t.vertical_scale)
+            self._rigid.set_terrain(hf, float(t.horizontal_scale), np.asarray(t.pos, dtype=np.float64))
 
     def step(self):
         self._rigid.step(self._substeps)

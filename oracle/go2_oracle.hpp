@@ -181,7 +181,7 @@ inline void imp_aref(const real* p, real neg_pen, real vel, real pos, real& imp,
     aref = -b * vel - k * imp * pos;
 }
 
-enum { GEOM_SPHERE = 1, GEOM_CYLINDER = 3, GEOM_BOX = 5 };
+enum { GEOM_SPHERE = 1, GEOM_CYLINDER = 3, GEOM_BOX = 5, GEOM_TERRAIN = 7 };
 enum { CTRL_FORCE = 0, CTRL_VELOCITY = 1, CTRL_POSITION = 2 };
 enum { ERR_BROAD_OVERFLOW = 1, ERR_CONTACT_OVERFLOW = 2, ERR_NAN_FORCE = 4, ERR_NAN_ACC = 8 };
 
@@ -210,6 +210,12 @@ struct Model {
     V3 gravity;
     real kp[NV], kv[NV];
     int mass_parent_mask[NV][NV];
+    // heightfield terrain replacing the ground box (collider/collider.py:374-394 _init_terrain_state)
+    bool has_terrain;
+    const real* terrain_hf;      // [rc0][rc1] metres
+    int terrain_rc[2];
+    real terrain_scale;          // horizontal scale
+    real terrain_xyz_maxmin[6];  // x max, y max, z max, x min, y min, z min - 1
 };
 
 struct Contact {
@@ -242,6 +248,8 @@ struct Env {
     V3 cd_ang[NL], cd_vel[NL], cdd_ang[NL], cdd_vel[NL], cfrc_ang[NL], cfrc_vel[NL];
     V3 gpos[NG_MAX], aabb_min[NG_MAX], aabb_max[NG_MAX];
     Q4 gquat[NG_MAX];
+    V3 prism[6];          // collider_state.prism (terrain narrow phase)
+    real xyz_max_min[6];  // collider_state.xyz_max_min
     // dynamics
     real M[NV][NV], ML[NV][NV], MDinv[NV];
     real qf_applied[NV], qf_bias[NV], force[NV], qf_smooth[NV], acc_smooth[NV], acc[NV];

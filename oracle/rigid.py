@@ -70,6 +70,11 @@ class OracleRigid:
     def step(self, substeps=2):
         self.lib.orc_step(self.h, int(substeps))
 
+    def set_terrain(self, hf_m, h_scale, origin):
+        """Heightfield terrain (metres, [rows][cols]) instead of the ground plane."""
+        hf = _d(hf_m)
+        self.lib.orc_set_terrain(self.h, _p(hf), int(hf.shape[0]), int(hf.shape[1]), C.c_double(float(h_scale)), _p(_d(origin)))
+
     def control_dofs_force(self, force, dofs):
         f, d = _d(force), _i(dofs)
         self.lib.orc_control_dofs_force(self.h, _p(d), len(d), _p(f))

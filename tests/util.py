@@ -17,9 +17,9 @@ def load_golden(name):
 
 
 def make_env(kind, cfgs, B, backend, hostemu_lib=None, **kw):
-    from go2_b200.envs import Go2EnvBaseFlavour, Go2EnvWalk
+    from go2_b200.envs import Go2EnvBaseFlavour, Go2EnvStair, Go2EnvWalk
 
-    cls = Go2EnvWalk if kind == "walk" else Go2EnvBaseFlavour
+    cls = {"walk": Go2EnvWalk, "stair": Go2EnvStair}.get(kind, Go2EnvBaseFlavour)
     cfgs = json.loads(json.dumps(cfgs))
     if backend == "hostemu":
         return cls(B, *cfgs, device="cpu", lib_path=hostemu_lib, **kw)
@@ -58,7 +58,11 @@ def force_state(env, g, t, kind):
     b["ep_len"].copy_(_t(env, g["ep_len"][t][:, None], torch.int32))
     if g["ep_sums"].shape[1] > 0:
         b["ep_sums"].copy_(_t(env, g["ep_sums"][t].T))
-    if kind == "walk":
+    if kind == "stair":
+        b["terrain_row"].copy_(_t(env, g["terrain_row"][t][:, None], torch.int32))
+        b["last_x"].copy_(_t(env, g["last_x"][t][:, None]))
+        env._lock_terrain_rows = True
+    if kind in ("walk", "stair"):
         b["hist"].copy_(_t(env, g["hist"][t].reshape(B, -1)))
         env._action_history_write_idx = int(g["hist_idx"][t])
         b["applied"].copy_(_t(env, g["applied"][t]))
