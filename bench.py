@@ -28,7 +28,10 @@ for p in (ROOT, PKG):
 
 METRIC = "env-steps/sec (whole box) Go2 walk"
 UNIT = "env-steps/s"
-BYTES_PER_ENV_STEP = 1952  # algorithmic bytes per walk env-step
+BYTES_PER_ENV_STEP = {"walk": 1952, "stair": 2272}  # algorithmic bytes per env-step
+# from profiles/r01_v3_step_kernel_ncu_summary.txt (ncu --set full, walk, 65,536 envs, one launch)
+NCU_DRAM_BYTES_PER_LAUNCH_65536 = 4.334124e9 + 2.599485e9
+NCU_WARP_INSTR_PER_ENV_STEP = 763299468 / 65536
 
 
 def load_cfgs(name):
@@ -208,7 +211,12 @@ def run_gpu(args):
         value = world * B * args.steps / (ms_total * 1e-3)
         e2e = world * B * args.steps / (ms_e2e * 1e-3)
         peak, which = peaks()
-        ach = B * BYTES_PER_ENV_STEP / (kern_avg * 1e-3) / 1e9
+        bpe = BYTES_PER_ENV_STEP[args.workload]
+        ach = B * bpe / (kern_avg * 1e-3) / 1e9
+        walk64k = args.workload == "walk" and B == 65536
+        sm_mhz = (clocks or {}).get("sm_mhz") or 1965
+        n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
+        issue_frac = (NCU_WARP_INSTR_PER_ENV_STEP * B / (kern_avg * 1e-3)) / (4.0 * n_sm * sm_mhz * 1e6) if walk64k else None
         cores = os.cpu_count() or 1
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
@@ -222,15 +230,17 @@ def run_gpu(args):
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": f"Go2 {args.workload} (go2_train_{args.workload} cfg, full DR + curriculum), {B} envs/GPU, random actions on device",
-                       "envs_per_gpu": B, "l2": "per-step state + thread-local working set exceed the 126 MB L2 at this batch (inputs larger than L2)",
+                       "envs_per_gpu": B, "l2": "per-tick state (2 KB/env) + thread-local working set of the resident threads (~460 MB at 65,536 envs) exceed the 126 MB L2: inputs larger than L2, no flush needed",
                        "stats_sync_interval": env.stats_sync_interval},
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": B * env.num_actions * 4, "d2h_bytes_per_step": B * (env.num_obs * 4 + 4 + 1),
                     "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+            "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": NCU_DRAM_BYTES_PER_LAUNCH_65536 if walk64k else None,
+                         "traffic_unit": "B per launch (dram read+write, ncu --set full, profiles/r01_v3_step_kernel_ncu_summary.txt)",
+                         "algorithmic_bytes_per_launch": B * bpe, "issue_frac": issue_frac,
                          "peak_source": which, "kernel": "go2_step_kernel", "kernel_ms_avg": kern_avg, "kernel_ms_median": kern_ms[len(kern_ms) // 2],
-                         "bytes_per_env_step": BYTES_PER_ENV_STEP,
-                         "note": "path is fp32-ALU/latency bound (SURVEY 8d): HBM fraction is reported for accounting, see profiles/"},
+                         "bytes_per_env_step": bpe,
+                         "note": "thread-local-memory latency bound, not HBM-bandwidth shaped (DESIGN.md 4): HBM fraction is the designated accounting; issue_frac = issued warp-instr/s (ncu instr count per env-step x measured rate) / (4 x SMs x clock)"},
             "cpu_baseline": cpu, "clocks": clocks,
             "diag": {"mean_contacts": float(stats["ncontact"].float().mean()), "mean_newton_iters": float(stats["nnewton"].float().mean()),
                      "errno_envs": int((stats["errno"] != 0).sum())},

@@ -89,3 +89,22 @@ def test_oracle_free_fall():
     n, h = 20, 0.01
     assert abs(o.get_qpos()[0, 2] - (3.0 - 9.81 * h * h * n * (n + 1) / 2)) < 1e-9
     assert abs(o.get_qvel()[0, 2] + 9.81 * t) < 1e-9
+
+
+STAIR_HF_SHA256 = "9ccdb2c405cef8d826eebb46dd0f6b022728a6bca4618b9597040ba77463bc84"  # reference build_stair_terrain output (int16, C order)
+
+
+def test_stair_terrain_matches_reference_fixture():
+    """build_stair_terrain restated in go2_b200/terrain.py vs the digest of the reference's own function
+    (go2_env_stair.py:47-185, executed in the build container on go2_train_stair.get_cfgs()['terrain'])."""
+    import hashlib
+    import json
+
+    from go2_b200.terrain import build_stair_terrain
+
+    cfgs = json.load(open(os.path.join(ROOT, "go2-sim2real-locomotion-rl_b200/go2_b200/cfgs/stair.json")))
+    hf, info = build_stair_terrain(cfgs[0]["terrain"])
+    assert hf.shape == (704, 1560) and hf.dtype == np.int16
+    assert int(hf.astype(np.int64).sum()) == 49645440 and int(hf.max()) == 180
+    assert hashlib.sha256(hf.tobytes()).hexdigest() == STAIR_HF_SHA256
+    assert abs(info["row_centers"][0][0] - 1.0) < 1e-9 and abs(info["terrain_origin"][1] + 39.0) < 1e-9
