@@ -203,10 +203,34 @@ def run_gpu(args):
     barrier()
     ms_e2e = e0.elapsed_time(e1)
 
-    t = torch.tensor([ms_total, ms_e2e, kern_avg], device=dev, dtype=torch.float64)
+    # ---- closed loop with a policy in the timed region (BASELINE north star: "with the shipped go2-walk checkpoint
+    # policy"; the blob is missing from the reference checkout, so: the same 49-512-256-128-16 ELU actor of
+    # go2_train_walk.py's train_cfg, random-initialised with a fixed seed, evaluated by torch in fp32)
+    torch.manual_seed(188000)
+    dims = [env.num_obs, 512, 256, 128, env.num_actions]
+    layers = []
+    for i in range(4):
+        layers.append(torch.nn.Linear(dims[i], dims[i + 1]))
+        if i < 3:
+            layers.append(torch.nn.ELU())
+    actor = torch.nn.Sequential(*layers).to(dev).eval()
+    obs = env.obs_buf
+    with torch.no_grad():
+        for i in range(max(3, args.warmup // 2)):
+            obs, _, _, _ = env.step(actor(obs))
+        p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        p0.record()
+        for i in range(args.steps):
+            obs, _, _, _ = env.step(actor(obs))
+        p1.record()
+        barrier()
+    ms_pol = p0.elapsed_time(p1)
+
+    t = torch.tensor([ms_total, ms_e2e, kern_avg, ms_pol], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total, ms_e2e, kern_avg = [float(x) for x in t.tolist()]
+    ms_total, ms_e2e, kern_avg, ms_pol = [float(x) for x in t.tolist()]
     if rank == 0:
         value = world * B * args.steps / (ms_total * 1e-3)
         e2e = world * B * args.steps / (ms_e2e * 1e-3)
@@ -234,6 +258,8 @@ def run_gpu(args):
                        "stats_sync_interval": env.stats_sync_interval},
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": B * env.num_actions * 4, "d2h_bytes_per_step": B * (env.num_obs * 4 + 4 + 1),
                     "ms_per_step": ms_e2e / args.steps},
+            "with_policy": {"value": world * B * args.steps / (ms_pol * 1e-3), "unit": UNIT, "ms_per_step": ms_pol / args.steps,
+                            "policy": "49-512-256-128-16 ELU actor, fixed-seed random init (shipped model_188000.pt blob absent), torch fp32, inside the timed loop"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": NCU_DRAM_BYTES_PER_LAUNCH_65536 if walk64k else None,
                          "traffic_unit": "B per launch (dram read+write, ncu --set full, profiles/r01_v3_step_kernel_ncu_summary.txt)",

@@ -33,6 +33,7 @@ struct go2_handle {
     long long launches;
     int layout;  // 0 = thread per env (default), 1 = warp per env
     int tpb, nblocks;  // launch shape of the thread-per-env kernel
+    int smem_pad;      // experiment knob (GO2_B200_SMEM_PAD): unused dynamic shared memory that caps the blocks per SM
     std::string err;
 };
 
@@ -138,6 +139,8 @@ int go2_create(const int32_t* model_iv, int n_iv, const double* model_fv, int n_
         const char* tp = getenv("GO2_B200_TPB");
         if (tp && atoi(tp) >= 32 && atoi(tp) <= GO2_TPB) tpb = atoi(tp) / 32 * 32;
         h->tpb = tpb;
+        const char* pad = getenv("GO2_B200_SMEM_PAD");
+        h->smem_pad = pad ? atoi(pad) : 0;
         h->nblocks = (B + tpb - 1) / tpb;
     }
     const EnvConfig& c = h->cfg;
@@ -158,7 +161,8 @@ int go2_create(const int32_t* model_iv, int n_iv, const double* model_fv, int n_
     cudaMemcpy(h->d_cfg, &h->cfg, sizeof(EnvConfig), cudaMemcpyHostToDevice);
     cudaMallocHost(&h->h_stats, sizeof(float) * STATS_LEN);
     cudaFuncSetAttribute(go2_step_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(GO2_WARPS * sizeof(WarpS)));
-    cudaFuncSetAttribute(go2_step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 0);  // all of L1 for thread-local data
+    if (h->smem_pad > 0) cudaFuncSetAttribute(go2_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, h->smem_pad);
+    else cudaFuncSetAttribute(go2_step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 0);  // all of L1 for thread-local data
     cudaFuncSetAttribute(go2_links_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(GO2_WARPS * sizeof(WarpS)));
     std::string init(h->arena_bytes, 0);
     init_arena(c, offs, &init[0]);
@@ -200,7 +204,7 @@ static int launch_step(go2_handle* h, const float* d_actions, const void* params
     if (h->layout == 1)
         go2_step_warp_kernel<<<(B + GO2_WARPS - 1) / GO2_WARPS, GO2_WARPS * 32, GO2_WARPS * sizeof(WarpS), s>>>(h->d_model, h->d_cfg, sp, h->bf, d_actions);
     else
-        go2_step_kernel<<<h->nblocks, h->tpb, 0, s>>>(h->d_model, h->d_cfg, sp, h->bf, d_actions);
+        go2_step_kernel<<<h->nblocks, h->tpb, h->smem_pad, s>>>(h->d_model, h->d_cfg, sp, h->bf, d_actions);
     h->launches += 1;
     return ck(h, cudaGetLastError(), "go2_step_kernel") ? 0 : -1;
 }

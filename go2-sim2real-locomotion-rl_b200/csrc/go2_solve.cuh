@@ -248,8 +248,11 @@ G2_HD void update_gradient(Phys& p, const float* Ma, const float* qfc, float* gr
 #if defined(GO2_LS_STATS) && !defined(__CUDA_ARCH__)
 // host-only debugging counters of the line search (tests/host_emul with -DGO2_LS_STATS)
 static long g_ls_calls = 0, g_lsA[64] = {0}, g_lsB[64] = {0}, g_lsend[4] = {0};
+static long g_nfl[64] = {0}, g_refac[3] = {0};
 #define G2_LS_COUNT(nA, nB, k) (g_ls_calls++, g_lsA[nA]++, g_lsB[nB]++, g_lsend[k]++)
+#define G2_NT_COUNT(nfl, over, fail) (g_nfl[(nfl) < 63 ? (nfl) : 63]++, g_refac[0] += (over), g_refac[1] += (fail), g_refac[2]++)
 #else
+#define G2_NT_COUNT(nfl, over, fail)
 #define G2_LS_COUNT(nA, nB, k)
 #endif
 constexpr int LS_REG = 16;  // rows of the line search kept in registers (4 contacts)
@@ -452,7 +455,9 @@ constexpr int MAX_RANK1 = 6;  // more flips than this in one Newton iteration ->
 
 // Block-wide "does any thread still iterate": keeps the warps of a block in the same Newton iteration so that
 // they share instruction fetches (the solver body is ~60 KB of straight-line code).  Host: a single env.
-#ifdef __CUDA_ARCH__
+#if defined(__CUDA_ARCH__) && defined(G2_WARP_ANY)
+#define G2_BLOCK_ANY(x) (__any_sync(0xffffffffu, (x)))
+#elif defined(__CUDA_ARCH__)
 #define G2_BLOCK_ANY(x) (__syncthreads_or((x) ? 1 : 0) != 0)
 #else
 #define G2_BLOCK_ANY(x) (x)
@@ -511,6 +516,7 @@ G2_HDN void solve_constraints(const Go2Model& m, Phys& p, bool valid) {
                     int c = (int)((flist >> (8 * k)) & 0xffull);
                     if (!hessian_rank1(p, c, p.act[c] ? 1.0f : -1.0f)) refactor = true;
                 }
+                if (!first) G2_NT_COUNT(nfl, nfl > MAX_RANK1 ? 1 : 0, (refactor && nfl <= MAX_RANK1) ? 1 : 0);
                 if (refactor) hessian_factor(p);
                 update_gradient(p, Ma, qfc, grad, Mgrad);
                 if (!first) {
