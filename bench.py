@@ -30,8 +30,8 @@ METRIC = "env-steps/sec (whole box) Go2 walk"
 UNIT = "env-steps/s"
 BYTES_PER_ENV_STEP = {"walk": 1952, "stair": 2272}  # algorithmic bytes per env-step
 # from profiles/r01_v3_step_kernel_ncu_summary.txt (ncu --set full, walk, 65,536 envs, one launch)
-NCU_DRAM_BYTES_PER_LAUNCH_65536 = 4.334124e9 + 2.599485e9
-NCU_WARP_INSTR_PER_ENV_STEP = 763299468 / 65536
+NCU_DRAM_BYTES_PER_LAUNCH_65536 = 4.279058e9 + 2.581176e9
+NCU_WARP_INSTR_PER_ENV_STEP = 773032407 / 65536
 
 
 def load_cfgs(name):
