@@ -154,10 +154,22 @@ G2_HD void update_constraint(Phys& p, const float* qacc, const float* Ma, float*
     p.cost = gauss + ccost;
 }
 
+// G2_H_REGS (experiment): the Cholesky factor lives in a function-local array of solve_constraints and the helpers are
+// force-inlined, so that with 255 registers the compiler can keep it in registers across the Newton loop.
+#ifdef G2_H_REGS
+#define G2_HSOLVE G2_HD
+#else
+#define G2_HSOLVE G2_HDN
+#endif
+
 // H = M + J^T D J over active rows, then dense Cholesky H = L L^T; assembled and factored in registers,
 // L written to p.H once.
-G2_HDN void hessian_factor(Phys& p) {
+G2_HSOLVE void hessian_factor(Phys& p, float* Hs) {
+#ifdef G2_H_REGS
+    float* H = Hs;
+#else
     float H[NTRI];
+#endif
     G2_UNROLL_H
     for (int k = 0; k < NTRI; ++k) H[k] = p.M[k];
     int n = p.n_rows;
@@ -191,12 +203,14 @@ G2_HDN void hessian_factor(Phys& p) {
             H[tri(j, i)] = (H[tri(j, i)] - dt) * inv;
         }
     }
+#ifndef G2_H_REGS
     G2_UNROLL_H
-    for (int k = 0; k < NTRI; ++k) p.H[k] = H[k];
+    for (int k = 0; k < NTRI; ++k) Hs[k] = H[k];
+#endif
 }
 
 // rank-1 up/down-date of the Cholesky factor for row c; returns false if a downdate degenerated
-G2_HDN bool hessian_rank1(Phys& p, int c, float sgn) {
+G2_HSOLVE bool hessian_rank1(Phys& p, float* Hs, int c, float sgn) {
     float vec[NV];
     float sd = sqrtf(p.Dd[c]);
     const float* Jr = p.J[c];
@@ -206,17 +220,17 @@ G2_HDN bool hessian_rank1(Phys& p, int c, float sgn) {
     G2_UNROLL
     for (int k = 0; k < NV; ++k) {
         if (ok && fabsf(vec[k]) > EPSF) {
-            float Lkk = p.H[tri(k, k)];
+            float Lkk = Hs[tri(k, k)];
             float t = Lkk * Lkk + sgn * vec[k] * vec[k];
             if (t < EPSF) {
                 ok = false;
             } else {
                 float r = sqrtf(t), cc = r / Lkk, ci = 1.0f / cc, s = vec[k] / Lkk;
-                p.H[tri(k, k)] = r;
+                Hs[tri(k, k)] = r;
                 G2_UNROLL
                 for (int i = k + 1; i < NV; ++i) {
-                    float h = (p.H[tri(i, k)] + s * vec[i] * sgn) * ci;
-                    p.H[tri(i, k)] = h;
+                    float h = (Hs[tri(i, k)] + s * vec[i] * sgn) * ci;
+                    Hs[tri(i, k)] = h;
                     vec[i] = vec[i] * cc - s * h;
                 }
             }
@@ -226,22 +240,22 @@ G2_HDN bool hessian_rank1(Phys& p, int c, float sgn) {
 }
 
 // grad = Ma - force - qfc;  Mgrad = H^-1 grad (two triangular solves with the Cholesky factor)
-G2_HD void update_gradient(Phys& p, const float* Ma, const float* qfc, float* grad, float* Mgrad) {
+G2_HD void update_gradient(Phys& p, const float* Hs, const float* Ma, const float* qfc, float* grad, float* Mgrad) {
     G2_UNROLL
     for (int d = 0; d < NV; ++d) grad[d] = Ma[d] - p.force[d] - qfc[d];
     G2_UNROLL
     for (int i = 0; i < NV; ++i) {
         float c = grad[i];
         G2_UNROLL
-        for (int j = 0; j < i; ++j) c -= p.H[tri(i, j)] * Mgrad[j];
-        Mgrad[i] = c / p.H[tri(i, i)];
+        for (int j = 0; j < i; ++j) c -= Hs[tri(i, j)] * Mgrad[j];
+        Mgrad[i] = c / Hs[tri(i, i)];
     }
     G2_UNROLL
     for (int i = NV - 1; i >= 0; --i) {
         float c = Mgrad[i];
         G2_UNROLL
-        for (int j = i + 1; j < NV; ++j) c -= p.H[tri(j, i)] * Mgrad[j];
-        Mgrad[i] = c / p.H[tri(i, i)];
+        for (int j = i + 1; j < NV; ++j) c -= Hs[tri(j, i)] * Mgrad[j];
+        Mgrad[i] = c / Hs[tri(i, i)];
     }
 }
 
@@ -470,6 +484,12 @@ constexpr int MAX_RANK1 = 6;  // more flips than this in one Newton iteration ->
 G2_HDN void solve_constraints(const Go2Model& m, Phys& p, bool valid) {
     const int n = valid ? p.n_rows : 0;
     float qacc[NV], Ma[NV], qfc[NV], grad[NV], Mgrad[NV], search[NV], mv[NV];
+#ifdef G2_H_REGS
+    float Hloc[NTRI];
+    float* Hs = Hloc;
+#else
+    float* Hs = p.H;
+#endif
     if (valid) {
         bool ws = n > 0 && p.warm;
         G2_UNROLL
@@ -514,11 +534,11 @@ G2_HDN void solve_constraints(const Go2Model& m, Phys& p, bool valid) {
                 bool refactor = first || nfl > MAX_RANK1;
                 for (int k = nfl - 1; k >= 0 && !refactor; --k) {
                     int c = (int)((flist >> (8 * k)) & 0xffull);
-                    if (!hessian_rank1(p, c, p.act[c] ? 1.0f : -1.0f)) refactor = true;
+                    if (!hessian_rank1(p, Hs, c, p.act[c] ? 1.0f : -1.0f)) refactor = true;
                 }
                 if (!first) G2_NT_COUNT(nfl, nfl > MAX_RANK1 ? 1 : 0, (refactor && nfl <= MAX_RANK1) ? 1 : 0);
-                if (refactor) hessian_factor(p);
-                update_gradient(p, Ma, qfc, grad, Mgrad);
+                if (refactor) hessian_factor(p, Hs);
+                update_gradient(p, Hs, Ma, qfc, grad, Mgrad);
                 if (!first) {
                     float gn = 0.0f;
                     G2_UNROLL
