@@ -244,10 +244,11 @@ def run_gpu(args):
         cores = os.cpu_count() or 1
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
-            n_envs = max(64, 32 * cores)
-            v, dt_cpu = cpu_oracle_throughput(n_envs, 150, cores)
+            n_envs = max(64, 64 * cores)
+            cpu_ticks = 2500  # ~10 s of host work on this pool's 16-core boxes
+            v, dt_cpu = cpu_oracle_throughput(n_envs, cpu_ticks, cores)
             cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
-                   "sample": f"oracle rigid step (2 substeps, torque control; env-level torch ops excluded), {n_envs} envs x 150 ticks, {dt_cpu:.1f} s"}
+                   "sample": f"oracle rigid step (2 substeps, torque control; env-level torch ops excluded), {n_envs} envs x {cpu_ticks} ticks, {dt_cpu:.1f} s"}
         stats = env.core.buf
         print(json.dumps({
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
