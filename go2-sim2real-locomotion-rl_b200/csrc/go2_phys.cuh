@@ -52,7 +52,7 @@ struct Phys {
     //   kin -> smooth : inertias about the root COM, cdof time derivatives (written by kinematics()/velocities()
     //                   at the end of a substep, read by the next smooth_dynamics()), LtDL factor of M
     //   collide       : geom AABBs
-    //   solve         : Cholesky factor of the Newton Hessian, constraint rows, Jacobian
+    //   solve         : constraint rows, then Cholesky factor of the Newton Hessian + Jacobian (dense or arrow form)
     union {
         struct {
             float cin_I[NLINK][6];  // symmetric inertia about root COM: xx,xy,xz,yy,yz,zz
@@ -65,12 +65,24 @@ struct Phys {
             v3 g_c[NGEOM], g_h[NGEOM];  // world AABB centre / half extents
         };
         struct {
-            float H[NTRI];
             uint8_t act[MAX_ROWS];
             float Dd[MAX_ROWS], aref[MAX_ROWS], Jaref[MAX_ROWS], jv[MAX_ROWS], efc[MAX_ROWS];
-            float J[MAX_ROWS][NV];
+            union {
+                struct {  // dense mode (some contact couples two different legs)
+                    float H[NTRI];
+                    float J[MAX_ROWS][NV];
+                };
+                struct {  // arrow mode: every row touches the base dofs + ONE leg; dofs ordered legs first, base last
+                    float Hbb[21];      // Cholesky factor, base-base block (packed lower triangle)
+                    float Hl[4][6];     // per leg: 3x3 diagonal block (packed lower triangle; hip, thigh, calf)
+                    float Hbl[4][18];   // per leg: base rows x leg columns [r*3 + a]
+                    uint8_t rleg[MAX_ROWS];
+                    float Js[MAX_ROWS][9];  // row Jacobian: 6 base dofs, then hip/thigh/calf of leg rleg
+                };
+            };
         };
     };
+    int arrow;  // 1 = arrow mode (see above)
     v3 cforce[NLINK];  // net contact force per link
     int err;
     int n_newton;

@@ -14,7 +14,12 @@
 //   * the line search is a two-loop state machine with ONE evaluation site per loop;
 //   * active-set flips are collected in a packed list while the constraint state is updated, and the rank-1
 //     updates run "k-th flip of every lane" together instead of row by row;
-//   * M keeps only its tree-structured nonzeros in products.
+//   * M keeps only its tree-structured nonzeros in products;
+//   * ARROW mode (every row touches the 6 base dofs + ONE leg - true unless two different legs touch each other):
+//     rows keep 9 Jacobian entries, and the Newton Hessian is factored with the legs eliminated first, which
+//     makes the factor an arrowhead (four 3x3 leg blocks, four 6x3 base-leg blocks, one 6x6 base block = 117 of
+//     171 entries); a rank-1 update touches 45 entries instead of 171.  Same minimiser, other rounding than
+//     the reference's dense factor in dof order (constraint/solver.py:1088-1143), which the DENSE mode keeps.
 #pragma once
 #include "go2_collide.cuh"
 
@@ -49,7 +54,54 @@ G2_HD void mul_M(const float* M, const float* x, float* y) {
     }
 }
 
-G2_HDN void assemble_constraints(const Go2Model& m, Phys& p) {
+// ---- row access, dense (J[c][18]) or arrow (Js[c][9] + leg id) ---------------------------------------
+G2_HD float sel4(int k, float a, float b, float c, float d) {
+    float lo = (k & 1) ? b : a, hi = (k & 1) ? d : c;
+    return (k & 2) ? hi : lo;
+}
+// J[c] . x   (arrow: same summation order as the dense row with its zeros skipped -> bit-identical)
+template <bool AR>
+G2_HD float row_dot(const Phys& p, int c, const float* x, float s0) {
+    float s = s0;
+    if (AR) {
+        const float* Jr = p.Js[c];
+        int leg = p.rleg[c];
+        G2_UNROLL
+        for (int d = 0; d < 6; ++d) s += Jr[d] * x[d];
+        s += Jr[6] * sel4(leg, x[6], x[7], x[8], x[9]);
+        s += Jr[7] * sel4(leg, x[10], x[11], x[12], x[13]);
+        s += Jr[8] * sel4(leg, x[14], x[15], x[16], x[17]);
+    } else {
+        const float* Jr = p.J[c];
+        G2_UNROLL
+        for (int d = 0; d < NV; ++d) s += Jr[d] * x[d];
+    }
+    return s;
+}
+// y += J[c]^T f
+template <bool AR>
+G2_HD void row_axpy(const Phys& p, int c, float f, float* y) {
+    if (AR) {
+        const float* Jr = p.Js[c];
+        int leg = p.rleg[c];
+        G2_UNROLL
+        for (int d = 0; d < 6; ++d) y[d] += Jr[d] * f;
+        G2_UNROLL
+        for (int a = 0; a < 3; ++a) {
+            float t = Jr[6 + a] * f;
+            G2_UNROLL
+            for (int l = 0; l < 4; ++l) y[6 + 4 * a + l] += (leg == l) ? t : 0.0f;
+        }
+    } else {
+        const float* Jr = p.J[c];
+        G2_UNROLL
+        for (int d = 0; d < NV; ++d) y[d] += Jr[d] * f;
+    }
+}
+
+template <bool AR>
+G2_HDN void assemble_rows(const Go2Model& m, Phys& p) {
+    constexpr int NC = AR ? 9 : NV;
     int r = 0;
     for (int ic = 0; ic < p.n_contacts; ++ic) {
         const Contact& c = p.con[ic];
@@ -64,23 +116,27 @@ G2_HDN void assemble_constraints(const Go2Model& m, Phys& p) {
             v3 d = (k < 2 ? d1 : d2) * (float)(2 * (k % 2) - 1);
             n[k] = d * c.mu - c.normal;
             jqv[k] = 0.0f;
-            float* Jr = p.J[r + k];
+            float* Jr = AR ? p.Js[r + k] : p.J[r + k];
             G2_UNROLL
-            for (int i = 0; i < NV; ++i) Jr[i] = 0.0f;
+            for (int i = 0; i < NC; ++i) Jr[i] = 0.0f;
         }
+        int leg = 0;
         for (int side = 0; side < 2; ++side) {
             float sgn = side == 0 ? -1.0f : 1.0f;
             int l = side == 0 ? c.la : c.lb;
+            if (l > 0) leg = (l - 1) & 3;
             while (l >= 0) {
                 int d0 = l == 0 ? 0 : 5 + l, nd = l == 0 ? 6 : 1;
                 for (int i = d0 + nd - 1; i >= d0; --i) {
                     v3 vel = p.cdof_v[i] - cross(tp, p.cdof_a[i]);
                     float qv = p.qvel[i];
+                    int col = AR ? (i < 6 ? i : 6 + ((i - 6) >> 2)) : i;
                     G2_UNROLL
                     for (int k = 0; k < 4; ++k) {
                         float j = sgn * dot(vel, n[k]);
                         jqv[k] += j * qv;
-                        p.J[r + k][i] += j;
+                        if (AR) p.Js[r + k][col] += j;
+                        else p.J[r + k][col] += j;
                     }
                 }
                 l = l == 0 ? -1 : m.parent[l];
@@ -95,6 +151,7 @@ G2_HDN void assemble_constraints(const Go2Model& m, Phys& p) {
             diag = fmaxf(diag, EPSF);
             p.aref[r + k] = ar;
             p.Dd[r + k] = 1.0f / diag;
+            if (AR) p.rleg[r + k] = (uint8_t)leg;
         }
         r += 4;
     }
@@ -107,10 +164,11 @@ G2_HDN void assemble_constraints(const Go2Model& m, Phys& p) {
             float imp, ar;
             imp_aref(m.sol_params, pd, j * p.qvel[d], pd, imp, ar);
             float diag = fmaxf(m.invweight_dof[d] * (1.0f - imp) / imp, EPSF);
-            float* Jr = p.J[r];
+            float* Jr = AR ? p.Js[r] : p.J[r];
             G2_UNROLL
-            for (int i = 0; i < NV; ++i) Jr[i] = 0.0f;
-            Jr[d] = j;
+            for (int i = 0; i < NC; ++i) Jr[i] = 0.0f;
+            Jr[AR ? 6 + ((d - 6) >> 2) : d] = j;
+            if (AR) p.rleg[r] = (uint8_t)((d - 6) & 3);
             p.aref[r] = ar;
             p.Dd[r] = 1.0f / diag;
             ++r;
@@ -119,8 +177,30 @@ G2_HDN void assemble_constraints(const Go2Model& m, Phys& p) {
     p.n_rows = r;
 }
 
+#if defined(GO2_LS_STATS) && !defined(__CUDA_ARCH__)
+static long g_pairkind[4] = {0};  // contacts: ground-robot, base-leg, same leg, two legs
+#endif
+// Picks the row format (arrow unless two different legs touch each other) and builds the rows.
+G2_HD void assemble_constraints(const Go2Model& m, Phys& p) {
+    int arrow = 1;
+    for (int ic = 0; ic < p.n_contacts; ++ic) {
+        int a = p.con[ic].la, b = p.con[ic].lb;
+        if (a > 0 && b > 0 && ((a - 1) & 3) != ((b - 1) & 3)) arrow = 0;
+#if defined(GO2_LS_STATS) && !defined(__CUDA_ARCH__)
+        g_pairkind[(a < 0 || b < 0) ? 0 : (a == 0 || b == 0) ? 1 : (((a - 1) & 3) == ((b - 1) & 3)) ? 2 : 3]++;
+#endif
+    }
+#ifdef G2_FORCE_DENSE
+    arrow = 0;
+#endif
+    p.arrow = arrow;
+    if (arrow) assemble_rows<true>(m, p);
+    else assemble_rows<false>(m, p);
+}
+
 // Active set, constraint forces, qfc = J^T f, cost.  Rows whose active flag changed are appended to a packed
 // list (8 bits per row index, newest in the low byte); `nfl` counts all of them.
+template <bool AR>
 G2_HD void update_constraint(Phys& p, const float* qacc, const float* Ma, float* qfc, unsigned long long& flist, int& nfl) {
     p.prev_cost = p.cost;
     G2_UNROLL
@@ -137,9 +217,7 @@ G2_HD void update_constraint(Phys& p, const float* qacc, const float* Ma, float*
         float f = a ? -ja * D : 0.0f;
         p.efc[c] = f;
         if (a) {
-            const float* Jr = p.J[c];
-            G2_UNROLL
-            for (int d = 0; d < NV; ++d) qfc[d] += Jr[d] * f;
+            row_axpy<AR>(p, c, f, qfc);
             ccost += 0.5f * ja * ja * D;
         }
         if (a != old) {
@@ -259,6 +337,226 @@ G2_HD void update_gradient(Phys& p, const float* Hs, const float* Ma, const floa
     }
 }
 
+// ---- arrow mode: H = M + J^T D J with the dofs ordered (leg 0, leg 1, leg 2, leg 3, base) ------------------
+// Leg l owns dofs 6+l (hip), 10+l (thigh), 14+l (calf).  H has no leg-leg coupling between different legs
+// (M: tree structure; rows: one leg each), so L = [diag(La_l), 0; Lb_l, Lc].
+G2_HD void arrow_acc_row(const float* jr, float D, float* C, float* tA, float* tB) {
+    G2_UNROLL
+    for (int i = 0; i < 6; ++i) {
+        float sb = jr[i] * D;
+        G2_UNROLL
+        for (int j = 0; j <= i; ++j) C[tri(i, j)] += jr[j] * sb;
+        G2_UNROLL
+        for (int a = 0; a < 3; ++a) tB[i * 3 + a] += jr[6 + a] * sb;
+    }
+    G2_UNROLL
+    for (int a = 0; a < 3; ++a) {
+        float sa = jr[6 + a] * D;
+        G2_UNROLL
+        for (int b = 0; b <= a; ++b) tA[tri(a, b)] += jr[6 + b] * sa;
+    }
+}
+
+G2_HDN void hessian_factor_a(Phys& p) {
+    float C[21];
+    G2_UNROLL
+    for (int k = 0; k < 21; ++k) C[k] = p.M[k];  // base block: dofs 0..5 = first 21 packed entries
+    G2_UNROLL
+    for (int l = 0; l < 4; ++l) {
+        G2_UNROLL
+        for (int a = 0; a < 3; ++a) {
+            G2_UNROLL
+            for (int b = 0; b <= a; ++b) p.Hl[l][tri(a, b)] = p.M[tri(6 + 4 * a + l, 6 + 4 * b + l)];
+            G2_UNROLL
+            for (int r = 0; r < 6; ++r) p.Hbl[l][r * 3 + a] = p.M[tri(6 + 4 * a + l, r)];
+        }
+    }
+    // rows come in groups sharing a leg: 4 per contact, then single joint-limit rows
+    const int n = p.n_rows, ncr = 4 * p.n_contacts;
+    for (int c0 = 0; c0 < n; c0 += (c0 < ncr ? 4 : 1)) {
+        float tA[6], tB[18];
+        G2_UNROLL
+        for (int k = 0; k < 6; ++k) tA[k] = 0.0f;
+        G2_UNROLL
+        for (int k = 0; k < 18; ++k) tB[k] = 0.0f;
+        const int leg = p.rleg[c0];
+        const bool grp = c0 < ncr;
+        bool any = false;
+        G2_UNROLL
+        for (int k = 0; k < 4; ++k) {
+            if ((k == 0 || grp) && p.act[c0 + k]) {
+                float jr[9];
+                G2_UNROLL
+                for (int i = 0; i < 9; ++i) jr[i] = p.Js[c0 + k][i];
+                arrow_acc_row(jr, p.Dd[c0 + k], C, tA, tB);
+                any = true;
+            }
+        }
+        if (any) {
+            float* A = p.Hl[leg];
+            float* Bm = p.Hbl[leg];
+            G2_UNROLL
+            for (int k = 0; k < 6; ++k) A[k] += tA[k];
+            G2_UNROLL
+            for (int k = 0; k < 18; ++k) Bm[k] += tB[k];
+        }
+    }
+    G2_UNROLL
+    for (int l = 0; l < 4; ++l) {
+        float* A = p.Hl[l];
+        float* Bm = p.Hbl[l];
+        float l00 = sqrtf(fmaxf(A[0], EPSF)), i00 = 1.0f / l00;
+        float l10 = A[1] * i00, l20 = A[3] * i00;
+        float l11 = sqrtf(fmaxf(A[2] - l10 * l10, EPSF)), i11 = 1.0f / l11;
+        float l21 = (A[4] - l20 * l10) * i11;
+        float l22 = sqrtf(fmaxf(A[5] - l20 * l20 - l21 * l21, EPSF)), i22 = 1.0f / l22;
+        A[0] = l00; A[1] = l10; A[2] = l11; A[3] = l20; A[4] = l21; A[5] = l22;
+        float X[6][3];
+        G2_UNROLL
+        for (int r = 0; r < 6; ++r) {
+            float x0 = Bm[r * 3 + 0] * i00;
+            float x1 = (Bm[r * 3 + 1] - x0 * l10) * i11;
+            float x2 = (Bm[r * 3 + 2] - x0 * l20 - x1 * l21) * i22;
+            Bm[r * 3 + 0] = x0; Bm[r * 3 + 1] = x1; Bm[r * 3 + 2] = x2;
+            X[r][0] = x0; X[r][1] = x1; X[r][2] = x2;
+        }
+        G2_UNROLL
+        for (int i = 0; i < 6; ++i) {
+            G2_UNROLL
+            for (int j = 0; j <= i; ++j) C[tri(i, j)] -= X[i][0] * X[j][0] + X[i][1] * X[j][1] + X[i][2] * X[j][2];
+        }
+    }
+    G2_UNROLL
+    for (int i = 0; i < 6; ++i) {
+        float t = C[tri(i, i)];
+        G2_UNROLL
+        for (int j = 0; j < i; ++j) t -= C[tri(i, j)] * C[tri(i, j)];
+        float lii = sqrtf(fmaxf(t, EPSF));
+        C[tri(i, i)] = lii;
+        float inv = 1.0f / lii;
+        G2_UNROLL
+        for (int j = i + 1; j < 6; ++j) {
+            float dt = 0.0f;
+            G2_UNROLL
+            for (int k = 0; k < i; ++k) dt += C[tri(j, k)] * C[tri(i, k)];
+            C[tri(j, i)] = (C[tri(j, i)] - dt) * inv;
+        }
+    }
+    G2_UNROLL
+    for (int k = 0; k < 21; ++k) p.Hbb[k] = C[k];
+}
+
+// rank-1 up/down-date of the arrow factor for row c: the leg's 3 columns, then the 6 base columns
+G2_HDN bool hessian_rank1_a(Phys& p, int c, float sgn) {
+    float vl[3], vb[6];
+    const float sd = sqrtf(p.Dd[c]);
+    const float* Jr = p.Js[c];
+    G2_UNROLL
+    for (int d = 0; d < 6; ++d) vb[d] = Jr[d] * sd;
+    G2_UNROLL
+    for (int a = 0; a < 3; ++a) vl[a] = Jr[6 + a] * sd;
+    float* A = p.Hl[p.rleg[c]];
+    float* Bm = p.Hbl[p.rleg[c]];
+    bool ok = true;
+    G2_UNROLL
+    for (int k = 0; k < 3; ++k) {
+        if (ok && fabsf(vl[k]) > EPSF) {
+            float Lkk = A[tri(k, k)];
+            float t = Lkk * Lkk + sgn * vl[k] * vl[k];
+            if (t < EPSF) {
+                ok = false;
+            } else {
+                float r = sqrtf(t), cc = r / Lkk, ci = 1.0f / cc, s = vl[k] / Lkk;
+                A[tri(k, k)] = r;
+                G2_UNROLL
+                for (int i = k + 1; i < 3; ++i) {
+                    float h = (A[tri(i, k)] + s * vl[i] * sgn) * ci;
+                    A[tri(i, k)] = h;
+                    vl[i] = vl[i] * cc - s * h;
+                }
+                G2_UNROLL
+                for (int i = 0; i < 6; ++i) {
+                    float h = (Bm[i * 3 + k] + s * vb[i] * sgn) * ci;
+                    Bm[i * 3 + k] = h;
+                    vb[i] = vb[i] * cc - s * h;
+                }
+            }
+        }
+    }
+    G2_UNROLL
+    for (int k = 0; k < 6; ++k) {
+        if (ok && fabsf(vb[k]) > EPSF) {
+            float Lkk = p.Hbb[tri(k, k)];
+            float t = Lkk * Lkk + sgn * vb[k] * vb[k];
+            if (t < EPSF) {
+                ok = false;
+            } else {
+                float r = sqrtf(t), cc = r / Lkk, ci = 1.0f / cc, s = vb[k] / Lkk;
+                p.Hbb[tri(k, k)] = r;
+                G2_UNROLL
+                for (int i = k + 1; i < 6; ++i) {
+                    float h = (p.Hbb[tri(i, k)] + s * vb[i] * sgn) * ci;
+                    p.Hbb[tri(i, k)] = h;
+                    vb[i] = vb[i] * cc - s * h;
+                }
+            }
+        }
+    }
+    return ok;
+}
+
+// grad = Ma - force - qfc;  Mgrad = H^-1 grad through the arrow factor
+G2_HD void update_gradient_a(Phys& p, const float* Ma, const float* qfc, float* grad, float* Mgrad) {
+    G2_UNROLL
+    for (int d = 0; d < NV; ++d) grad[d] = Ma[d] - p.force[d] - qfc[d];
+    float yb[6];
+    G2_UNROLL
+    for (int r = 0; r < 6; ++r) yb[r] = grad[r];
+    G2_UNROLL
+    for (int l = 0; l < 4; ++l) {
+        const float* A = p.Hl[l];
+        const float* Bm = p.Hbl[l];
+        float y0 = grad[6 + l] / A[0];
+        float y1 = (grad[10 + l] - A[1] * y0) / A[2];
+        float y2 = (grad[14 + l] - A[3] * y0 - A[4] * y1) / A[5];
+        Mgrad[6 + l] = y0; Mgrad[10 + l] = y1; Mgrad[14 + l] = y2;
+        G2_UNROLL
+        for (int r = 0; r < 6; ++r) yb[r] -= Bm[r * 3 + 0] * y0 + Bm[r * 3 + 1] * y1 + Bm[r * 3 + 2] * y2;
+    }
+    G2_UNROLL
+    for (int i = 0; i < 6; ++i) {
+        float c = yb[i];
+        G2_UNROLL
+        for (int j = 0; j < i; ++j) c -= p.Hbb[tri(i, j)] * yb[j];
+        yb[i] = c / p.Hbb[tri(i, i)];
+    }
+    G2_UNROLL
+    for (int i = 5; i >= 0; --i) {
+        float c = yb[i];
+        G2_UNROLL
+        for (int j = i + 1; j < 6; ++j) c -= p.Hbb[tri(j, i)] * yb[j];
+        yb[i] = c / p.Hbb[tri(i, i)];
+    }
+    G2_UNROLL
+    for (int r = 0; r < 6; ++r) Mgrad[r] = yb[r];
+    G2_UNROLL
+    for (int l = 0; l < 4; ++l) {
+        const float* A = p.Hl[l];
+        const float* Bm = p.Hbl[l];
+        float z0 = Mgrad[6 + l], z1 = Mgrad[10 + l], z2 = Mgrad[14 + l];
+        G2_UNROLL
+        for (int r = 0; r < 6; ++r) {
+            z0 -= Bm[r * 3 + 0] * yb[r];
+            z1 -= Bm[r * 3 + 1] * yb[r];
+            z2 -= Bm[r * 3 + 2] * yb[r];
+        }
+        float x2 = z2 / A[5];
+        float x1 = (z1 - A[4] * x2) / A[2];
+        float x0 = (z0 - A[1] * x1 - A[3] * x2) / A[0];
+        Mgrad[6 + l] = x0; Mgrad[10 + l] = x1; Mgrad[14 + l] = x2;
+    }
+}
+
 #if defined(GO2_LS_STATS) && !defined(__CUDA_ARCH__)
 // host-only debugging counters of the line search (tests/host_emul with -DGO2_LS_STATS)
 static long g_ls_calls = 0, g_lsA[64] = {0}, g_lsB[64] = {0}, g_lsend[4] = {0};
@@ -296,6 +594,7 @@ G2_HD int bracket_update(LsPt& pt, const LsPt* cand, float& next_alpha) {
 
 // Exact line search along `search` (constraint/solver.py:2246-2417).  Fills mv = M search and p.jv = J search;
 // returns the step length.  Same decisions as the reference, arranged as two loops with one evaluation site each.
+template <bool AR>
 G2_HD float linesearch(const Go2Model& m, Phys& p, const float* search, const float* Ma, float* mv) {
     float sn = 0.0f;
     G2_UNROLL
@@ -312,22 +611,14 @@ G2_HD float linesearch(const Go2Model& m, Phys& p, const float* search, const fl
     for (int c = 0; c < LS_REG; ++c) {
         float s = 0.0f, ja = 0.0f, D = 0.0f;
         if (c < n) {
-            const float* Jr = p.J[c];
-            G2_UNROLL
-            for (int d = 0; d < NV; ++d) s += Jr[d] * search[d];
+            s = row_dot<AR>(p, c, search, 0.0f);
             p.jv[c] = s;
             ja = p.Jaref[c];
             D = p.Dd[c];
         }
         rja[c] = ja; rjv[c] = s; rD[c] = D;
     }
-    for (int c = LS_REG; c < n; ++c) {
-        const float* Jr = p.J[c];
-        float s = 0.0f;
-        G2_UNROLL
-        for (int d = 0; d < NV; ++d) s += Jr[d] * search[d];
-        p.jv[c] = s;
-    }
+    for (int c = LS_REG; c < n; ++c) p.jv[c] = row_dot<AR>(p, c, search, 0.0f);
     float g1 = 0.0f, g2 = 0.0f;
     G2_UNROLL
     for (int d = 0; d < NV; ++d) {
@@ -481,7 +772,8 @@ constexpr int MAX_RANK1 = 6;  // more flips than this in one Newton iteration ->
 // Called by EVERY thread of the block (`valid` = the thread owns an env) because the iteration loop contains
 // block barriers.  Trip 0 of the loop is the initial evaluation (active set, Hessian factorisation, gradient);
 // trips >= 1 are the Newton iterations of constraint/solver.py:2862-2938, each helper having ONE call site.
-G2_HDN void solve_constraints(const Go2Model& m, Phys& p, bool valid) {
+template <bool AR>
+G2_HDN void solve_constraints_t(const Go2Model& m, Phys& p, bool valid) {
     const int n = valid ? p.n_rows : 0;
     float qacc[NV], Ma[NV], qfc[NV], grad[NV], Mgrad[NV], search[NV], mv[NV];
 #ifdef G2_H_REGS
@@ -496,11 +788,7 @@ G2_HDN void solve_constraints(const Go2Model& m, Phys& p, bool valid) {
         for (int d = 0; d < NV; ++d) qacc[d] = ws ? p.qacc_ws[d] : p.acc_smooth[d];
         if (n > 0) mul_M(p.M, qacc, Ma);
         for (int c = 0; c < n; ++c) {
-            const float* Jr = p.J[c];
-            float s = -p.aref[c];
-            G2_UNROLL
-            for (int d = 0; d < NV; ++d) s += Jr[d] * qacc[d];
-            p.Jaref[c] = s;
+            p.Jaref[c] = row_dot<AR>(p, c, qacc, -p.aref[c]);
             p.act[c] = 0;
         }
         p.cost = 0.0f;
@@ -514,7 +802,7 @@ G2_HDN void solve_constraints(const Go2Model& m, Phys& p, bool valid) {
             bool first = it == 0;
             if (!first) {
                 n_newton++;
-                float alpha = linesearch(m, p, search, Ma, mv);
+                float alpha = linesearch<AR>(m, p, search, Ma, mv);
                 if (fabsf(alpha) < EPSF) {
                     active = false;
                 } else {
@@ -529,16 +817,21 @@ G2_HDN void solve_constraints(const Go2Model& m, Phys& p, bool valid) {
             if (active) {
                 unsigned long long flist;
                 int nfl;
-                update_constraint(p, qacc, Ma, qfc, flist, nfl);
+                update_constraint<AR>(p, qacc, Ma, qfc, flist, nfl);
                 // active-set changes: k-th flip of every lane together, oldest first (row order, like the reference)
                 bool refactor = first || nfl > MAX_RANK1;
                 for (int k = nfl - 1; k >= 0 && !refactor; --k) {
                     int c = (int)((flist >> (8 * k)) & 0xffull);
-                    if (!hessian_rank1(p, Hs, c, p.act[c] ? 1.0f : -1.0f)) refactor = true;
+                    float sg = p.act[c] ? 1.0f : -1.0f;
+                    if (!(AR ? hessian_rank1_a(p, c, sg) : hessian_rank1(p, Hs, c, sg))) refactor = true;
                 }
                 if (!first) G2_NT_COUNT(nfl, nfl > MAX_RANK1 ? 1 : 0, (refactor && nfl <= MAX_RANK1) ? 1 : 0);
-                if (refactor) hessian_factor(p, Hs);
-                update_gradient(p, Hs, Ma, qfc, grad, Mgrad);
+                if (refactor) {
+                    if (AR) hessian_factor_a(p);
+                    else hessian_factor(p, Hs);
+                }
+                if (AR) update_gradient_a(p, Ma, qfc, grad, Mgrad);
+                else update_gradient(p, Hs, Ma, qfc, grad, Mgrad);
                 if (!first) {
                     float gn = 0.0f;
                     G2_UNROLL
@@ -577,6 +870,13 @@ G2_HDN void solve_constraints(const Go2Model& m, Phys& p, bool valid) {
         if (c.la >= 0) p.cforce[c.la] = p.cforce[c.la] - f;
         if (c.lb >= 0) p.cforce[c.lb] = p.cforce[c.lb] + f;
     }
+}
+
+// Every thread of the block calls this (see solve_constraints_t); envs in dense mode are rare, so the second loop
+// normally ends at its first block vote.
+G2_HD void solve_constraints(const Go2Model& m, Phys& p, bool valid) {
+    solve_constraints_t<true>(m, p, valid && p.arrow != 0);
+    solve_constraints_t<false>(m, p, valid && p.arrow == 0);
 }
 
 }  // namespace go2

@@ -166,6 +166,7 @@ void go2_ls_stats(long* out) {  // [calls, A[64], B[64], end[4]]
     for (int i = 0; i < 4; ++i) out[129 + i] = g_lsend[i];
     for (int i = 0; i < 64; ++i) out[133 + i] = g_nfl[i];
     for (int i = 0; i < 3; ++i) out[197 + i] = g_refac[i];
+    for (int i = 0; i < 4; ++i) out[200 + i] = g_pairkind[i];
 }
 #endif
 }
