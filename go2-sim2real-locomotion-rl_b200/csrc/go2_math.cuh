@@ -6,6 +6,28 @@
 
 namespace go2 {
 
+#if defined(__CUDACC__) && defined(G2_ROLLED)
+#define G2_UNROLL _Pragma("unroll 1")
+#elif defined(__CUDACC__)
+#define G2_UNROLL _Pragma("unroll")
+#else
+#define G2_UNROLL
+#endif
+#if defined(__CUDACC__) && defined(G2_ROLLED) && !defined(G2_ROLLED_ALL)
+#define G2_UNROLL_H _Pragma("unroll")
+#else
+#define G2_UNROLL_H G2_UNROLL
+#endif
+
+G2_HD int tri(int i, int j) { return (i * (i + 1)) / 2 + j; }  // packed lower triangle, j <= i
+// M[i][j] is structurally nonzero iff one of the dofs is a base dof or both hinges belong to the same leg
+G2_HD bool m_nz(int i, int j) { return i < 6 || j < 6 || (((i - 6) & 3) == ((j - 6) & 3)); }
+G2_HD int trs(int i, int j) { return i >= j ? tri(i, j) : tri(j, i); }
+// Fixed Go2 tree: links 1-4 hips (parent = base), 5-8 thighs, 9-12 calves (parent = l - 4); hinge of link l = dof 5 + l.
+// Checked against the loaded model at handle creation (go2_model_host.hpp).
+G2_HD int par_link(int l) { return l == 0 ? -1 : (l <= 4 ? 0 : l - 4); }
+
+
 struct v3 {
     float x, y, z;
 };
@@ -119,7 +141,6 @@ G2_HD void imp_aref(const float* p, float neg_pen, float vel, float pos, float& 
     aref = -b * vel - k * imp * pos;
 }
 
-G2_HD int tri(int i, int j) { return (i * (i + 1)) / 2 + j; }  // packed lower triangle, j <= i
 
 // ---- counter-based RNG: Philox4x32-10 ---------------------------------------------------------------
 struct u4 {

@@ -17,6 +17,7 @@ inline bool unpack_model(Go2Model& m, const int32_t* iv, int n_iv, const double*
         n_dofs[l] = iv[k++];
         k++;  // q_start (implied: hinge l <-> dof 5+l, qpos 6+l)
         if (l > 0 && (dof_start[l] != 5 + l || n_dofs[l] != 1)) return false;
+        if (m.parent[l] != par_link(l)) return false;  // the kernels unroll the fixed Go2 tree (go2_math.cuh)
     }
     for (int g = 0; g < NGEOM; ++g) {
         int lg = iv[k++];

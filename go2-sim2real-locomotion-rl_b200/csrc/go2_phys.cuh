@@ -97,8 +97,9 @@ G2_HDN void kinematics(const Go2Model& m, const float* mass_shift, const float* 
     p.lquat[0] = qnormalize(mk4(p.qpos[3], p.qpos[4], p.qpos[5], p.qpos[6]));
     v3 anchor[NLINK], axis_w[NLINK];
     anchor[0] = p.lpos[0];
+    G2_UNROLL
     for (int l = 1; l < NLINK; ++l) {
-        int par = m.parent[l];
+        const int par = par_link(l);
         v3 pos = p.lpos[par] + qrot(ld3(m.l_pos[l]), p.lquat[par]);
         q4 quat = qcompose(ld4(m.l_quat[l]), p.lquat[par]);
         v3 ax = ld3(m.axis[l]);
@@ -112,6 +113,7 @@ G2_HDN void kinematics(const Go2Model& m, const float* mass_shift, const float* 
     v3 comw[NLINK];
     v3 acc = mk3(0, 0, 0);
     float msum = 0.0f;
+    G2_UNROLL
     for (int l = 0; l < NLINK; ++l) {
         float mass = m.mass[l] + mass_shift[l];
         v3 ip = ld3(m.inertial_pos[l]);
@@ -122,6 +124,7 @@ G2_HDN void kinematics(const Go2Model& m, const float* mass_shift, const float* 
         p.cin_m[l] = mass;
     }
     p.root_com = acc * (1.0f / msum);
+    G2_UNROLL
     for (int l = 0; l < NLINK; ++l) {
         v3 t = comw[l] - p.root_com;
         float mass = p.cin_m[l];
@@ -154,6 +157,7 @@ G2_HDN void kinematics(const Go2Model& m, const float* mass_shift, const float* 
             p.cdof_v[3 + i] = cross(c, off);
         }
     }
+    G2_UNROLL
     for (int l = 1; l < NLINK; ++l) {
         v3 off = p.root_com - anchor[l];
         p.cdof_a[5 + l] = axis_w[l];
@@ -180,8 +184,9 @@ G2_HDN void velocities(const Go2Model& m, Phys& p) {
     }
     p.cd_v[0] = cv;
     p.cd_a[0] = ca;
+    G2_UNROLL
     for (int l = 1; l < NLINK; ++l) {
-        int par = m.parent[l], d = 5 + l;
+        const int par = par_link(l), d = 5 + l;
         v3 pv = p.cd_v[par], pa = p.cd_a[par];
         p.cdofd_a[d] = cross(pa, p.cdof_a[d]);
         p.cdofd_v[d] = cross(pa, p.cdof_v[d]) + cross(pv, p.cdof_a[d]);
@@ -202,70 +207,79 @@ G2_HD void inertia_mul(const float* I, v3 h, float mass, v3 vel, v3 ang, v3& fa,
 // Mass matrix by composite rigid bodies; only the tree-structured nonzeros are computed
 // (base block, each leg's 3x3 block and its coupling with the base).  Packed lower triangle.
 G2_HDN void mass_matrix(const Go2Model& m, Phys& p, float diag_extra_hinge) {
+    (void)m;
     float cI[NLINK][6];
     v3 ch[NLINK];
     float cm[NLINK];
+    G2_UNROLL
     for (int l = 0; l < NLINK; ++l) {
+        G2_UNROLL
         for (int k = 0; k < 6; ++k) cI[l][k] = p.cin_I[l][k];
         ch[l] = p.cin_h[l];
         cm[l] = p.cin_m[l];
     }
+    G2_UNROLL
     for (int l = NLINK - 1; l >= 1; --l) {
-        int par = m.parent[l];
+        const int par = par_link(l);
+        G2_UNROLL
         for (int k = 0; k < 6; ++k) cI[par][k] += cI[l][k];
         ch[par] = ch[par] + ch[l];
         cm[par] += cm[l];
     }
-    for (int k = 0; k < NTRI; ++k) p.M[k] = 0.0f;
-    // row dof i (link li): M[i][j] = f_i . cdof_j for j in dofs of li's ancestors (and li itself, j <= i)
+    // row dof i (link li): M[i][j] = f_i . cdof_j for the dofs j <= i on li's chain (= structural nonzeros)
+    G2_UNROLL
     for (int i = 0; i < NV; ++i) {
-        int li = i < 6 ? 0 : i - 5;
+        const int li = i < 6 ? 0 : i - 5;
         v3 fa, fv;
         inertia_mul(cI[li], ch[li], cm[li], p.cdof_v[i], p.cdof_a[i], fa, fv);
-        if (i < 6) {
-            for (int j = 0; j <= i; ++j) p.M[tri(i, j)] = dot(fa, p.cdof_a[j]) + dot(fv, p.cdof_v[j]);
-        } else {
-            int l = li;
-            while (l >= 0) {
-                if (l == 0) {
-                    for (int j = 0; j < 6; ++j) p.M[tri(i, j)] = dot(fa, p.cdof_a[j]) + dot(fv, p.cdof_v[j]);
-                } else {
-                    int j = 5 + l;
-                    p.M[tri(i, j)] = dot(fa, p.cdof_a[j]) + dot(fv, p.cdof_v[j]);
-                }
-                l = m.parent[l];
-            }
+        G2_UNROLL
+        for (int j = 0; j <= i; ++j) {
+            if (m_nz(i, j)) p.M[tri(i, j)] = dot(fa, p.cdof_a[j]) + dot(fv, p.cdof_v[j]);
+            else p.M[tri(i, j)] = 0.0f;
         }
     }
+    G2_UNROLL
     for (int d = 6; d < NV; ++d) p.M[tri(d, d)] += m.armature[d] + diag_extra_hinge;
 }
 
-// In-place LtDL of M (MuJoCo order: last dof first), exploiting nothing but the packed layout.
+// In-place LtDL of M (MuJoCo order: last dof first) over the structural nonzeros (the factor of a tree has no fill).
 G2_HDN void factor_mass(Phys& p) {
+    G2_UNROLL
     for (int k = 0; k < NTRI; ++k) p.L[k] = p.M[k];
+    G2_UNROLL
     for (int i = NV - 1; i >= 0; --i) {
         float dinv = 1.0f / p.L[tri(i, i)];
         p.Dinv[i] = dinv;
+        G2_UNROLL
         for (int j = i - 1; j >= 0; --j) {
-            float a = p.L[tri(i, j)] * dinv;
-            if (a != 0.0f) {
-                for (int k = 0; k <= j; ++k) p.L[tri(j, k)] -= a * p.L[tri(i, k)];
+            if (m_nz(i, j)) {
+                float a = p.L[tri(i, j)] * dinv;
+                G2_UNROLL
+                for (int k = 0; k <= j; ++k)
+                    if (m_nz(i, k)) p.L[tri(j, k)] -= a * p.L[tri(i, k)];
+                p.L[tri(i, j)] = a;
             }
-            p.L[tri(i, j)] = a;
         }
         p.L[tri(i, i)] = 1.0f;
     }
 }
 G2_HDN void solve_mass(const Phys& p, const float* vec, float* out) {
+    G2_UNROLL
     for (int i = NV - 1; i >= 0; --i) {
         float c = vec[i];
-        for (int j = i + 1; j < NV; ++j) c -= p.L[tri(j, i)] * out[j];
+        G2_UNROLL
+        for (int j = i + 1; j < NV; ++j)
+            if (m_nz(i, j)) c -= p.L[tri(j, i)] * out[j];
         out[i] = c;
     }
+    G2_UNROLL
     for (int i = 0; i < NV; ++i) out[i] *= p.Dinv[i];
+    G2_UNROLL
     for (int i = 0; i < NV; ++i) {
         float c = out[i];
-        for (int j = 0; j < i; ++j) c -= p.L[tri(i, j)] * out[j];
+        G2_UNROLL
+        for (int j = 0; j < i; ++j)
+            if (m_nz(i, j)) c -= p.L[tri(i, j)] * out[j];
         out[i] = c;
     }
 }
@@ -292,13 +306,15 @@ G2_HDN void smooth_dynamics(const Go2Model& m, Phys& p) {
         dda[0] = a;
         ddv[0] = v;
     }
+    G2_UNROLL
     for (int l = 1; l < NLINK; ++l) {
-        int par = m.parent[l], d = 5 + l;
+        const int par = par_link(l), d = 5 + l;
         ddv[l] = ddv[par] + p.cdofd_v[d] * p.qvel[d];
         dda[l] = dda[par] + p.cdofd_a[d] * p.qvel[d];
     }
     // per-link inertial + gyroscopic force, external push, then child -> parent accumulation
     v3 fa[NLINK], fv[NLINK];
+    G2_UNROLL
     for (int l = 0; l < NLINK; ++l) {
         v3 a1, v1, a2, v2;
         inertia_mul(p.cin_I[l], p.cin_h[l], p.cin_m[l], ddv[l], dda[l], a1, v1);
@@ -310,13 +326,15 @@ G2_HDN void smooth_dynamics(const Go2Model& m, Phys& p) {
             fa[l] = fa[l] - p.ext_t;
         }
     }
+    G2_UNROLL
     for (int l = NLINK - 1; l >= 1; --l) {
-        int par = m.parent[l];
+        const int par = par_link(l);
         fv[par] = fv[par] + fv[l];
         fa[par] = fa[par] + fa[l];
     }
+    G2_UNROLL
     for (int d = 0; d < NV; ++d) {
-        int l = d < 6 ? 0 : d - 5;
+        const int l = d < 6 ? 0 : d - 5;
         float bias = dot(p.cdof_a[d], fa[l]) + dot(p.cdof_v[d], fv[l]);
         float ap = d < 6 ? 0.0f : applied_force(m, p, d);
         p.force[d] = ap - bias;

@@ -25,23 +25,6 @@
 
 namespace go2 {
 
-#if defined(__CUDACC__) && defined(G2_ROLLED)
-#define G2_UNROLL _Pragma("unroll 1")
-#elif defined(__CUDACC__)
-#define G2_UNROLL _Pragma("unroll")
-#else
-#define G2_UNROLL
-#endif
-#if defined(__CUDACC__) && defined(G2_ROLLED) && !defined(G2_ROLLED_ALL)
-#define G2_UNROLL_H _Pragma("unroll")
-#else
-#define G2_UNROLL_H G2_UNROLL
-#endif
-
-// M[i][j] is structurally nonzero iff one of the dofs is a base dof or both hinges belong to the same leg
-G2_HD bool m_nz(int i, int j) { return i < 6 || j < 6 || (((i - 6) & 3) == ((j - 6) & 3)); }
-G2_HD int trs(int i, int j) { return i >= j ? tri(i, j) : tri(j, i); }
-
 // y = M x over the structural nonzeros (packed lower triangle)
 G2_HD void mul_M(const float* M, const float* x, float* y) {
     G2_UNROLL
@@ -139,7 +122,7 @@ G2_HDN void assemble_rows(const Go2Model& m, Phys& p) {
                         else p.J[r + k][col] += j;
                     }
                 }
-                l = l == 0 ? -1 : m.parent[l];
+                l = par_link(l);
             }
         }
         G2_UNROLL
@@ -177,6 +160,88 @@ G2_HDN void assemble_rows(const Go2Model& m, Phys& p) {
     p.n_rows = r;
 }
 
+// Arrow-mode rows with the 4 pyramid rows of a contact built in registers (static columns: 6 base dofs, then the hip /
+// thigh / calf of the contact's leg) and stored once.  Same operation order as assemble_rows (link -> root, side a
+// then side b), so the two produce identical numbers.
+G2_HDN void assemble_rows_a(const Go2Model& m, Phys& p) {
+    int r = 0;
+    for (int ic = 0; ic < p.n_contacts; ++ic) {
+        const Contact& c = p.con[ic];
+        v3 d1, d2;
+        orthobasis(c.normal, d1, d2);
+        float invw = (c.la >= 0 ? m.invweight_link[c.la] : 0.0f) + (c.lb >= 0 ? m.invweight_link[c.lb] : 0.0f);
+        v3 tp = c.pos - p.root_com;
+        v3 n[4];
+        float jqv[4], jr[4][9];
+        G2_UNROLL
+        for (int k = 0; k < 4; ++k) {
+            v3 d = (k < 2 ? d1 : d2) * (float)(2 * (k % 2) - 1);
+            n[k] = d * c.mu - c.normal;
+            jqv[k] = 0.0f;
+            G2_UNROLL
+            for (int i = 0; i < 9; ++i) jr[k][i] = 0.0f;
+        }
+        int leg = 0;
+        G2_UNROLL
+        for (int side = 0; side < 2; ++side) {
+            const float sgn = side == 0 ? -1.0f : 1.0f;
+            const int l = side == 0 ? c.la : c.lb;
+            if (l >= 0) {
+                const int depth = l == 0 ? 0 : 1 + ((l - 1) >> 2);  // hinges between the link and the base
+                if (l > 0) leg = (l - 1) & 3;
+                G2_UNROLL
+                for (int col = 8; col >= 0; --col) {
+                    if (col < 6 || col - 6 < depth) {
+                        const int i = col < 6 ? col : 6 + 4 * (col - 6) + ((l - 1) & 3);
+                        v3 vel = p.cdof_v[i] - cross(tp, p.cdof_a[i]);
+                        float qv = p.qvel[i];
+                        G2_UNROLL
+                        for (int k = 0; k < 4; ++k) {
+                            float j = sgn * dot(vel, n[k]);
+                            jqv[k] += j * qv;
+                            jr[k][col] += j;
+                        }
+                    }
+                }
+            }
+        }
+        G2_UNROLL
+        for (int k = 0; k < 4; ++k) {
+            float imp, ar;
+            imp_aref(m.sol_params, -c.pen, jqv[k], -c.pen, imp, ar);
+            float diag = invw + c.mu * c.mu * invw;
+            diag *= 2.0f * c.mu * c.mu * (1.0f - imp) / imp;
+            diag = fmaxf(diag, EPSF);
+            p.aref[r + k] = ar;
+            p.Dd[r + k] = 1.0f / diag;
+            p.rleg[r + k] = (uint8_t)leg;
+            G2_UNROLL
+            for (int i = 0; i < 9; ++i) p.Js[r + k][i] = jr[k][i];
+        }
+        r += 4;
+    }
+    for (int d = 6; d < NV; ++d) {
+        float q = p.qpos[d + 1];
+        float dmin = q - m.limit_lo[d], dmax = m.limit_hi[d] - q;
+        float pd = fminf(dmin, dmax);
+        if (pd < 0.0f) {
+            float j = dmin < dmax ? 1.0f : -1.0f;
+            float imp, ar;
+            imp_aref(m.sol_params, pd, j * p.qvel[d], pd, imp, ar);
+            float diag = fmaxf(m.invweight_dof[d] * (1.0f - imp) / imp, EPSF);
+            float* Jr = p.Js[r];
+            G2_UNROLL
+            for (int i = 0; i < 9; ++i) Jr[i] = 0.0f;
+            Jr[6 + ((d - 6) >> 2)] = j;
+            p.rleg[r] = (uint8_t)((d - 6) & 3);
+            p.aref[r] = ar;
+            p.Dd[r] = 1.0f / diag;
+            ++r;
+        }
+    }
+    p.n_rows = r;
+}
+
 #if defined(GO2_LS_STATS) && !defined(__CUDA_ARCH__)
 static long g_pairkind[4] = {0};  // contacts: ground-robot, base-leg, same leg, two legs
 #endif
@@ -194,7 +259,7 @@ G2_HD void assemble_constraints(const Go2Model& m, Phys& p) {
     arrow = 0;
 #endif
     p.arrow = arrow;
-    if (arrow) assemble_rows<true>(m, p);
+    if (arrow) assemble_rows_a(m, p);
     else assemble_rows<false>(m, p);
 }
 
@@ -446,17 +511,24 @@ G2_HDN void hessian_factor_a(Phys& p) {
     for (int k = 0; k < 21; ++k) p.Hbb[k] = C[k];
 }
 
-// rank-1 up/down-date of the arrow factor for row c: the leg's 3 columns, then the 6 base columns
+// rank-1 up/down-date of the arrow factor for row c: the leg's 3 columns, then the 6 base columns.  The 45 entries it
+// touches are staged in registers first (one burst of independent loads instead of a load per dependent step).
 G2_HDN bool hessian_rank1_a(Phys& p, int c, float sgn) {
-    float vl[3], vb[6];
+    float vl[3], vb[6], A[6], Bm[18], Cb[21];
     const float sd = sqrtf(p.Dd[c]);
     const float* Jr = p.Js[c];
+    float* Ap = p.Hl[p.rleg[c]];
+    float* Bp = p.Hbl[p.rleg[c]];
     G2_UNROLL
     for (int d = 0; d < 6; ++d) vb[d] = Jr[d] * sd;
     G2_UNROLL
     for (int a = 0; a < 3; ++a) vl[a] = Jr[6 + a] * sd;
-    float* A = p.Hl[p.rleg[c]];
-    float* Bm = p.Hbl[p.rleg[c]];
+    G2_UNROLL
+    for (int k = 0; k < 6; ++k) A[k] = Ap[k];
+    G2_UNROLL
+    for (int k = 0; k < 18; ++k) Bm[k] = Bp[k];
+    G2_UNROLL
+    for (int k = 0; k < 21; ++k) Cb[k] = p.Hbb[k];
     bool ok = true;
     G2_UNROLL
     for (int k = 0; k < 3; ++k) {
@@ -486,22 +558,29 @@ G2_HDN bool hessian_rank1_a(Phys& p, int c, float sgn) {
     G2_UNROLL
     for (int k = 0; k < 6; ++k) {
         if (ok && fabsf(vb[k]) > EPSF) {
-            float Lkk = p.Hbb[tri(k, k)];
+            float Lkk = Cb[tri(k, k)];
             float t = Lkk * Lkk + sgn * vb[k] * vb[k];
             if (t < EPSF) {
                 ok = false;
             } else {
                 float r = sqrtf(t), cc = r / Lkk, ci = 1.0f / cc, s = vb[k] / Lkk;
-                p.Hbb[tri(k, k)] = r;
+                Cb[tri(k, k)] = r;
                 G2_UNROLL
                 for (int i = k + 1; i < 6; ++i) {
-                    float h = (p.Hbb[tri(i, k)] + s * vb[i] * sgn) * ci;
-                    p.Hbb[tri(i, k)] = h;
+                    float h = (Cb[tri(i, k)] + s * vb[i] * sgn) * ci;
+                    Cb[tri(i, k)] = h;
                     vb[i] = vb[i] * cc - s * h;
                 }
             }
         }
     }
+    // a degenerate downdate is followed by a refactorisation from scratch, so partial results may be stored too
+    G2_UNROLL
+    for (int k = 0; k < 6; ++k) Ap[k] = A[k];
+    G2_UNROLL
+    for (int k = 0; k < 18; ++k) Bp[k] = Bm[k];
+    G2_UNROLL
+    for (int k = 0; k < 21; ++k) p.Hbb[k] = Cb[k];
     return ok;
 }
 
@@ -567,6 +646,20 @@ static long g_nfl[64] = {0}, g_refac[3] = {0};
 #define G2_NT_COUNT(nfl, over, fail)
 #define G2_LS_COUNT(nA, nB, k)
 #endif
+// The line search stops on |derivative| < gtol with gtol at fp32 rounding level (LS_TOL * SOLVER_TOL).  That test is
+// met through the exact cancellation of SEPARATELY rounded products; with fused multiply-adds the residual never
+// cancels and 13 % of the searches run to the 50-evaluation cap (measured, host build with -mfma: 0 % without).  The
+// evaluations therefore use explicitly unfused arithmetic on the device, like the CPU builds (-ffp-contract=off).
+#if defined(__CUDA_ARCH__)
+G2_HD float mul_nf(float a, float b) { return __fmul_rn(a, b); }
+G2_HD float add_nf(float a, float b) { return __fadd_rn(a, b); }
+#elif defined(G2_HOST_FMA_TEST)
+G2_HD float mul_nf(float a, float b) { volatile float r = a * b; return r; }
+G2_HD float add_nf(float a, float b) { volatile float r = a + b; return r; }
+#else
+G2_HD float mul_nf(float a, float b) { return a * b; }
+G2_HD float add_nf(float a, float b) { return a + b; }
+#endif
 constexpr int LS_REG = 16;  // rows of the line search kept in registers (4 contacts)
 struct LsPt {
     float alpha, cost, d0, d1;
@@ -574,9 +667,9 @@ struct LsPt {
 G2_HD LsPt ls_point(float alpha, float q0, float q1, float q2) {
     LsPt r;
     r.alpha = alpha;
-    r.cost = alpha * alpha * q2 + alpha * q1 + q0;
-    r.d0 = 2.0f * alpha * q2 + q1;
-    r.d1 = 2.0f * q2;
+    r.cost = add_nf(add_nf(mul_nf(mul_nf(alpha, alpha), q2), mul_nf(alpha, q1)), q0);
+    r.d0 = add_nf(mul_nf(mul_nf(2.0f, alpha), q2), q1);
+    r.d1 = mul_nf(2.0f, q2);
     if (r.d1 <= 0.0f) r.d1 = EPSF;
     return r;
 }
@@ -588,7 +681,7 @@ G2_HD int bracket_update(LsPt& pt, const LsPt* cand, float& next_alpha) {
         else if (pt.d0 > 0.0f && cand[i].d0 > 0.0f && pt.d0 > cand[i].d0) { pt = cand[i]; flag = 2; }
     }
     next_alpha = pt.alpha;
-    if (flag > 0) next_alpha = pt.alpha - pt.d0 / pt.d1;
+    if (flag > 0) next_alpha = add_nf(pt.alpha, -(pt.d0 / pt.d1));
     return flag;
 }
 
@@ -639,18 +732,18 @@ G2_HD float linesearch(const Go2Model& m, Phys& p, const float* search, const fl
         G2_UNROLL
         for (int c = 0; c < LS_REG; ++c) {
             float ja = rja[c], jv = rjv[c], D = rD[c];
-            if (ja + alpha * jv < 0.0f) {
-                q0 += D * (0.5f * ja * ja);
-                q1 += D * (jv * ja);
-                q2 += D * (0.5f * jv * jv);
+            if (add_nf(ja, mul_nf(alpha, jv)) < 0.0f) {
+                q0 = add_nf(q0, mul_nf(D, mul_nf(mul_nf(0.5f, ja), ja)));
+                q1 = add_nf(q1, mul_nf(D, mul_nf(jv, ja)));
+                q2 = add_nf(q2, mul_nf(D, mul_nf(mul_nf(0.5f, jv), jv)));
             }
         }
         for (int c = LS_REG; c < n; ++c) {
             float ja = p.Jaref[c], jv = p.jv[c], D = p.Dd[c];
-            if (ja + alpha * jv < 0.0f) {
-                q0 += D * (0.5f * ja * ja);
-                q1 += D * (jv * ja);
-                q2 += D * (0.5f * jv * jv);
+            if (add_nf(ja, mul_nf(alpha, jv)) < 0.0f) {
+                q0 = add_nf(q0, mul_nf(D, mul_nf(mul_nf(0.5f, ja), ja)));
+                q1 = add_nf(q1, mul_nf(D, mul_nf(jv, ja)));
+                q2 = add_nf(q2, mul_nf(D, mul_nf(mul_nf(0.5f, jv), jv)));
             }
         }
         LsPt e = ls_point(alpha, q0, q1, q2);
@@ -658,7 +751,7 @@ G2_HD float linesearch(const Go2Model& m, Phys& p, const float* search, const fl
         bool more;
         if (stage == 0) {
             p0 = e;
-            alpha = p0.alpha - p0.d0 / p0.d1;
+            alpha = add_nf(p0.alpha, -(p0.d0 / p0.d1));
             stage = 1;
             more = true;
         } else {
@@ -681,7 +774,7 @@ G2_HD float linesearch(const Go2Model& m, Phys& p, const float* search, const fl
                 if (p1.d0 * dir <= -gtol && ls_it < LS_ITERS) {
                     p2 = p1;
                     p2upd = true;
-                    alpha = p1.alpha - p1.d0 / p1.d1;
+                    alpha = add_nf(p1.alpha, -(p1.d0 / p1.d1));
                     more = true;
                 } else {
                     more = false;
@@ -695,7 +788,7 @@ G2_HD float linesearch(const Go2Model& m, Phys& p, const float* search, const fl
         finished = true;
     }
     // ---- loop B: three-point refinement of the bracket [p1, p2]
-    float a[3] = {p1.alpha - p1.d0 / p1.d1, p1.alpha, (p1.alpha + p2.alpha) * 0.5f};
+    float a[3] = {add_nf(p1.alpha, -(p1.d0 / p1.d1)), p1.alpha, mul_nf(add_nf(p1.alpha, p2.alpha), 0.5f)};
     int nA = ls_it, nB = 0, endk = finished ? 0 : 3;
     (void)nA; (void)nB; (void)endk;
     while (!finished && ls_it < LS_ITERS) {
@@ -706,18 +799,18 @@ G2_HD float linesearch(const Go2Model& m, Phys& p, const float* search, const fl
         G2_UNROLL
         for (int c = 0; c < LS_REG; ++c) {
             float ja = rja[c], jv = rjv[c], D = rD[c];
-            float f0 = D * (0.5f * ja * ja), f1 = D * (jv * ja), f2 = D * (0.5f * jv * jv);
+            float f0 = mul_nf(D, mul_nf(mul_nf(0.5f, ja), ja)), f1 = mul_nf(D, mul_nf(jv, ja)), f2 = mul_nf(D, mul_nf(mul_nf(0.5f, jv), jv));
             G2_UNROLL
             for (int k = 0; k < 3; ++k) {
-                if (ja + a[k] * jv < 0.0f) { t[k][0] += f0; t[k][1] += f1; t[k][2] += f2; }
+                if (add_nf(ja, mul_nf(a[k], jv)) < 0.0f) { t[k][0] = add_nf(t[k][0], f0); t[k][1] = add_nf(t[k][1], f1); t[k][2] = add_nf(t[k][2], f2); }
             }
         }
         for (int c = LS_REG; c < n; ++c) {
             float ja = p.Jaref[c], jv = p.jv[c], D = p.Dd[c];
-            float f0 = D * (0.5f * ja * ja), f1 = D * (jv * ja), f2 = D * (0.5f * jv * jv);
+            float f0 = mul_nf(D, mul_nf(mul_nf(0.5f, ja), ja)), f1 = mul_nf(D, mul_nf(jv, ja)), f2 = mul_nf(D, mul_nf(mul_nf(0.5f, jv), jv));
             G2_UNROLL
             for (int k = 0; k < 3; ++k) {
-                if (ja + a[k] * jv < 0.0f) { t[k][0] += f0; t[k][1] += f1; t[k][2] += f2; }
+                if (add_nf(ja, mul_nf(a[k], jv)) < 0.0f) { t[k][0] = add_nf(t[k][0], f0); t[k][1] = add_nf(t[k][1], f1); t[k][2] = add_nf(t[k][2], f2); }
             }
         }
         LsPt cand[3];
@@ -743,7 +836,7 @@ G2_HD float linesearch(const Go2Model& m, Phys& p, const float* search, const fl
                 finished = true;
                 endk = 2;
             } else {
-                a[0] = n1; a[1] = n2; a[2] = (p1.alpha + p2.alpha) * 0.5f;
+                a[0] = n1; a[1] = n2; a[2] = mul_nf(add_nf(p1.alpha, p2.alpha), 0.5f);
             }
         }
     }

@@ -77,3 +77,10 @@ for fn, ex in sfunc.most_common(40):
 print("\ntop lines by stall samples")
 for (f, l), s in sline.most_common(40):
     print(f"{f}:{l:5d} instr% {100*byline[(f,l)]/max(tot,1):6.2f} stall% {100*s/max(stot,1):6.2f}")
+if os.environ.get("HOTSPOTS_BY_INSTR"):
+    tl = collections.Counter()
+    for r in rows[hdr_i + 1:]:
+        pass
+    print("\ntop lines by issued warp instructions")
+    for (f, l), ex in byline.most_common(int(os.environ["HOTSPOTS_BY_INSTR"])):
+        print(f"{f}:{l:5d} instr% {100*ex/max(tot,1):6.2f} stall% {100*sline[(f,l)]/max(stot,1):6.2f}")
