@@ -28,10 +28,11 @@ for p in (ROOT, PKG):
 
 METRIC = "env-steps/sec (whole box) Go2 walk"
 UNIT = "env-steps/s"
-BYTES_PER_ENV_STEP = {"walk": 1952, "stair": 2272}  # algorithmic bytes per env-step
-# from profiles/r01_v3_step_kernel_ncu_summary.txt (ncu --set full, walk, 65,536 envs, one launch)
-NCU_DRAM_BYTES_PER_LAUNCH_65536 = 4.279058e9 + 2.581176e9
-NCU_WARP_INSTR_PER_ENV_STEP = 773032407 / 65536
+BYTES_PER_ENV_STEP = {"walk": 1952, "stair": 2272, "crouch": 948, "jump": 948}  # algorithmic bytes per env-step
+# from profiles/r01_v4_step_kernel_ncu_summary.txt (ncu --set full, walk, 65,536 envs, one launch)
+NCU_PROFILE = "profiles/r01_v4_step_kernel_ncu_summary.txt"
+NCU_DRAM_BYTES_PER_LAUNCH_65536 = 2.516372e9 + 2.011230e9
+NCU_WARP_INSTR_PER_ENV_STEP = 495122640 / 65536
 
 
 def load_cfgs(name):
@@ -83,12 +84,25 @@ class ClockSampler:
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(sm)}
 
 
-def cpu_oracle_throughput(n_envs, n_steps, threads):
+_CPU_KIND = None
+
+
+def _best_cpu_kind(threads):
+    """The -O3 -march=native oracle build with or without FMA contraction, whichever is faster on this host."""
+    global _CPU_KIND
+    if _CPU_KIND is None:
+        n = max(64, 8 * threads)
+        rates = {k: max(cpu_oracle_throughput(n, 40, threads, kind=k)[0] for _ in range(2)) for k in ("f32_fast", "f32_fast_nc")}
+        _CPU_KIND = max(rates, key=rates.get)
+    return _CPU_KIND
+
+
+def cpu_oracle_throughput(n_envs, n_steps, threads, kind=None):
     """Oracle rigid step (2 substeps, torque control held) on `threads` host threads; env-steps/s."""
     import numpy as np
     from oracle.rigid import OracleRigid
 
-    o = OracleRigid(n_envs, kind="f32_fast", n_threads=threads)
+    o = OracleRigid(n_envs, kind=kind or _best_cpu_kind(threads), n_threads=threads)
     mdi = [7, 11, 15, 6, 10, 14, 9, 13, 17, 8, 12, 16]
     q0 = np.array([0, 0.8, -1.5, 0, 0.8, -1.5, 0, 1.0, -1.5, 0, 1.0, -1.5])
     o.set_dofs_position(np.tile(q0, (n_envs, 1)), mdi)
@@ -137,7 +151,7 @@ def run_gpu(args):
     import numpy as np
     import torch
     import torch.distributed as dist
-    from go2_b200.envs import Go2EnvStair, Go2EnvWalk
+    from go2_b200.envs import Go2EnvBaseFlavour, Go2EnvStair, Go2EnvWalk
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -147,7 +161,7 @@ def run_gpu(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     B = args.envs
-    env_cls = Go2EnvStair if args.workload == "stair" else Go2EnvWalk
+    env_cls = {"walk": Go2EnvWalk, "stair": Go2EnvStair}.get(args.workload, Go2EnvBaseFlavour)
     env = env_cls(B, *load_cfgs(args.workload), device=dev, seed=1, env_offset=rank * B, total_envs=world * B)
     env.reset()
     g = torch.Generator(device=dev).manual_seed(1234 + rank)
@@ -254,16 +268,16 @@ def run_gpu(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": f"Go2 {args.workload} (go2_train_{args.workload} cfg, full DR + curriculum), {B} envs/GPU, random actions on device",
-                       "envs_per_gpu": B, "l2": "per-tick state (2 KB/env) + thread-local working set of the resident threads (~460 MB at 65,536 envs) exceed the 126 MB L2: inputs larger than L2, no flush needed",
+            "config": {"workload": f"Go2 {args.workload} (go2_train_{args.workload} cfg{', full DR + curriculum' if args.workload in ('walk', 'stair') else ''}), {B} envs/GPU, random actions on device",
+                       "envs_per_gpu": B, "l2": "per-tick state (2 KB/env) + thread-local working set of the resident threads (~300 MB at 65,536 envs) exceed the 126 MB L2: inputs larger than L2, no flush needed",
                        "stats_sync_interval": env.stats_sync_interval},
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": B * env.num_actions * 4, "d2h_bytes_per_step": B * (env.num_obs * 4 + 4 + 1),
                     "ms_per_step": ms_e2e / args.steps},
             "with_policy": {"value": world * B * args.steps / (ms_pol * 1e-3), "unit": UNIT, "ms_per_step": ms_pol / args.steps,
-                            "policy": "49-512-256-128-16 ELU actor, fixed-seed random init (shipped model_188000.pt blob absent), torch fp32, inside the timed loop"},
+                            "policy": f"{env.num_obs}-512-256-128-{env.num_actions} ELU actor, fixed-seed random init (shipped model_188000.pt blob absent), torch fp32, inside the timed loop"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": NCU_DRAM_BYTES_PER_LAUNCH_65536 if walk64k else None,
-                         "traffic_unit": "B per launch (dram read+write, ncu --set full, profiles/r01_v3_step_kernel_ncu_summary.txt)",
+                         "traffic_unit": f"B per launch (dram read+write, ncu --set full, {NCU_PROFILE})",
                          "algorithmic_bytes_per_launch": B * bpe, "issue_frac": issue_frac,
                          "peak_source": which, "kernel": "go2_step_kernel", "kernel_ms_avg": kern_avg, "kernel_ms_median": kern_ms[len(kern_ms) // 2],
                          "bytes_per_env_step": bpe,
@@ -284,7 +298,8 @@ def main():
     ap.add_argument("--envs", type=int, default=65536, help="envs per GPU")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="walk", choices=["walk", "stair"], help="walk = headline metric; stair = BASELINE configs[2]")
+    ap.add_argument("--workload", default="walk", choices=["walk", "stair", "crouch", "jump"],
+                    help="walk = headline metric; stair = BASELINE configs[2]; crouch / jump = configs[3] (base env)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -20,7 +20,8 @@ if _PKG not in sys.path:
 from go2_b200.model import flatten_model, load_model  # noqa: E402
 
 NL, NV, NQ = 14, 18, 19
-_LIBS = {"f32": "libgo2oracle_f32.so", "f64": "libgo2oracle_f64.so", "f32_fast": "libgo2oracle_f32_fast.so"}
+_LIBS = {"f32": "libgo2oracle_f32.so", "f64": "libgo2oracle_f64.so", "f32_fast": "libgo2oracle_f32_fast.so",
+         "f32_fast_nc": "libgo2oracle_f32_fast_nc.so"}
 
 
 def build(force=False):

@@ -84,3 +84,25 @@ if os.environ.get("HOTSPOTS_BY_INSTR"):
     print("\ntop lines by issued warp instructions")
     for (f, l), ex in byline.most_common(int(os.environ["HOTSPOTS_BY_INSTR"])):
         print(f"{f}:{l:5d} instr% {100*ex/max(tot,1):6.2f} stall% {100*sline[(f,l)]/max(stot,1):6.2f}")
+if os.environ.get("HOTSPOTS_MEM"):
+    isrc = hdr.index("Source")
+    ld = collections.Counter(); st = collections.Counter(); gl = collections.Counter()
+    for r in rows[hdr_i + 1:]:
+        if len(r) <= max(ia, ie, isrc):
+            continue
+        try:
+            a = int(r[ia], 16) if not r[ia].isdigit() else int(r[ia])
+        except ValueError:
+            continue
+        f, l = addr2line.get(a - base, ("?", 0))
+        fn = func_of(f, l)
+        ex = int(r[ie] or 0)
+        op = r[isrc]
+        w = 4 if ".128" in op else 2 if ".64" in op else 1
+        if "LDL" in op: ld[fn] += ex * w
+        elif "STL" in op: st[fn] += ex * w
+        elif "LDG" in op or "STG" in op or " LD." in op or " ST." in op: gl[fn] += ex * w
+    tl, ts, tg = sum(ld.values()), sum(st.values()), sum(gl.values())
+    print(f"\nlocal-memory warp-level word accesses: loads {tl} stores {ts}; global {tg}")
+    for fn, n in (ld + st).most_common(int(os.environ["HOTSPOTS_MEM"])):
+        print(f"{fn:32s} ld% {100*ld[fn]/max(tl,1):6.2f} st% {100*st[fn]/max(ts,1):6.2f} global% {100*gl[fn]/max(tg,1):6.2f}")
