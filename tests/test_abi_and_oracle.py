@@ -20,6 +20,11 @@ def test_header_symbols_exported():
         pytest.skip("libgo2_b200.so not built (run __graft_entry__.build())")
     lib = abi.Go2Lib(abi.CUDA_LIB_PATH)  # dlopen + symbol + struct-size checks; no CUDA call is made
     assert lib.stats_len == 36
+    hdr2 = open(os.path.join(ROOT, "include/go2_policy.h")).read()
+    declared2 = set(re.findall(r"\b(go2_[a-z_]+)\s*\(", hdr2))
+    assert declared2 == set(abi._POLICY_EXPORTS), declared2 ^ set(abi._POLICY_EXPORTS)
+    for name in abi._POLICY_EXPORTS:
+        assert hasattr(lib.lib, name), name
 
 
 def test_missing_library_fails_loudly(tmp_path):
