@@ -48,6 +48,14 @@ def peaks():
         return 6650.0, "fallback"
 
 
+def tensor_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["bf16_tflops"])
+    except Exception:
+        return 2250.0  # nominal dense bf16 (B200_PROFILING.md fallback)
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled during the timed region (B200_PROFILING.md)."""
 
@@ -241,10 +249,62 @@ def run_gpu(args):
         barrier()
     ms_pol = p0.elapsed_time(p1)
 
-    t = torch.tensor([ms_total, ms_e2e, kern_avg, ms_pol], device=dev, dtype=torch.float64)
+    # ---- the same closed loop on the fused tcgen05 actor (go2_b200.rollout, csrc/go2_policy.cu), the kernel timed alone
+    # against torch fp32 on the same weights, and 24-step rollout collection (actor sample + log-prob, critic, env step,
+    # storage rows, GAE) as rsl-rl's OnPolicyRunner does it (BASELINE.json configs[4])
+    from go2_b200.rollout import FusedActorCritic, RolloutCollector
+    n_priv = env.get_privileged_observations().shape[1]
+    cdims = [n_priv, 512, 256, 128, 1]
+    clayers = []
+    for i in range(4):
+        clayers.append(torch.nn.Linear(cdims[i], cdims[i + 1]))
+        if i < 3:
+            clayers.append(torch.nn.ELU())
+    critic = torch.nn.Sequential(*clayers).to(dev).eval()
+    ac = FusedActorCritic(actor, critic, 0.5 * torch.ones(env.num_actions), dev, seed=188000, env_offset=rank * B)
+    act_buf = torch.empty((B, env.num_actions), device=dev)
+    obs = env.obs_buf
+    for i in range(max(3, args.warmup // 2)):
+        obs, _, _, _ = env.step(ac.act_inference(obs, act_buf))
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    f0.record()
+    for i in range(args.steps):
+        obs, _, _, _ = env.step(ac.act_inference(obs, act_buf))
+    f1.record()
+    barrier()
+    ms_fused = f0.elapsed_time(f1)
+    x = torch.randn(B, env.num_obs, device=dev)
+    def _time(fn, n=20):
+        for _ in range(3):
+            fn()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        a.record()
+        for _ in range(n):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / n
+    with torch.no_grad():
+        ms_k_fused = _time(lambda: ac.act_inference(x, act_buf))
+        ms_k_torch = _time(lambda: actor(x))
+    col = RolloutCollector(env, ac, num_steps=24)
+    o_, c_ = col.collect()
+    r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n_roll = max(1, args.steps // 24)
+    barrier()
+    r0.record()
+    for _ in range(n_roll):
+        o_, c_ = col.collect(o_, c_)
+    r1.record()
+    barrier()
+    ms_roll = r0.elapsed_time(r1)
+
+    t = torch.tensor([ms_total, ms_e2e, kern_avg, ms_pol, ms_fused, ms_roll, ms_k_fused, ms_k_torch], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total, ms_e2e, kern_avg, ms_pol = [float(x) for x in t.tolist()]
+    ms_total, ms_e2e, kern_avg, ms_pol, ms_fused, ms_roll, ms_k_fused, ms_k_torch = [float(x) for x in t.tolist()]
     if rank == 0:
         value = world * B * args.steps / (ms_total * 1e-3)
         e2e = world * B * args.steps / (ms_e2e * 1e-3)
@@ -275,6 +335,13 @@ def run_gpu(args):
                     "ms_per_step": ms_e2e / args.steps},
             "with_policy": {"value": world * B * args.steps / (ms_pol * 1e-3), "unit": UNIT, "ms_per_step": ms_pol / args.steps,
                             "policy": f"{env.num_obs}-512-256-128-{env.num_actions} ELU actor, fixed-seed random init (shipped model_188000.pt blob absent), torch fp32, inside the timed loop"},
+            "with_policy_fused": {"value": world * B * args.steps / (ms_fused * 1e-3), "unit": UNIT, "ms_per_step": ms_fused / args.steps,
+                                  "policy": "same actor on the fused tcgen05 kernel (bf16 operands, fp32 accumulate), one launch per tick"},
+            "rollout": {"value": world * B * 24 * n_roll / (ms_roll * 1e-3), "unit": UNIT, "ms_per_step": ms_roll / (24 * n_roll), "rollouts": n_roll,
+                        "what": "24-step collection: fused actor (sample + log-prob) + fused critic + env step + rsl-rl storage rows + GAE"},
+            "policy_kernel": {"kernel": "go2_mlp_kernel", "bound": "tensor", "ms_fused": ms_k_fused, "ms_torch_fp32": ms_k_torch,
+                              "achieved": 2.0 * B * sum(dims[i] * dims[i + 1] for i in range(4)) / (ms_k_fused * 1e-3) / 1e12,
+                              "peak": tensor_peak(), "unit": "TFLOP/s"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": NCU_DRAM_BYTES_PER_LAUNCH_65536 if walk64k else None,
                          "traffic_unit": f"B per launch (dram read+write, ncu --set full, {NCU_PROFILE})",

@@ -6,9 +6,9 @@
 // The reference runs 8 cuBLAS fp32 GEMMs + ~20 elementwise launches per tick; here ONE kernel launch per network:
 //
 //   * one CTA owns a tile of 128 envs (= the 128 TMEM lanes) and walks the 4 layers without leaving the SM;
-//   * weights are pre-packed on the host into the exact shared-memory image of each (layer, N-chunk, 64-wide K stage)
-//     and streamed with 1-D TMA bulk copies (cp.async.bulk + mbarrier complete_tx) into a 2-deep ring;
-//   * each stage is 4 x tcgen05.mma (kind::f16, bf16 operands, fp32 accumulate, M = 128, N <= 256, K = 16) issued by one
+//   * weights are pre-packed on the host into the exact shared-memory image of each (layer, N-chunk, 32-wide K stage)
+//     and streamed with 1-D TMA bulk copies (cp.async.bulk + mbarrier complete_tx) into a 4-deep ring;
+//   * each stage is 2 x tcgen05.mma (kind::f16, bf16 operands, fp32 accumulate, M = 128, N <= 256, K = 16) issued by one
 //     thread, accumulators in TMEM (up to 512 columns), completion signalled with tcgen05.commit -> mbarrier;
 //   * the epilogue (tcgen05.ld 32x32b, bias, ELU, bf16 pack) writes the next layer's A operand straight back into shared
 //     memory in the K-major core-matrix layout the next tcgen05.mma reads - activations never touch HBM;
@@ -31,11 +31,15 @@ namespace go2pol {
 
 constexpr int TILE_M = 128;        // envs per CTA = TMEM lanes
 constexpr int MAX_LAYERS = 4;
-constexpr int KSTAGE = 64;         // K elements per weight stage (4 MMAs of K = 16)
+constexpr int NTHREADS = 256;      // 8 warps: two per TMEM lane quarter (they split the columns of an epilogue)
+constexpr int KPAD = 64;           // layer widths are padded to multiples of this
+constexpr int KSTAGE = 32;         // K elements per weight stage (2 MMAs of K = 16)
+constexpr int NSTAGE = 4;          // depth of the TMA weight ring
 constexpr int NCHUNK = 256;        // max N of one tcgen05.mma
-constexpr int STAGE_BYTES = (KSTAGE / 8) * NCHUNK * 16;  // 32 KB
+constexpr int STAGE_BYTES = (KSTAGE / 8) * NCHUNK * 16;  // 16 KB
 constexpr int ACT_BYTES = (512 / 8) * TILE_M * 16;        // widest activation tile: 128 x 512 bf16 = 128 KB
-constexpr int SMEM_BYTES = ACT_BYTES + 2 * STAGE_BYTES + 256;
+constexpr int BIAS_FLOATS = 512 + 512 + 512 + 16;
+constexpr int SMEM_BYTES = ACT_BYTES + NSTAGE * STAGE_BYTES + 256 + BIAS_FLOATS * 4;
 
 struct MlpDesc {
     int n_layers;
@@ -121,23 +125,26 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
     __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
     return *reinterpret_cast<uint32_t*>(&h);
 }
-__device__ __forceinline__ float elu(float x) { return x > 0.0f ? x : expm1f(x); }
+// exp(x) - 1 through the fast exponential: its absolute error (~1e-7) is far below the bf16 rounding of the result
+__device__ __forceinline__ float elu(float x) { return x > 0.0f ? x : __expf(x) - 1.0f; }
 
 
-// ---- the fused MLP kernel: 128 threads, one 128-env tile per CTA ---------------------------------------------
-__global__ void __launch_bounds__(TILE_M, 1) go2_mlp_kernel(MlpDesc d, const float* __restrict__ in, int B, ActOut o) {
+// ---- the fused MLP kernel: 256 threads, one 128-env tile per CTA -----------------------------------------------
+__global__ void __launch_bounds__(NTHREADS, 1) go2_mlp_kernel(MlpDesc d, const float* __restrict__ in, int B, ActOut o) {
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* act = smem;
     uint8_t* wbuf = smem + ACT_BYTES;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + ACT_BYTES + 2 * STAGE_BYTES);
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
-    const uint32_t full0 = smem_u32(&bars[0]), empty0 = smem_u32(&bars[2]), layer_bar = smem_u32(&bars[4]);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + ACT_BYTES + NSTAGE * STAGE_BYTES);  // full[4], empty[4], layer
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * NSTAGE + 2);
+    float* sbias = reinterpret_cast<float*>(smem + ACT_BYTES + NSTAGE * STAGE_BYTES + 256);
+    const uint32_t full0 = smem_u32(&bars[0]), empty0 = smem_u32(&bars[NSTAGE]), layer_bar = smem_u32(&bars[2 * NSTAGE]);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int row = blockIdx.x * TILE_M + tid;
+    const int trow_i = (warp & 3) * 32 + lane;   // row of the tile = TMEM lane this thread reads
+    const int half = warp >> 2;                   // which half of the columns of an epilogue this warp takes
+    const int row = blockIdx.x * TILE_M + trow_i;
 
     if (tid == 0) {
-        mbar_init(full0, 1); mbar_init(full0 + 8, 1);
-        mbar_init(empty0, 1); mbar_init(empty0 + 8, 1);
+        for (int i = 0; i < NSTAGE; ++i) { mbar_init(full0 + 8 * i, 1); mbar_init(empty0 + 8 * i, 1); }
         mbar_init(layer_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -145,18 +152,29 @@ __global__ void __launch_bounds__(TILE_M, 1) go2_mlp_kernel(MlpDesc d, const flo
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(tmem_slot)) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
+    // biases of all layers -> shared memory (epilogues read them as broadcasts)
+    int boff[MAX_LAYERS];
+    {
+        int acc = 0;
+        for (int l = 0; l < d.n_layers; ++l) {
+            boff[l] = acc;
+            for (int i = tid; i < d.N[l]; i += NTHREADS) sbias[acc + i] = d.b[l][i];
+            acc += d.N[l];
+        }
+    }
     // input tile -> bf16 A operand (K-major core matrices); rows past B and columns past n_in are zero
     {
         const int kchunks = d.K[0] >> 3;
-        for (int kc = 0; kc < kchunks; ++kc) {
+        const int grow = blockIdx.x * TILE_M + (tid & (TILE_M - 1));
+        for (int kc = tid >> 7; kc < kchunks; kc += NTHREADS / TILE_M) {
             float x[8];
 #pragma unroll
             for (int e = 0; e < 8; ++e) {
                 int k = kc * 8 + e;
-                x[e] = (row < B && k < d.n_in) ? in[(size_t)row * d.n_in + k] : 0.0f;
+                x[e] = (grow < B && k < d.n_in) ? in[(size_t)grow * d.n_in + k] : 0.0f;
             }
             uint4 v = make_uint4(pack_bf16(x[0], x[1]), pack_bf16(x[2], x[3]), pack_bf16(x[4], x[5]), pack_bf16(x[6], x[7]));
-            *reinterpret_cast<uint4*>(act + ((size_t)kc * TILE_M + tid) * 16) = v;
+            *reinterpret_cast<uint4*>(act + ((size_t)kc * TILE_M + (tid & (TILE_M - 1))) * 16) = v;
         }
     }
     fence_async_smem();
@@ -165,33 +183,29 @@ __global__ void __launch_bounds__(TILE_M, 1) go2_mlp_kernel(MlpDesc d, const flo
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    // stage table walk (warp 0 only): stage = (layer, n-chunk, 64-wide k stage), weights contiguous per stage
+    // stage table walk (warp 0 only): stage = (layer, n-chunk, 32-wide k stage), weights contiguous per stage
     int total = 0;
     for (int l = 0; l < d.n_layers; ++l) total += ((d.N[l] + NCHUNK - 1) / NCHUNK) * (d.K[l] / KSTAGE);
-    auto stage_src = [&](int s, const __nv_bfloat16*& src, uint32_t& bytes) {
-        for (int l = 0; l < d.n_layers; ++l) {
-            int nch = (d.N[l] + NCHUNK - 1) / NCHUNK, ks = d.K[l] / KSTAGE, nc_w = d.N[l] < NCHUNK ? d.N[l] : NCHUNK;
-            if (s < nch * ks) {
-                int nc = s / ks, k = s % ks;
-                src = d.w[l] + ((size_t)nc * (d.K[l] >> 3) + (size_t)k * (KSTAGE >> 3)) * nc_w * 8;
-                bytes = (KSTAGE >> 3) * nc_w * 16;
-                return;
-            }
-            s -= nch * ks;
-        }
-    };
     auto issue_tma = [&](int s) {
         const __nv_bfloat16* src = nullptr;
         uint32_t bytes = 0;
-        stage_src(s, src, bytes);
-        uint32_t bar = full0 + 8 * (s & 1);
+        int r = s;
+        for (int l = 0; l < d.n_layers; ++l) {
+            int nch = (d.N[l] + NCHUNK - 1) / NCHUNK, ks = d.K[l] / KSTAGE, nc_w = d.N[l] < NCHUNK ? d.N[l] : NCHUNK;
+            if (r < nch * ks) {
+                int nc = r / ks, k = r % ks;
+                src = d.w[l] + ((size_t)nc * (d.K[l] >> 3) + (size_t)k * (KSTAGE >> 3)) * nc_w * 8;
+                bytes = (KSTAGE >> 3) * nc_w * 16;
+                break;
+            }
+            r -= nch * ks;
+        }
+        uint32_t bar = full0 + 8 * (s % NSTAGE);
         mbar_expect_tx(bar, bytes);
-        tma_bulk_g2s(smem_u32(wbuf + (size_t)(s & 1) * STAGE_BYTES), src, bytes, bar);
+        tma_bulk_g2s(smem_u32(wbuf + (size_t)(s % NSTAGE) * STAGE_BYTES), src, bytes, bar);
     };
-    if (tid == 0) {
-        issue_tma(0);
-        if (total > 1) issue_tma(1);
-    }
+    if (tid == 0)
+        for (int i = 0; i < NSTAGE && i < total; ++i) issue_tma(i);
 
     int s = 0;
     for (int l = 0; l < d.n_layers; ++l) {
@@ -201,8 +215,8 @@ __global__ void __launch_bounds__(TILE_M, 1) go2_mlp_kernel(MlpDesc d, const flo
             for (int nc = 0; nc < nch; ++nc) {
                 for (int ks = 0; ks < kst; ++ks, ++s) {
                     if (lane == 0) {
-                        const int b = s & 1;
-                        mbar_wait(full0 + 8 * b, (s >> 1) & 1);
+                        const int b = s % NSTAGE;
+                        mbar_wait(full0 + 8 * b, (s / NSTAGE) & 1);
                         tc_fence_after();
                         const uint32_t a_base = smem_u32(act) + (uint32_t)(ks * (KSTAGE >> 3)) * TILE_M * 16;
                         const uint32_t b_base = smem_u32(wbuf + (size_t)b * STAGE_BYTES);
@@ -216,9 +230,9 @@ __global__ void __launch_bounds__(TILE_M, 1) go2_mlp_kernel(MlpDesc d, const flo
                         tc_commit(empty0 + 8 * b);
                         if (nc == nch - 1 && ks == kst - 1) tc_commit(layer_bar);
                         // refill the buffer of the previous stage (its MMAs are older than the ones just issued)
-                        if (s >= 1 && s + 1 < total) {
-                            mbar_wait(empty0 + 8 * ((s - 1) & 1), ((s - 1) >> 1) & 1);
-                            issue_tma(s + 1);
+                        if (s >= 1 && s - 1 + NSTAGE < total) {
+                            mbar_wait(empty0 + 8 * ((s - 1) % NSTAGE), ((s - 1) / NSTAGE) & 1);
+                            issue_tma(s - 1 + NSTAGE);
                         }
                     }
                     __syncwarp();
@@ -227,10 +241,10 @@ __global__ void __launch_bounds__(TILE_M, 1) go2_mlp_kernel(MlpDesc d, const flo
         }
         mbar_wait(layer_bar, l & 1);
         tc_fence_after();
-        const uint32_t trow = tmem_base + ((uint32_t)(warp * 32) << 16);
-        const float* bias = d.b[l];
+        const uint32_t trow = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
+        const float* bias = sbias + boff[l];
         if (l + 1 < d.n_layers) {
-            for (int c0 = 0; c0 < Nl; c0 += 32) {
+            for (int c0 = 32 * half; c0 < Nl; c0 += 64) {
                 uint32_t v[32];
                 tmem_ld32(trow + (uint32_t)c0, v);
                 float x[32];
@@ -240,11 +254,11 @@ __global__ void __launch_bounds__(TILE_M, 1) go2_mlp_kernel(MlpDesc d, const flo
                 for (int q = 0; q < 4; ++q) {
                     uint4 w4 = make_uint4(pack_bf16(x[8 * q], x[8 * q + 1]), pack_bf16(x[8 * q + 2], x[8 * q + 3]),
                                           pack_bf16(x[8 * q + 4], x[8 * q + 5]), pack_bf16(x[8 * q + 6], x[8 * q + 7]));
-                    *reinterpret_cast<uint4*>(act + ((size_t)((c0 >> 3) + q) * TILE_M + tid) * 16) = w4;
+                    *reinterpret_cast<uint4*>(act + ((size_t)((c0 >> 3) + q) * TILE_M + trow_i) * 16) = w4;
                 }
             }
             fence_async_smem();
-        } else {
+        } else if (half == 0) {
             uint32_t v[16];
             tmem_ld16(trow, v);
             if (row < B) {
@@ -337,7 +351,7 @@ int go2_mlp_create(const int32_t* dims, int n_layers, const float* params, int d
     const float* p = params;
     for (int l = 0; l < n_layers; ++l) {
         const int kr = dims[l], nr = dims[l + 1];
-        const int K = pad_to(kr, KSTAGE), N = (l + 1 < n_layers) ? pad_to(nr, KSTAGE) : 16;
+        const int K = pad_to(kr, KPAD), N = (l + 1 < n_layers) ? pad_to(nr, KPAD) : 16;
         d.K[l] = K;
         d.N[l] = N;
         const float* W = p;          // [nr][kr] row-major (torch.nn.Linear.weight)
@@ -381,7 +395,7 @@ void go2_mlp_destroy(go2_mlp* h) {
 static int launch_mlp(go2_mlp* h, const float* d_in, int B, const ActOut& o, void* stream) {
     if (!h || !d_in || B <= 0) return 1;
     int grid = (B + TILE_M - 1) / TILE_M;
-    go2_mlp_kernel<<<grid, TILE_M, SMEM_BYTES, (cudaStream_t)stream>>>(h->d, d_in, B, o);
+    go2_mlp_kernel<<<grid, NTHREADS, SMEM_BYTES, (cudaStream_t)stream>>>(h->d, d_in, B, o);
     return cudaGetLastError() == cudaSuccess ? 0 : 7;
 }
 
