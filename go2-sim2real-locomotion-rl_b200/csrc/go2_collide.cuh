@@ -354,34 +354,49 @@ G2_HDN void terrain_contacts(const Go2Model& m, Phys& p, int g, float mu) {
     c_max = c_max < m.terrain_c - 1 ? c_max : m.terrain_c - 1;
     float tol = 0.5f * MC_TOL * aabb_diag(m, g);  // the terrain's own AABB diagonal is never the smaller one
     int n_con = 0, first = p.n_contacts;
-    for (int r = r_min; r < r_max; ++r) {
-        int nvert = 0;
-        for (int cc = c_min; cc <= c_max; ++cc) {
-            for (int i = 0; i < 2; ++i) {
-                if (n_con >= TERRAIN_PAIR_CONTACTS) continue;
-                nvert++;
-                prism[0] = prism[1]; prism[1] = prism[2]; prism[3] = prism[4]; prism[4] = prism[5];
-                float x = sh * (float)(r + i), y = sh * (float)cc;
-                prism[2].x = x; prism[2].y = y;
-                prism[5] = mk3(x, y, m.terrain_hf[(size_t)(r + i) * m.terrain_c + cc]);
-                if (nvert > 2 && (prism[3].z >= lo[2] || prism[4].z >= lo[2] || prism[5].z >= lo[2])) {
-                    v3 cb = mk3(0, 0, 0);
-                    for (int k = 0; k < 6; ++k) cb = cb + prism[k];
-                    cb = cb * (1.0f / 6.0f);
-                    v3 n, pos;
-                    float pen;
-                    if (mpr(m, c, c.pa, cb, n, pen, pos)) {
-                        pos = pos + org;
-                        bool dup = false;
-                        for (int j = 0; j < n_con && !dup; ++j) {
-                            int idx = p.n_contacts - 1 - j;
-                            if (idx >= first && norm3(pos - p.con[idx].pos) < tol) dup = true;
-                        }
-                        if (!dup) {
-                            push_contact(m, p, g, 0, n, pos, pen, mu);
-                            n_con++;
-                        }
-                    }
+    // Two passes per batch of candidates so that the lanes of a warp run MPR together: (1) walk the vertex strip of each row
+    // (vertex n of row r = cell column c_min + (n-1)/2, row r + (n-1)%2) and record the prisms whose top reaches the geom's
+    // lowest point; (2) rebuild each recorded prism and run MPR on it, in strip order (so duplicates and the contact cap
+    // resolve exactly as in a single sweep).  ncu on the single-sweep version: MPR ran with 3 of 32 lanes.
+    constexpr int CAP = 48;
+    int cand[CAP];
+    const int nmax = 2 * (c_max - c_min + 1);
+    int r = r_min, n = 1;
+    float hA = 0.0f, hB = 0.0f;
+    while (r < r_max && nmax >= 3 && n_con < TERRAIN_PAIR_CONTACTS) {
+        int ncand = 0;
+        while (r < r_max && ncand < CAP) {
+            int cc = c_min + ((n - 1) >> 1), i = (n - 1) & 1;
+            float h = m.terrain_hf[(size_t)(r + i) * m.terrain_c + cc];
+            if (n > 2 && (hA >= lo[2] || hB >= lo[2] || h >= lo[2])) cand[ncand++] = (r << 12) | n;
+            hA = hB;
+            hB = h;
+            if (++n > nmax) { n = 1; ++r; }
+        }
+        for (int k = 0; k < ncand && n_con < TERRAIN_PAIR_CONTACTS; ++k) {
+            const int cr = cand[k] >> 12, cn = cand[k] & 4095;
+            v3 cb = mk3(0, 0, 0);
+            for (int j = 0; j < 3; ++j) {
+                int vn = cn - 2 + j;
+                int cc = c_min + ((vn - 1) >> 1), i = (vn - 1) & 1;
+                float x = sh * (float)(cr + i), y = sh * (float)cc;
+                prism[j] = mk3(x, y, m.terrain_zbot);
+                prism[3 + j] = mk3(x, y, m.terrain_hf[(size_t)(cr + i) * m.terrain_c + cc]);
+            }
+            for (int j = 0; j < 6; ++j) cb = cb + prism[j];
+            cb = cb * (1.0f / 6.0f);
+            v3 nrm, pos;
+            float pen;
+            if (mpr(m, c, c.pa, cb, nrm, pen, pos)) {
+                pos = pos + org;
+                bool dup = false;
+                for (int j = 0; j < n_con && !dup; ++j) {
+                    int idx = p.n_contacts - 1 - j;
+                    if (idx >= first && norm3(pos - p.con[idx].pos) < tol) dup = true;
+                }
+                if (!dup) {
+                    push_contact(m, p, g, 0, nrm, pos, pen, mu);
+                    n_con++;
                 }
             }
         }
