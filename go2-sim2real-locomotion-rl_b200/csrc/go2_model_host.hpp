@@ -1,12 +1,17 @@
 // go2_b200 - host-side unpacking of the flat model table (go2_b200/model.py:flatten_model) into Go2Model.
 #pragma once
 #include "go2_types.cuh"
+#include <stdlib.h>
 #include <string.h>
 
 namespace go2 {
 
 inline bool unpack_model(Go2Model& m, const int32_t* iv, int n_iv, const double* fv, int n_fv) {
     memset(&m, 0, sizeof(m));
+    {
+        const char* fd = getenv("GO2_B200_FORCE_DENSE");  // test hook: exercise the dense solver path on every env
+        m.force_dense = (fd && fd[0] == '1') ? 1 : 0;
+    }
     int k = 0, f = 0;
     int nl = iv[k++], ng = iv[k++], np = iv[k++];
     if (nl != NLINK || ng != NGEOM || np > MAX_PAIRS_STATIC) return false;

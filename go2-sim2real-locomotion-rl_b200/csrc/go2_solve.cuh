@@ -258,6 +258,7 @@ G2_HD void assemble_constraints(const Go2Model& m, Phys& p) {
 #ifdef G2_FORCE_DENSE
     arrow = 0;
 #endif
+    if (m.force_dense) arrow = 0;
     p.arrow = arrow;
     if (arrow) assemble_rows_a(m, p);
     else assemble_rows<false>(m, p);

@@ -67,6 +67,7 @@ struct Go2Model {
     int terrain_on, terrain_r, terrain_c;
     float terrain_sh, terrain_org[3], terrain_zmax, terrain_zbot;  // zbot = min(hf) - 1 (prism bottoms)
     const float* terrain_hf;
+    int force_dense;  // test hook (GO2_B200_FORCE_DENSE=1): every env uses the dense solver path (go2_solve.cuh)
 };
 
 // Reward terms (union of the walk / stair / base env zoos).

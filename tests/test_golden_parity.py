@@ -67,3 +67,23 @@ def test_free_running_prefix(name, kind, horizon, backend, hostemu_lib):
         assert _frac_ok(np_(env.core.buf["qpos"]), g["o_qpos"][t]) == 1.0, f"qpos diverged at step {t}"
         assert _frac_ok(np_(rew), g["o_rew"][t]) == 1.0, f"reward diverged at step {t}"
         assert _frac_ok(np_(obs), g["o_obs"][t]) >= 0.99
+
+
+@pytest.mark.parametrize("backend", BACKENDS)
+def test_dense_solver_path_matches_too(backend, hostemu_lib, monkeypatch):
+    """Envs whose legs touch each other use the dense 18x18 Newton path instead of the arrow factorisation
+    (go2_solve.cuh); the fixtures never produce such contacts, so the path is forced on every env here."""
+    monkeypatch.setenv("GO2_B200_FORCE_DENSE", "1")
+    g, cfgs = load_golden("walk_det")
+    T, B = g["actions"].shape[:2]
+    env = make_env("walk", cfgs, B, backend, hostemu_lib)
+    env.reset()
+    bad = total = 0
+    for t in range(0, T, 3):
+        force_state(env, g, t, "walk")
+        obs, rew, done, extras = env.step(torch.as_tensor(g["actions"][t], device=env.device))
+        same = np_(done).astype(np.uint8) == g["o_reset"][t]
+        ok = close(np_(obs), g["o_obs"][t], ATOL, RTOL).all(1) & close(np_(env.core.buf["qvel"]), g["o_qvel"][t], 10 * ATOL, RTOL).all(1)
+        bad += int((~ok[same]).sum())
+        total += int(same.sum())
+    assert bad <= total // 500, f"{bad} of {total} env-steps outside tolerance on the dense path"
