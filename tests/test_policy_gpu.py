@@ -113,3 +113,19 @@ def test_rollout_collector_runs_on_the_env():
     assert abs(float(col.advantages.mean())) < 1e-3
     assert torch.isfinite(col.actions).all() and float(col.actions.abs().max()) < 10.0
     assert (col.observations[1] != col.observations[0]).any()
+
+
+def test_policy_noise_is_shard_invariant():
+    """Two ranks holding envs [0, B/2) and [B/2, B) draw the same exploration noise as one rank holding all B envs
+    (the generator is keyed by the GLOBAL env id, like the env kernel's)."""
+    from go2_b200.rollout import FusedActorCritic
+
+    actor, critic = mlp([49, 512, 256, 128, 16], 1), mlp([104, 512, 256, 128, 1], 2)
+    std = 0.7 * torch.ones(16)
+    B = 512
+    obs = torch.randn(B, 49, device="cuda")
+    whole = FusedActorCritic(actor, critic, std, "cuda:0", seed=11).act(obs, step=3)[0]
+    lo = FusedActorCritic(actor, critic, std, "cuda:0", seed=11, env_offset=0).act(obs[: B // 2].contiguous(), step=3)[0]
+    hi = FusedActorCritic(actor, critic, std, "cuda:0", seed=11, env_offset=B // 2).act(obs[B // 2:].contiguous(), step=3)[0]
+    torch.cuda.synchronize()
+    assert torch.equal(whole, torch.cat([lo, hi]))
