@@ -31,7 +31,8 @@ namespace go2pol {
 
 constexpr int TILE_M = 128;        // envs per CTA = TMEM lanes
 constexpr int MAX_LAYERS = 4;
-constexpr int NTHREADS = 256;      // 8 warps: two per TMEM lane quarter (they split the columns of an epilogue)
+constexpr int NCOMPUTE = 256;      // 8 warps: two per TMEM lane quarter (they split the columns of an epilogue)
+constexpr int NTHREADS = NCOMPUTE + 32;  // + one TMA producer warp (keeps the weight ring full, never joins the layer barriers)
 constexpr int KPAD = 64;           // layer widths are padded to multiples of this
 constexpr int KSTAGE = 32;         // K elements per weight stage (2 MMAs of K = 16)
 constexpr int NSTAGE = 4;          // depth of the TMA weight ring
@@ -129,7 +130,7 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 __device__ __forceinline__ float elu(float x) { return x > 0.0f ? x : __expf(x) - 1.0f; }
 
 
-// ---- the fused MLP kernel: 256 threads, one 128-env tile per CTA -----------------------------------------------
+// ---- the fused MLP kernel: 8 compute warps + 1 producer warp, one 128-env tile per CTA -----------------------------------------------
 __global__ void __launch_bounds__(NTHREADS, 1) go2_mlp_kernel(MlpDesc d, const float* __restrict__ in, int B, ActOut o) {
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* act = smem;
@@ -166,7 +167,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) go2_mlp_kernel(MlpDesc d, const f
     {
         const int kchunks = d.K[0] >> 3;
         const int grow = blockIdx.x * TILE_M + (tid & (TILE_M - 1));
-        for (int kc = tid >> 7; kc < kchunks; kc += NTHREADS / TILE_M) {
+        for (int kc = tid >> 7; kc < kchunks && tid < NCOMPUTE; kc += NCOMPUTE / TILE_M) {
             float x[8];
 #pragma unroll
             for (int e = 0; e < 8; ++e) {
@@ -204,11 +205,20 @@ __global__ void __launch_bounds__(NTHREADS, 1) go2_mlp_kernel(MlpDesc d, const f
         mbar_expect_tx(bar, bytes);
         tma_bulk_g2s(smem_u32(wbuf + (size_t)(s % NSTAGE) * STAGE_BYTES), src, bytes, bar);
     };
-    if (tid == 0)
-        for (int i = 0; i < NSTAGE && i < total; ++i) issue_tma(i);
+    if (warp == NCOMPUTE / 32) {
+        // producer warp: stage s goes into ring slot s % NSTAGE as soon as the MMAs of stage s - NSTAGE have released it
+        if (lane == 0) {
+            for (int i = 0; i < NSTAGE && i < total; ++i) issue_tma(i);
+            for (int i = NSTAGE; i < total; ++i) {
+                mbar_wait(empty0 + 8 * (i % NSTAGE), ((i / NSTAGE) - 1) & 1);
+                issue_tma(i);
+            }
+        }
+        __syncwarp();
+    }
 
     int s = 0;
-    for (int l = 0; l < d.n_layers; ++l) {
+    for (int l = 0; l < d.n_layers && warp < NCOMPUTE / 32; ++l) {
         const int Kl = d.K[l], Nl = d.N[l];
         const int nch = (Nl + NCHUNK - 1) / NCHUNK, kst = Kl / KSTAGE, nc_w = Nl < NCHUNK ? Nl : NCHUNK;
         if (warp == 0) {
@@ -229,11 +239,6 @@ __global__ void __launch_bounds__(NTHREADS, 1) go2_mlp_kernel(MlpDesc d, const f
                         }
                         tc_commit(empty0 + 8 * b);
                         if (nc == nch - 1 && ks == kst - 1) tc_commit(layer_bar);
-                        // refill the buffer of the previous stage (its MMAs are older than the ones just issued)
-                        if (s >= 1 && s - 1 + NSTAGE < total) {
-                            mbar_wait(empty0 + 8 * ((s - 1) % NSTAGE), ((s - 1) / NSTAGE) & 1);
-                            issue_tma(s - 1 + NSTAGE);
-                        }
                     }
                     __syncwarp();
                 }
@@ -287,9 +292,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) go2_mlp_kernel(MlpDesc d, const f
             }
         }
         tc_fence_before();
-        __syncthreads();
+        asm volatile("bar.sync 1, %0;" ::"n"(NCOMPUTE) : "memory");  // compute warps only
         tc_fence_after();
     }
+    __syncthreads();
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
 }
 
