@@ -131,7 +131,16 @@ __device__ __forceinline__ float elu(float x) { return x > 0.0f ? x : __expf(x) 
 
 
 // ---- the fused MLP kernel: 8 compute warps + 1 producer warp, one 128-env tile per CTA -----------------------------------------------
-__global__ void __launch_bounds__(NTHREADS, 1) go2_mlp_kernel(MlpDesc d, const float* __restrict__ in, int B, ActOut o) {
+// blockIdx.y selects the network (0 / 1): actor and critic of one tick go out in ONE launch (twice the tiles per wave)
+struct MlpJob {
+    MlpDesc d;
+    const float* in;
+    ActOut o;
+};
+__global__ void __launch_bounds__(NTHREADS, 1) go2_mlp_kernel(MlpJob j0, MlpJob j1, int B) {
+    const MlpDesc& d = blockIdx.y ? j1.d : j0.d;
+    const float* __restrict__ in = blockIdx.y ? j1.in : j0.in;
+    const ActOut& o = blockIdx.y ? j1.o : j0.o;
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* act = smem;
     uint8_t* wbuf = smem + ACT_BYTES;
@@ -401,7 +410,11 @@ void go2_mlp_destroy(go2_mlp* h) {
 static int launch_mlp(go2_mlp* h, const float* d_in, int B, const ActOut& o, void* stream) {
     if (!h || !d_in || B <= 0) return 1;
     int grid = (B + TILE_M - 1) / TILE_M;
-    go2_mlp_kernel<<<grid, NTHREADS, SMEM_BYTES, (cudaStream_t)stream>>>(h->d, d_in, B, o);
+    MlpJob j;
+    j.d = h->d;
+    j.in = d_in;
+    j.o = o;
+    go2_mlp_kernel<<<dim3(grid, 1), NTHREADS, SMEM_BYTES, (cudaStream_t)stream>>>(j, j, B);
     return cudaGetLastError() == cudaSuccess ? 0 : 7;
 }
 
@@ -427,6 +440,21 @@ int go2_policy_act(go2_mlp* actor, const float* d_obs, int B, const float* d_std
     o.step = step;
     o.env_offset = env_offset;
     return launch_mlp(actor, d_obs, B, o, stream);
+}
+
+int go2_policy_act_critic(go2_mlp* actor, go2_mlp* critic, const float* d_obs, const float* d_critic_obs, int B, const float* d_std,
+                          uint64_t seed, uint32_t step, uint32_t env_offset, float* d_actions, float* d_mu, float* d_sigma, float* d_logp,
+                          float* d_values, void* stream) {
+    if (!actor || !critic || !d_obs || !d_critic_obs || !d_std || !d_actions || !d_values || B <= 0) return 1;
+    MlpJob ja, jc;
+    memset(&ja.o, 0, sizeof(ActOut));
+    memset(&jc.o, 0, sizeof(ActOut));
+    ja.d = actor->d; ja.in = d_obs;
+    ja.o.out = d_mu; ja.o.actions = d_actions; ja.o.sigma = d_sigma; ja.o.logp = d_logp; ja.o.std = d_std;
+    ja.o.seed_lo = (uint32_t)seed; ja.o.seed_hi = (uint32_t)(seed >> 32); ja.o.step = step; ja.o.env_offset = env_offset;
+    jc.d = critic->d; jc.in = d_critic_obs; jc.o.out = d_values;
+    go2_mlp_kernel<<<dim3((B + TILE_M - 1) / TILE_M, 2), NTHREADS, SMEM_BYTES, (cudaStream_t)stream>>>(ja, jc, B);
+    return cudaGetLastError() == cudaSuccess ? 0 : 7;
 }
 
 int go2_gae(const float* d_rewards, const uint8_t* d_dones, const float* d_values, const float* d_last_values, int T, int B, float gamma,

@@ -94,7 +94,7 @@ _EXPORTS = [
     "go2_step_host", "go2_read_stats", "go2_export_links", "go2_launch_count", "go2_set_terrain",
 ]
 # include/go2_policy.h (CUDA library only; the host-emulation test library has no tensor cores to emulate)
-_POLICY_EXPORTS = ["go2_mlp_create", "go2_mlp_destroy", "go2_mlp_forward", "go2_policy_act", "go2_gae"]
+_POLICY_EXPORTS = ["go2_mlp_create", "go2_mlp_destroy", "go2_mlp_forward", "go2_policy_act", "go2_policy_act_critic", "go2_gae"]
 _DTYPES = {0: np.float32, 1: np.int32, 2: np.uint8}
 
 

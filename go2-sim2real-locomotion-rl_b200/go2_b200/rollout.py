@@ -114,6 +114,18 @@ class FusedActorCritic:
         return actions, mu, sigma, logp
 
 
+    def act_and_evaluate(self, obs, critic_obs, step, actions, mu, sigma, logp, values):
+        """`act` + `evaluate` in one launch (actor tiles and critic tiles share the grid)."""
+        self.actor._check(obs)
+        self.critic._check(critic_obs)
+        rc = self.actor._lib.go2_policy_act_critic(self.actor._h, self.critic._h, _ptr(obs), _ptr(critic_obs), obs.shape[0], _ptr(self.std),
+                                                   C.c_uint64(self.seed), C.c_uint32(int(step)), C.c_uint32(self.env_offset), _ptr(actions),
+                                                   _ptr(mu), _ptr(sigma), _ptr(logp), _ptr(values), _stream())
+        if rc != 0:
+            raise RuntimeError(f"go2_policy_act_critic failed rc={rc}")
+        return actions, values
+
+
 def gae(rewards, dones, values, last_values, gamma, lam):
     """[T, B] returns and (un-normalised) advantages; `RolloutStorage.compute_returns` without the normalisation."""
     T, B = rewards.shape[:2]
@@ -149,8 +161,7 @@ class RolloutCollector:
         for t in range(self.T):
             self.observations[t].copy_(obs)
             self.privileged_observations[t].copy_(critic_obs)
-            ac.act(obs, self.tick, self.actions[t], self.mu[t], self.sigma[t], self.actions_log_prob[t])
-            ac.evaluate(critic_obs, self.values[t])
+            ac.act_and_evaluate(obs, critic_obs, self.tick, self.actions[t], self.mu[t], self.sigma[t], self.actions_log_prob[t], self.values[t])
             obs, rew, done, extras = env.step(self.actions[t])
             critic_obs = env.get_privileged_observations()
             # PPO.process_env_step: bootstrap on time-outs

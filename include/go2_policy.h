@@ -29,6 +29,12 @@ int go2_mlp_forward(go2_mlp* h, const float* d_in, int B, float* d_out, void* st
 int go2_policy_act(go2_mlp* actor, const float* d_obs, int B, const float* d_std, uint64_t seed, uint32_t step, uint32_t env_offset,
                    float* d_actions, float* d_mu, float* d_sigma, float* d_logp, void* stream);
 
+/* go2_policy_act for the actor and go2_mlp_forward for the critic (d_values[B] = critic(d_critic_obs)) in ONE launch:
+ * what PPO.act does per tick (ppo.py: actions = actor_critic.act(obs); values = actor_critic.evaluate(critic_obs)). */
+int go2_policy_act_critic(go2_mlp* actor, go2_mlp* critic, const float* d_obs, const float* d_critic_obs, int B, const float* d_std,
+                          uint64_t seed, uint32_t step, uint32_t env_offset, float* d_actions, float* d_mu, float* d_sigma, float* d_logp,
+                          float* d_values, void* stream);
+
 /* Replaces RolloutStorage.compute_returns (rsl_rl/storage/rollout_storage.py) without the advantage normalisation:
  * rewards / values / returns / advantages are [T][B] f32, dones [T][B] u8, last_values [B]. */
 int go2_gae(const float* d_rewards, const uint8_t* d_dones, const float* d_values, const float* d_last_values, int T, int B, float gamma,

@@ -129,3 +129,18 @@ def test_policy_noise_is_shard_invariant():
     hi = FusedActorCritic(actor, critic, std, "cuda:0", seed=11, env_offset=B // 2).act(obs[B // 2:].contiguous(), step=3)[0]
     torch.cuda.synchronize()
     assert torch.equal(whole, torch.cat([lo, hi]))
+
+
+def test_actor_and_critic_in_one_launch_match_the_separate_calls():
+    from go2_b200.rollout import FusedActorCritic
+
+    ac = FusedActorCritic(mlp([49, 512, 256, 128, 16], 1), mlp([104, 512, 256, 128, 1], 2), 0.5 * torch.ones(16), "cuda:0", seed=5)
+    B = 1000
+    obs, cobs = torch.randn(B, 49, device="cuda"), torch.randn(B, 104, device="cuda")
+    a, mu, sg, lp = ac.act(obs, step=9)
+    v = ac.evaluate(cobs)
+    a2, mu2, sg2, lp2, v2 = (torch.empty_like(x) for x in (a, mu, sg, lp, v))
+    ac.act_and_evaluate(obs, cobs, 9, a2, mu2, sg2, lp2, v2)
+    torch.cuda.synchronize()
+    for x, y in ((a, a2), (mu, mu2), (sg, sg2), (lp, lp2), (v, v2)):
+        assert torch.equal(x, y)
