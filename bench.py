@@ -253,7 +253,8 @@ def run_gpu(args):
     # against torch fp32 on the same weights, and 24-step rollout collection (actor sample + log-prob, critic, env step,
     # storage rows, GAE) as rsl-rl's OnPolicyRunner does it (BASELINE.json configs[4])
     from go2_b200.rollout import FusedActorCritic, RolloutCollector
-    n_priv = env.get_privileged_observations().shape[1]
+    _po = env.get_privileged_observations()
+    n_priv = _po.shape[1] if _po is not None else env.num_obs
     cdims = [n_priv, 512, 256, 128, 1]
     clayers = []
     for i in range(4):

@@ -158,12 +158,14 @@ class RolloutCollector:
         if obs is None:
             obs = env.get_observations()[0]
             critic_obs = env.get_privileged_observations()
+            critic_obs = obs if critic_obs is None else critic_obs
         for t in range(self.T):
             self.observations[t].copy_(obs)
             self.privileged_observations[t].copy_(critic_obs)
             ac.act_and_evaluate(obs, critic_obs, self.tick, self.actions[t], self.mu[t], self.sigma[t], self.actions_log_prob[t], self.values[t])
             obs, rew, done, extras = env.step(self.actions[t])
             critic_obs = env.get_privileged_observations()
+            critic_obs = obs if critic_obs is None else critic_obs  # base envs: the critic sees the actor's observations
             # PPO.process_env_step: bootstrap on time-outs
             torch.addcmul(rew.unsqueeze(1), self.values[t], extras["time_outs"].unsqueeze(1).to(torch.float32), value=self.gamma, out=self.rewards[t])
             self.dones[t].copy_(done.unsqueeze(1))
