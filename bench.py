@@ -349,7 +349,7 @@ def run_gpu(args):
                          "algorithmic_bytes_per_launch": B * bpe, "issue_frac": issue_frac,
                          "peak_source": which, "kernel": "go2_step_kernel", "kernel_ms_avg": kern_avg, "kernel_ms_median": kern_ms[len(kern_ms) // 2],
                          "bytes_per_env_step": bpe,
-                         "note": "thread-local-memory latency bound, not HBM-bandwidth shaped (DESIGN.md 4 item 8): HBM fraction is the designated accounting; issue_frac = issued warp-instr/s (ncu instr count per env-step x measured rate) / (4 x SMs x clock)"},
+                         "note": "thread-local-memory latency bound, not HBM-bandwidth shaped (DESIGN.md 4 item 9): HBM fraction is the designated accounting; issue_frac = issued warp-instr/s (ncu instr count per env-step x measured rate) / (4 x SMs x clock)"},
             "cpu_baseline": cpu, "clocks": clocks,
             "diag": {"mean_contacts": float(stats["ncontact"].float().mean()), "mean_newton_iters": float(stats["nnewton"].float().mean()),
                      "errno_envs": int((stats["errno"] != 0).sum())},
