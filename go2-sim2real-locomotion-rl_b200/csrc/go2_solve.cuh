@@ -661,7 +661,10 @@ G2_HD float add_nf(float a, float b) { volatile float r = a + b; return r; }
 G2_HD float mul_nf(float a, float b) { return a * b; }
 G2_HD float add_nf(float a, float b) { return a + b; }
 #endif
-constexpr int LS_REG = 16;  // rows of the line search kept in registers (4 contacts)
+#ifndef G2_LS_REG
+#define G2_LS_REG 16
+#endif
+constexpr int LS_REG = G2_LS_REG;  // rows of the line search kept in registers (16 = 4 contacts)
 struct LsPt {
     float alpha, cost, d0, d1;
 };
