@@ -747,8 +747,22 @@ G2_HD void store_phys(const Buffers& bf, int b, const Phys& p) {
 #else
 #define G2_PHASE_SYNC()
 #endif
+// Profiling build (-DG2_PHASE_CLOCKS): thread 0 of every block adds the SM clock ticks it spent in each phase to a global
+// table (0 load+FK+env_pre, 1 smooth, 2 collide, 3 assemble, 4 solve, 5 integrate+FK, 6 env_post+store); read by
+// profiles/tools/phase_clocks.py through go2_phase_clocks().
+#if defined(G2_PHASE_CLOCKS) && defined(__CUDACC__)
+__device__ unsigned long long g2_phase_clk[8];
+#endif
+#if defined(G2_PHASE_CLOCKS) && defined(__CUDA_ARCH__)
+#define G2_CLK(i) do { if (threadIdx.x == 0) { long long t1_ = clock64(); atomicAdd(&g2_phase_clk[i], (unsigned long long)(t1_ - t0_)); t0_ = t1_; } } while (0)
+#define G2_CLK_INIT() long long t0_ = clock64()
+#else
+#define G2_CLK(i)
+#define G2_CLK_INIT()
+#endif
 G2_HD void t_env_step(const Go2Model& m, const EnvConfig& cfg, const StepParams& sp, const Buffers& bf, const float* actions, int b,
                       bool valid, Phys& p, EnvLocal& e, EnvStepOut& out) {
+    G2_CLK_INIT();
     if (valid) {
         load_phys(bf, b, p);
         kinematics(m, sp.mass_shift, sp.com_shift, p);
@@ -758,13 +772,18 @@ G2_HD void t_env_step(const Go2Model& m, const EnvConfig& cfg, const StepParams&
     if (sp.do_physics) {
         for (int s = 0; s < 2; ++s) {
             G2_PHASE_SYNC();
+            G2_CLK(s == 0 ? 0 : 5);
             if (valid) smooth_dynamics(m, p);
             G2_PHASE_SYNC();
+            G2_CLK(1);
             if (valid) detect_collisions(m, p, sp.friction);
             G2_PHASE_SYNC();
+            G2_CLK(2);
             if (valid) assemble_constraints(m, p);
+            G2_CLK(3);
             solve_constraints(m, p, valid);  // block-synchronous iteration loop: every thread calls it
             G2_PHASE_SYNC();
+            G2_CLK(4);
             if (valid) {
                 integrate(m, p);
                 kinematics(m, sp.mass_shift, sp.com_shift, p);
@@ -773,10 +792,12 @@ G2_HD void t_env_step(const Go2Model& m, const EnvConfig& cfg, const StepParams&
         }
     }
     G2_PHASE_SYNC();
+    G2_CLK(5);
     if (valid) {
         env_post(m, cfg, sp, bf, b, p, e, out);
         store_phys(bf, b, p);
     }
+    G2_CLK(6);
 }
 
 #undef F32

@@ -296,6 +296,16 @@ int go2_set_terrain(go2_handle* h, const float* hf_m, int rows, int cols, float 
     return ck(h, cudaMemcpy(h->d_model, &m, sizeof(Go2Model), cudaMemcpyHostToDevice), "model upload") ? 0 : -1;
 }
 
+#ifdef G2_PHASE_CLOCKS
+// profiling build only: read (and clear) the per-phase clock table of go2_env.cuh
+void go2_phase_clocks(unsigned long long* out8) {
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out8, go2::g2_phase_clk, sizeof(unsigned long long) * 8);
+    unsigned long long z[8] = {0};
+    cudaMemcpyToSymbol(go2::g2_phase_clk, z, sizeof(z));
+}
+#endif
+
 long long go2_launch_count(go2_handle* h) { return h ? h->launches : 0; }
 
 }  // extern "C"
