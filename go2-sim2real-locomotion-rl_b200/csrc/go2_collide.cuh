@@ -321,122 +321,6 @@ G2_HDN bool pair_contacts(const Go2Model& m, Phys& p, int ga, int gb, v3 nws, bo
     return true;
 }
 
-// Narrow phase of a lane's candidate pairs as ONE loop with ONE mpr() call site: every trip runs the lane's next pending
-// detection (first detection of the next pair, its retry without the warm start, or one of the 4 perturbed re-detections),
-// so a lane on a sphere pair does not idle while its neighbours run the 4 perturbations of a box pair.  Per lane the
-// detections and their arithmetic are exactly those of pair_contacts() in the same order (bit-identical contacts / cache).
-G2_HDN void narrow_phase_jobs(const Go2Model& m, Phys& p, const int* cand, int ncand, float mu, int* new_pair, v3* new_n, int& n_new) {
-    int kc = 0, sub = -1;  // sub: -1 fetch the next pair, 0 first detection (or its retry), 1..4 perturbed detections
-    int ga = 0, gb = 0, jp = 0, first = 0, n_pair = 0;
-    bool have = false, multi = false;
-    float tol = 0.0f;
-    GeomPose A, B;
-    PairCtx c;
-    v3 nws, n0, pos0, ax0, ax1;
-    A.pos = B.pos = nws = n0 = pos0 = ax0 = ax1 = mk3(0, 0, 0);
-    A.quat = B.quat = mk4(1, 0, 0, 0);
-    c.prism = nullptr;
-    for (;;) {
-        if (sub < 0) {
-            if (kc >= ncand) break;
-            jp = cand[kc++];
-            ga = m.pair_a[jp];
-            gb = m.pair_b[jp];
-            if (m.g_type[ga] > m.g_type[gb]) { int t = ga; ga = gb; gb = t; }  // lower geom type first (sphere < cylinder < box)
-            nws = mk3(0, 0, 0);
-            have = false;
-            for (int k = 0; k < p.n_cache; ++k)
-                if (p.cache_pair[k] == jp) { nws = p.cache_n[k]; have = true; }
-            multi = m.g_type[ga] != GEOM_SPHERE && m.g_type[gb] != GEOM_SPHERE;
-            tol = 0.5f * MC_TOL * fminf(aabb_diag(m, ga), aabb_diag(m, gb));
-            A = geom_pose(m, p, ga);
-            B = geom_pose(m, p, gb);
-            c.ga = ga; c.gb = gb; c.pa = A.pos; c.pb = B.pos; c.Ra = qmat(A.quat); c.Rb = qmat(B.quat); c.prism = nullptr;
-            sub = 0;
-        }
-        PairCtx cp = c;
-        q4 qr = mk4(1, 0, 0, 0), qri = qr;
-        v3 ca, cb;
-        if (sub == 0) {
-            seed_centres(m, c, nws, have, ca, cb);
-        } else {
-            v3 axis = (float)(2 * (sub % 2) - 1) * ax0 + (float)(1 - 2 * ((sub / 2) % 2)) * ax1;
-            qr = rotvec_quat(axis * MC_PERTURB);
-            qri = qconj(qr);
-            // rotate both geoms about the first contact point, in opposite directions
-            q4 qa = qcompose(A.quat, qr);
-            v3 rel = pos0 - A.pos;
-            cp.pa = A.pos - (qrot(rel, qr) - rel);
-            cp.Ra = qmat(qa);
-            q4 qb = qcompose(B.quat, qri);
-            rel = pos0 - B.pos;
-            cp.pb = B.pos - (qrot(rel, qri) - rel);
-            cp.Rb = qmat(qb);
-            seed_centres(m, cp, n0, true, ca, cb);  // the cache already holds this detection's first normal
-        }
-        v3 n, pos;
-        float pen;
-        bool col = mpr(m, cp, ca, cb, n, pen, pos);
-        if (sub == 0) {
-            if (!col) {
-                if (have) have = false;  // retry without the warm start (narrowphase.py:690-700)
-                else sub = -1;
-                continue;
-            }
-            n0 = n;
-            pos0 = pos;
-            if (n_new < MAX_CPAIRS) {
-                new_pair[n_new] = jp;
-                new_n[n_new] = n0;
-                n_new++;
-            } else {
-                p.err |= ERR_CPAIR_OVERFLOW;
-            }
-            first = p.n_contacts;
-            push_contact(m, p, ga, gb, n0, pos0, pen, mu);
-            if (!multi) { sub = -1; continue; }
-            // perturbation axes: mix the principal axes of the smaller geom's link inertia with the normal
-            float va = m.g_half[ga][0] * m.g_half[ga][1] * m.g_half[ga][2], vb = m.g_half[gb][0] * m.g_half[gb][1] * m.g_half[gb][2];
-            int l = m.g_link[va < vb ? ga : gb];
-            m3 R;
-            if (l < 0) { q4 id = mk4(1, 0, 0, 0); R = qmat(id); }
-            else R = qmat(qcompose(ld4(m.inertial_quat[l]), p.lquat[l]));
-            int best = 0;
-            float amax = 0.0f;
-            for (int i = 0; i < 3; ++i) {
-                float a = fabsf(dot(mcol(R, i), n0));
-                if (a > amax) { amax = a; best = i; }
-            }
-            ax0 = mcol(R, (best + 1) % 3);
-            ax0 = normalize3(ax0 - dot(n0, ax0) * n0);
-            ax1 = cross(n0, ax0);
-            n_pair = 1;
-            sub = 1;
-            continue;
-        }
-        if (col) {
-            // undo the perturbation on the two surface points, first-order normal correction
-            v3 pA = qrot((pos - 0.5f * pen * n) - pos0, qri) + pos0;
-            v3 pB = qrot((pos + 0.5f * pen * n) - pos0, qr) + pos0;
-            pos = 0.5f * (pA + pB);
-            v3 tw = cross(n, n0);
-            tw = mk3(clampf(tw.x, -MC_PERTURB, MC_PERTURB), clampf(tw.y, -MC_PERTURB, MC_PERTURB), clampf(tw.z, -MC_PERTURB, MC_PERTURB));
-            n = n + cross(tw, n);
-            pen = dot(n, pB - pA);
-            bool rep = false;
-            for (int i = 0; i < n_pair && !rep; ++i) {
-                int idx = p.n_contacts - 1 - i;
-                if (idx >= first && norm3(pos - p.con[idx].pos) < tol) rep = true;
-            }
-            if (!rep && pen > -tol) {
-                push_contact(m, p, ga, gb, n, pos, fmaxf(pen, 0.0f), mu);
-                n_pair++;
-            }
-        }
-        sub = sub == 4 ? -1 : sub + 1;
-    }
-}
-
 // Geom g against the heightfield terrain (collider/narrowphase.py:346-512 func_contact_mpr_terrain): the cells under
 // the geom's extent are swept row by row as a strip of triangular prisms (each new vertex pair forms a prism with
 // the previous two), MPR runs against every prism whose top reaches the geom's lowest point, at most
@@ -527,51 +411,29 @@ G2_HDN void detect_collisions(const Go2Model& m, Phys& p, float friction) {
     int new_pair[MAX_CPAIRS];
     v3 new_n[MAX_CPAIRS];
     float mu = fmaxf(friction, 1e-2f);  // max(mu_a, mu_b, 0.01); the envs set one global mu on every geom
-    // Two passes per batch so that the lanes of a warp run the narrow phase together: (1) AABB-test the static pair table
-    // and record the overlapping pairs, (2) run the narrow phase on the k-th recorded pair of every lane.  Each lane still
-    // visits its pairs in table order, so contacts, cache and caps resolve exactly as in a single sweep.  (ncu on the
-    // single sweep: mpr ran with 11 of 32 lanes because lanes reach the call from different trips of the pair loop.)
-#ifndef G2_CPAIR_BATCH
-#define G2_CPAIR_BATCH 16
-#endif
-    int cand[G2_CPAIR_BATCH];
-    int ip = 0;
-    while (ip < m.npairs) {
-        int ncand = 0;
-        for (; ip < m.npairs && ncand < G2_CPAIR_BATCH; ++ip) {
-            int a = m.pair_a[ip], b = m.pair_b[ip];
-            v3 dc = p.g_c[a] - p.g_c[b], hs = p.g_h[a] + p.g_h[b];
-            if (fabsf(dc.x) < hs.x && fabsf(dc.y) < hs.y && fabsf(dc.z) < hs.z) cand[ncand++] = ip;
-        }
-#ifndef G2_NO_JOBS
-        if (!m.terrain_on) {  // flat ground (walk / crouch / jump): the job loop keeps the lanes on mpr() together
-            narrow_phase_jobs(m, p, cand, ncand, mu, new_pair, new_n, n_new);
+    for (int ip = 0; ip < m.npairs; ++ip) {
+        int a = m.pair_a[ip], b = m.pair_b[ip];
+        v3 dc = p.g_c[a] - p.g_c[b], hs = p.g_h[a] + p.g_h[b];
+        if (!(fabsf(dc.x) < hs.x && fabsf(dc.y) < hs.y && fabsf(dc.z) < hs.z)) continue;
+        if (m.terrain_on && (a == 0 || b == 0)) {  // geom 0 is the terrain: no normal cache, own narrow phase
+            terrain_contacts(m, p, a == 0 ? b : a, mu);
             continue;
         }
-#endif
-        for (int kc = 0; kc < ncand; ++kc) {
-            const int jp = cand[kc];
-            int a = m.pair_a[jp], b = m.pair_b[jp];
-            if (m.terrain_on && (a == 0 || b == 0)) {  // geom 0 is the terrain: no normal cache, own narrow phase
-                terrain_contacts(m, p, a == 0 ? b : a, mu);
-                continue;
-            }
-            // narrow phase wants the lower geom type first (sphere < cylinder < box)
-            int ga = a, gb = b;
-            if (m.g_type[ga] > m.g_type[gb]) { ga = b; gb = a; }
-            v3 nws = mk3(0, 0, 0);
-            bool have = false;
-            for (int k = 0; k < p.n_cache; ++k)
-                if (p.cache_pair[k] == jp) { nws = p.cache_n[k]; have = true; }
-            v3 n;
-            if (pair_contacts(m, p, ga, gb, nws, have, mu, n)) {
-                if (n_new < MAX_CPAIRS) {
-                    new_pair[n_new] = jp;
-                    new_n[n_new] = n;
-                    n_new++;
-                } else {
-                    p.err |= ERR_CPAIR_OVERFLOW;
-                }
+        // narrow phase wants the lower geom type first (sphere < cylinder < box)
+        int ga = a, gb = b;
+        if (m.g_type[ga] > m.g_type[gb]) { ga = b; gb = a; }
+        v3 nws = mk3(0, 0, 0);
+        bool have = false;
+        for (int k = 0; k < p.n_cache; ++k)
+            if (p.cache_pair[k] == ip) { nws = p.cache_n[k]; have = true; }
+        v3 n;
+        if (pair_contacts(m, p, ga, gb, nws, have, mu, n)) {
+            if (n_new < MAX_CPAIRS) {
+                new_pair[n_new] = ip;
+                new_n[n_new] = n;
+                n_new++;
+            } else {
+                p.err |= ERR_CPAIR_OVERFLOW;
             }
         }
     }
