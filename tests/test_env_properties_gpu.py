@@ -1,0 +1,126 @@
+"""GPU-side properties of the fused env step that the golden fixtures (deterministic cfgs, 8-12 envs) do not reach:
+
+  * the CUDA library against the SAME kernel source compiled for the host, on the SHIPPED cfgs (domain randomisation,
+    observation noise, pushes, curriculum, Philox draws) under random actions: the CUDA env runs freely, the host build is
+    re-seeded from its full state snapshot before every tick (one-step parity, tolerance |d| <= 2e-4 + 2e-3 |x|, reset
+    flags bit-exact up to threshold-borderline env-steps);
+  * BASELINE.json's full size (65,536 envs): run-to-run determinism and shard invariance (env i of a 4,096-env shard with
+    env_offset k * 4096 is bit-identical to env k * 4096 + i of the full batch - the property multi-GPU sharding rests on);
+  * go2_step_host (host buffers through the C ABI) returns exactly what the device-resident step leaves in HBM.
+"""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from util import ROOT, close, make_env, np_
+
+pytestmark = pytest.mark.gpu
+CFG_DIR = os.path.join(ROOT, "go2-sim2real-locomotion-rl_b200/go2_b200/cfgs")
+ATOL, RTOL = 2e-4, 2e-3
+
+
+def _cfgs(name):
+    with open(os.path.join(CFG_DIR, name + ".json")) as f:
+        return json.load(f)
+
+
+@pytest.mark.parametrize("name,kind,B,ticks", [("walk", "walk", 96, 40), ("stair", "stair", 64, 25), ("crouch", "base", 64, 40),
+                                               ("jump", "base", 64, 40)])
+def test_cuda_matches_host_build_of_the_source_on_shipped_cfgs(name, kind, B, ticks, hostemu_lib):
+    from go2_b200 import checkpoint as ck
+
+    cfgs = _cfgs(name)
+    dev = make_env(kind, cfgs, B, "cuda", seed=7)
+    host = make_env(kind, cfgs, B, "hostemu", hostemu_lib, seed=7)
+    dev.reset()
+    host.reset()
+    g = torch.Generator().manual_seed(3)
+    n_act = dev.num_actions
+    bad_float = bad_reset = checked = gross = n_contact_mismatch = 0
+    for t in range(ticks):
+        a = 0.5 * torch.randn(B, n_act, generator=g)
+        ck.load_env_state_dict(host, ck.env_state_dict(dev))
+        o_d, r_d, d_d, ex_d = dev.step(a.to(dev.device))
+        o_h, r_h, d_h, ex_h = host.step(a)
+        d_d, d_h = np_(d_d).astype(np.uint8), np_(d_h).astype(np.uint8)
+        same = d_d == d_h
+        bad_reset += int((~same).sum())
+        ok = close(np_(o_d), np_(o_h), ATOL, RTOL).all(1) & close(np_(r_d), np_(r_h), ATOL, RTOL)
+        ok &= close(np_(dev.core.buf["qpos"]), np_(host.core.buf["qpos"]), ATOL, RTOL).all(1)
+        ok &= close(np_(dev.core.buf["qvel"]), np_(host.core.buf["qvel"]), 10 * ATOL, RTOL).all(1)
+        if "critic" in ex_d.get("observations", {}):
+            ok &= close(np_(ex_d["observations"]["critic"]), np_(ex_h["observations"]["critic"]), ATOL, RTOL).all(1)
+        bad_float += int((~ok[same]).sum())
+        gross += int((np.abs(np_(dev.core.buf["qvel"]) - np_(host.core.buf["qvel"])).max(1) > 0.1)[same].sum())
+        n_contact_mismatch += int((np_(dev.core.buf["ncontact"]) != np_(host.core.buf["ncontact"])).sum())
+        checked += int(same.sum())
+    assert bad_reset <= max(1, ticks * B // 500), f"{bad_reset} reset mismatches"
+    assert n_contact_mismatch <= max(1, checked // 500), f"{n_contact_mismatch} contact-count mismatches"
+    # walk / crouch / jump: 1 % budget like test_golden_parity.py (measured on a B200: max |d qvel| 1e-4, nothing outside).
+    # stair: the robots are dropped from 0.84 m onto the steps; the landing ticks have ~11 contacts on step edges and the
+    # Newton solve of both builds stops at the reference's tolerance from differently rounded iterates (the device build
+    # contracts multiply-adds, the host build does not).  Measured: identical contact counts everywhere, 3.7 % of the
+    # env-steps outside the tight band, 1.5 % with |d qvel| > 1e-2, 0.06 % > 0.1 -> 8 % budget plus a 0.5 % cap on gross errors.
+    budget = checked // 12 if kind == "stair" else checked // 100
+    assert bad_float <= max(2, budget), f"{bad_float}/{checked} env-steps outside tolerance"
+    assert gross <= max(1, checked // 200), f"{gross}/{checked} env-steps with |d qvel| > 0.1"
+
+
+def _run(env, acts, lo=0):
+    env.reset()
+    outs = []
+    for a in acts:
+        obs, rew, done, _ = env.step(a[lo:lo + env.num_envs])
+        outs.append((obs.clone(), rew.clone(), done.clone(), env.core.buf["qpos"].clone()))
+    return outs
+
+
+def test_full_size_determinism_and_shard_invariance(monkeypatch):
+    B, S, k = 65536, 4096, 5
+    cfgs = _cfgs("walk")
+    g = torch.Generator(device="cuda").manual_seed(11)
+    acts = [0.5 * torch.randn(B, 16, generator=g, device="cuda") for _ in range(4)]
+    full = _run(make_env("walk", cfgs, B, "cuda", seed=11), acts)
+    again = _run(make_env("walk", cfgs, B, "cuda", seed=11), acts)
+    for x, y in zip(full, again):
+        for u, v in zip(x, y):
+            assert torch.equal(u, v), "two runs of the same seed differ"
+    # a shard on the same kernel instantiation (GO2_B200_SMALL=0: the 128-register kernel, other block shape) is bit-identical
+    monkeypatch.setenv("GO2_B200_SMALL", "0")
+    shard = _run(make_env("walk", cfgs, S, "cuda", seed=11, env_offset=k * S, total_envs=B), acts, lo=k * S)
+    # ... and on the 255-register instantiation used for small batches it stays within the parity tolerance
+    monkeypatch.setenv("GO2_B200_SMALL", "1")
+    shard_small = _run(make_env("walk", cfgs, S, "cuda", seed=11, env_offset=k * S, total_envs=B), acts, lo=k * S)
+    for t, (x, y, z) in enumerate(zip(full, shard, shard_small)):
+        if bool(torch.cat([f[2] for f in full[:t + 1]]).any()):
+            break  # after the first reset the host-side curriculum statistics of a lone shard differ by construction
+        for u, v, w in zip(x, y, z):
+            assert torch.equal(u[k * S:(k + 1) * S], v), f"shard differs from the full batch at tick {t}"
+            assert close(np_(w).astype(np.float64), np_(v).astype(np.float64), ATOL, RTOL).all()
+    assert t >= 1, "no tick was compared"
+
+
+def test_step_host_matches_device_step():
+    B = 300
+    cfgs = _cfgs("walk")
+    a_env = make_env("walk", cfgs, B, "cuda", seed=5)
+    b_env = make_env("walk", cfgs, B, "cuda", seed=5)
+    a_env.reset()
+    b_env.reset()
+    g = torch.Generator().manual_seed(9)
+    h_obs = np.empty((B, a_env.num_obs), dtype=np.float32)
+    h_rew = np.empty((B,), dtype=np.float32)
+    h_done = np.empty((B,), dtype=np.uint8)
+    h_priv = np.empty((B, a_env.num_privileged_obs), dtype=np.float32)
+    h_to = np.empty((B,), dtype=np.float32)
+    for _ in range(6):
+        a = (0.5 * torch.randn(B, 16, generator=g)).numpy()
+        obs, rew, done, ex = a_env.step(torch.as_tensor(a, device="cuda"))
+        b_env.step_host(np.ascontiguousarray(a), h_obs, h_rew, h_done, h_priv, h_to)
+        assert np.array_equal(np_(obs), h_obs) and np.array_equal(np_(rew), h_rew)
+        assert np.array_equal(np_(done).astype(np.uint8), h_done)
+        assert np.array_equal(np_(ex["observations"]["critic"]), h_priv)
+        assert np.array_equal(np_(ex["time_outs"]).astype(np.float32), h_to)
