@@ -373,6 +373,131 @@ G2_HDN void terrain_contacts(const Go2Model& m, Phys& p, int g, float mu) {
             hB = h;
             if (++n > nmax) { n = 1; ++r; }
         }
+#ifndef G2_NO_MPR_SM
+        // MPR over the recorded prisms as a per-lane state machine with ONE Minkowski-support site per trip: a lane fetches
+        // its next candidate as soon as the current one is decided, so the lanes of a warp stay on the support evaluation
+        // together whatever the depth at which their prisms leave the algorithm (ncu on the call-per-candidate version: the
+        // MPR code ran with 2-5 of 32 lanes).  Per lane the operations and their order are exactly those of mpr().
+        {
+            enum { ST_FETCH = 0, ST_S1, ST_S2, ST_DISC, ST_REFINE, ST_PEN };
+            int k = 0, stage = ST_FETCH, cnt = 0;
+            Portal s;
+            v3 d = mk3(0, 0, 0);
+            for (;;) {
+                if (stage == ST_FETCH) {
+                    if (k >= ncand || n_con >= TERRAIN_PAIR_CONTACTS) break;
+                    const int cr = cand[k] >> 12, cn = cand[k] & 4095;
+                    ++k;
+                    v3 cb = mk3(0, 0, 0);
+                    for (int j = 0; j < 3; ++j) {
+                        int vn = cn - 2 + j;
+                        int cc = c_min + ((vn - 1) >> 1), i = (vn - 1) & 1;
+                        float x = sh * (float)(cr + i), y = sh * (float)cc;
+                        prism[j] = mk3(x, y, m.terrain_zbot);
+                        prism[3 + j] = mk3(x, y, m.terrain_hf[(size_t)(cr + i) * m.terrain_c + cc]);
+                    }
+                    for (int j = 0; j < 6; ++j) cb = cb + prism[j];
+                    cb = cb * (1.0f / 6.0f);
+                    s.v1[0] = c.pa; s.v2[0] = cb; s.v[0] = c.pa - cb;
+                    if (tiny3(s.v[0])) s.v[0].x += 10.0f * CCD_EPS;
+                    d = -normalize3(s.v[0]);
+                    stage = ST_S1;
+                }
+                v3 v, v1, v2;
+                mink_support(m, c, d, v, v1, v2);
+                bool hit = false;
+                v3 nrm = mk3(0, 0, 0), pos = mk3(0, 0, 0);
+                float pen = 0.0f;
+                if (stage == ST_S1) {
+                    s.v[1] = v; s.v1[1] = v1; s.v2[1] = v2;
+                    if (dot(v, d) < CCD_EPS) { stage = ST_FETCH; continue; }
+                    d = cross(s.v[0], s.v[1]);
+                    if (dot(d, d) < CCD_EPS) {
+                        if (tiny3(s.v[1])) {  // touching at the origin
+                            pen = 0.0f;
+                            nrm = -normalize3(s.v[0]);
+                        } else {              // origin on the v0-v1 segment
+                            pen = norm3(s.v[1]);
+                            nrm = -normalize3(s.v[1]);
+                        }
+                        pos = (s.v1[1] + s.v2[1]) * 0.5f;
+                        hit = true;
+                    } else {
+                        d = normalize3(d);
+                        stage = ST_S2;
+                        continue;
+                    }
+                } else if (stage == ST_S2) {
+                    if (dot(v, d) < CCD_EPS) { stage = ST_FETCH; continue; }
+                    s.v[2] = v; s.v1[2] = v1; s.v2[2] = v2;
+                    d = normalize3(cross(s.v[1] - s.v[0], s.v[2] - s.v[0]));
+                    if (dot(d, s.v[0]) > 0.0f) {
+                        v3 t;
+                        t = s.v[1]; s.v[1] = s.v[2]; s.v[2] = t;
+                        t = s.v1[1]; s.v1[1] = s.v1[2]; s.v1[2] = t;
+                        t = s.v2[1]; s.v2[1] = s.v2[2]; s.v2[2] = t;
+                        d = -d;
+                    }
+                    cnt = 0;
+                    stage = ST_DISC;
+                    continue;
+                } else if (stage == ST_DISC) {
+                    if (dot(v, d) < CCD_EPS) { stage = ST_FETCH; continue; }
+                    bool again = false;
+                    if (dot(cross(s.v[1], v), s.v[0]) < -CCD_EPS) {
+                        s.v[2] = v; s.v1[2] = v1; s.v2[2] = v2;
+                        again = true;
+                    } else if (dot(cross(v, s.v[2]), s.v[0]) < -CCD_EPS) {
+                        s.v[1] = v; s.v1[1] = v1; s.v2[1] = v2;
+                        again = true;
+                    }
+                    if (again) {
+                        d = normalize3(cross(s.v[1] - s.v[0], s.v[2] - s.v[0]));
+                        if (++cnt == 15) stage = ST_FETCH;
+                        continue;
+                    }
+                    s.v[3] = v; s.v1[3] = v1; s.v2[3] = v2;
+                    // head of the refinement loop (guard = 0)
+                    cnt = 0;
+                    d = portal_dir(s);
+                    stage = dot(s.v[1], d) > -CCD_EPS ? ST_PEN : ST_REFINE;
+                    continue;
+                } else {  // ST_REFINE / ST_PEN: same helpers, other exits
+                    bool rt = reach_tol(s, v, d);
+                    if (stage == ST_REFINE) {
+                        if (!(dot(v, d) > -CCD_EPS) || rt) { stage = ST_FETCH; continue; }
+                    } else if (rt || cnt > CCD_ITERS) {
+                        pen = dot(d, s.v[1]);
+                        nrm = -d;
+                        float b1 = dot(cross(s.v[2], s.v[3]), d), b2 = dot(cross(s.v[3], s.v[1]), d), b3 = dot(cross(s.v[1], s.v[2]), d);
+                        float inv = 0.5f / (b1 + b2 + b3);
+                        pos = ((b1 * s.v1[1] + b2 * s.v1[2] + b3 * s.v1[3]) + (b1 * s.v2[1] + b2 * s.v2[2] + b3 * s.v2[3])) * inv;
+                        hit = true;
+                    }
+                    if (!hit) {
+                        expand_portal(s, v, v1, v2);
+                        ++cnt;
+                        if (stage == ST_REFINE && cnt > 4 * CCD_ITERS) { stage = ST_FETCH; continue; }
+                        d = portal_dir(s);
+                        if (stage == ST_REFINE && dot(s.v[1], d) > -CCD_EPS) { stage = ST_PEN; cnt = 0; }
+                        continue;
+                    }
+                }
+                // decided: collision
+                stage = ST_FETCH;
+                pos = pos + org;
+                bool dup = false;
+                for (int j = 0; j < n_con && !dup; ++j) {
+                    int idx = p.n_contacts - 1 - j;
+                    if (idx >= first && norm3(pos - p.con[idx].pos) < tol) dup = true;
+                }
+                if (!dup) {
+                    push_contact(m, p, g, 0, nrm, pos, pen, mu);
+                    n_con++;
+                }
+            }
+        }
+#else
         for (int k = 0; k < ncand && n_con < TERRAIN_PAIR_CONTACTS; ++k) {
             const int cr = cand[k] >> 12, cn = cand[k] & 4095;
             v3 cb = mk3(0, 0, 0);
@@ -400,6 +525,7 @@ G2_HDN void terrain_contacts(const Go2Model& m, Phys& p, int g, float mu) {
                 }
             }
         }
+#endif
     }
 }
 
