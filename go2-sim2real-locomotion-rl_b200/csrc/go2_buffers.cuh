@@ -1,14 +1,14 @@
 // go2_b200 - device buffer table.  The library owns one arena; the Python side wraps each entry as a
 // non-owning torch view (see go2_b200/core.py).
-// every buffer is env-major ([B][K]): with one warp per env the lanes read one env's row contiguously, and
-// the env-level tensors the reference exposes as torch attributes get the reference's shapes.
+// every buffer is env-major ([B][K]): the env-level tensors the reference exposes as torch attributes get the
+// reference's shapes and the physics state can be teacher-forced from the host.
 #pragma once
 #include "go2_types.cuh"
 
 namespace go2 {
 
 enum BufId {
-    // ---- physics state, env-major (one warp loads one env's rows with coalesced lane accesses)
+    // ---- physics state, env-major
     B_QPOS = 0,      // f32 [B][19]
     B_QVEL,          // f32 [B][18]
     B_QACC_WS,       // f32 [B][18]
@@ -57,11 +57,16 @@ enum BufId {
     B_LINK_VEL,      // f32 [B][13][3]
     B_CONTACT_FORCE, // f32 [B][13][3]  net contact force per link (get_links_net_contact_force)
     B_TORQUE,        // f32 [B][12]     control force in action order (get_dofs_control_force)
-    B_STATS,         // f32 [STATS_LEN] per-step episode statistics (device-side reduction)
+    B_STATS,         // f32 [3][STATS_LEN] episode statistics: rows 0/1 = this tick (by StepParams.parity), row 2 = accumulator
     B_NCONTACT,      // i32 [B]  diagnostics: contacts in the last substep
     B_NNEWTON,       // i32 [B]  diagnostics: Newton iterations in the last substep
     B_TERRAIN_ROW,   // i32 [B]  stair: difficulty row of the env
     B_LAST_X,        // f32 [B]  stair: base x at the previous tick (forward_progress)
+    B_GLOBALS,       // f32 [2][GLOBALS_LEN] global physics DR in force (friction, mass / COM shifts, reset counter), double-buffered
+    B_REW_TERMS,     // f32 [B][n_rew]  scaled reward terms of the tick (cfg.export_rew_terms)
+    B_REPLAY,        // f32 [B][REPLAY_LEN] replayed random draws (cfg.replay_rows, StepParams.replay_on)
+    B_FK_FRESH,      // u8  [B]  1 = the env's kinematics were refreshed (reset / state setter) after the last global mass / COM change
+    B_EXT_FORCE,     // f32 [B][4]  external force of the tick: robot-local link (as float), fx, fy, fz (world frame, at the link origin)
     B_COUNT
 };
 

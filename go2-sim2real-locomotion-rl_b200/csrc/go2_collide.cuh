@@ -530,15 +530,18 @@ G2_HDN void terrain_contacts(const Go2Model& m, Phys& p, int g, float mu) {
 }
 
 // Full detection for one env: AABBs -> static pair table -> narrow phase; rebuilds the normal cache.
-G2_HDN void detect_collisions(const Go2Model& m, Phys& p, float friction) {
+// `fric_ground` / `fric_robot`: friction of the ground entity's and the robot entity's geoms (set_friction is per entity,
+// rigid_geom.py:327-336); a contact uses max(mu_a, mu_b, 0.01) (narrowphase.py).
+G2_HDN void detect_collisions(const Go2Model& m, Phys& p, float fric_ground, float fric_robot) {
     geom_aabbs(m, p);
     p.n_contacts = 0;
     int n_new = 0;
     int new_pair[MAX_CPAIRS];
     v3 new_n[MAX_CPAIRS];
-    float mu = fmaxf(friction, 1e-2f);  // max(mu_a, mu_b, 0.01); the envs set one global mu on every geom
+    const float mu_rr = fmaxf(fric_robot, 1e-2f), mu_gr = fmaxf(fmaxf(fric_ground, fric_robot), 1e-2f);
     for (int ip = 0; ip < m.npairs; ++ip) {
         int a = m.pair_a[ip], b = m.pair_b[ip];
+        const float mu = (a == 0 || b == 0) ? mu_gr : mu_rr;
         v3 dc = p.g_c[a] - p.g_c[b], hs = p.g_h[a] + p.g_h[b];
         if (!(fabsf(dc.x) < hs.x && fabsf(dc.y) < hs.y && fabsf(dc.z) < hs.z)) continue;
         if (m.terrain_on && (a == 0 || b == 0)) {  // geom 0 is the terrain: no normal cache, own narrow phase

@@ -8,7 +8,6 @@
 // reset -> obs.  Base: termination -> reset -> rewards -> obs.
 #pragma once
 #include "go2_buffers.cuh"
-#include "go2_warp.cuh"
 #include "go2_solve.cuh"
 
 namespace go2 {
@@ -47,14 +46,16 @@ G2_HD v3 quat_to_rpy_deg(q4 q) {
     return mk3(r * k, pch * k, y * k);
 }
 
-G2_HD float w_applied_force(const Go2Model& m, const Phys& p, int d) { return applied_force(m, p, d); }
-
 template <class P>
 G2_HD v3 link_vel_world(const P& p, int l) { return p.cd_v[l] + cross(p.cd_a[l], p.lpos[l] - p.root_com); }
 
-G2_HD void resample_commands(const EnvConfig& cfg, const StepParams& sp, const Rng& rng, uint32_t slot, int gid, float* cmd) {
+// `rp` != null: the three command values the reference drew in the replayed tick (B_REPLAY) instead of Philox draws
+G2_HD void resample_commands(const EnvConfig& cfg, const StepParams& sp, const Rng& rng, uint32_t slot, int gid, float* cmd,
+                             const float* rp) {
     u4 r = rng4(rng, slot);
-    if (cfg.compound_commands) {
+    if (rp) {
+        cmd[0] = rp[0]; cmd[1] = rp[1]; cmd[2] = rp[2];
+    } else if (cfg.compound_commands) {
         cmd[0] = urange(sp.cmd_lo[0], sp.cmd_hi[0], r.a);
         cmd[1] = urange(sp.cmd_lo[1], sp.cmd_hi[1], r.b);
         cmd[2] = urange(sp.cmd_lo[2], sp.cmd_hi[2], r.c);
@@ -226,6 +227,7 @@ G2_HDN void reset_env(const Go2Model& m, const EnvConfig& cfg, const StepParams&
                       P& p, EnvLocal& e, EnvStepOut& out) {
     const float dt = 0.02f;
     int A = cfg.num_actions;
+    const float* rp = sp.replay_on ? F32(B_REPLAY) + (size_t)b * REPLAY_LEN : nullptr;  // fixture replay of the draws
     if (cfg.kind != ENV_BASE) {
         // per-episode domain randomisation (per-env draws; the global ones are host-side scalars)
         if (cfg.ctrl == CTRL_MANUAL_PLS || cfg.ctrl == CTRL_MANUAL_FIXED) {
@@ -233,14 +235,14 @@ G2_HDN void reset_env(const Go2Model& m, const EnvConfig& cfg, const StepParams&
                 u4 r1 = rng4(rng, SLOT_RESET + k), r2 = rng4(rng, SLOT_RESET + 3 + k);
                 uint32_t a1[4] = {r1.a, r1.b, r1.c, r1.d}, a2[4] = {r2.a, r2.b, r2.c, r2.d};
                 for (int j = 0; j < 4; ++j) {
-                    if (cfg.has_kp_factor) F32(B_KP_FACTORS)[b * NHINGE + 4 * k + j] = urange(sp.kpf_lo, sp.kpf_hi, a1[j]);
-                    if (cfg.has_kd_factor) F32(B_KD_FACTORS)[b * NHINGE + 4 * k + j] = urange(sp.kdf_lo, sp.kdf_hi, a2[j]);
+                    if (cfg.has_kp_factor) F32(B_KP_FACTORS)[b * NHINGE + 4 * k + j] = rp ? rp[RP_KPF + 4 * k + j] : urange(sp.kpf_lo, sp.kpf_hi, a1[j]);
+                    if (cfg.has_kd_factor) F32(B_KD_FACTORS)[b * NHINGE + 4 * k + j] = rp ? rp[RP_KDF + 4 * k + j] : urange(sp.kdf_lo, sp.kdf_hi, a2[j]);
                 }
             }
         }
         if (cfg.ctrl == CTRL_MANUAL_FIXED && cfg.has_kp_range) {  // go2_env_walk.py:775-795
             u4 r = rng4(rng, SLOT_RESET + 11);
-            float kp = urange(sp.kp_lo, sp.kp_hi, r.a), kd = urange(sp.kd_lo, sp.kd_hi, r.b);
+            float kp = rp ? rp[RP_KP] : urange(sp.kp_lo, sp.kp_hi, r.a), kd = rp ? rp[RP_KD] : urange(sp.kd_lo, sp.kd_hi, r.b);
             for (int j = 0; j < NHINGE; ++j) {
                 F32(B_EFF_KP)[b * NHINGE + j] = kp * F32(B_KP_FACTORS)[b * NHINGE + j];
                 F32(B_EFF_KD)[b * NHINGE + j] = kd * F32(B_KD_FACTORS)[b * NHINGE + j];
@@ -250,16 +252,16 @@ G2_HDN void reset_env(const Go2Model& m, const EnvConfig& cfg, const StepParams&
             for (int k = 0; k < 3; ++k) {
                 u4 r = rng4(rng, SLOT_RESET + 6 + k);
                 uint32_t a[4] = {r.a, r.b, r.c, r.d};
-                for (int j = 0; j < 4; ++j) F32(B_MOTOR_STRENGTH)[b * NHINGE + 4 * k + j] = urange(sp.ms_lo, sp.ms_hi, a[j]);
+                for (int j = 0; j < 4; ++j) F32(B_MOTOR_STRENGTH)[b * NHINGE + 4 * k + j] = rp ? rp[RP_MS + 4 * k + j] : urange(sp.ms_lo, sp.ms_hi, a[j]);
             }
         }
         u4 rg = rng4(rng, SLOT_RESET + 9);
         if (cfg.has_gravity_offset) {
-            F32(B_GRAV_OFF)[b * 3 + 0] = urange(sp.go_lo, sp.go_hi, rg.a);
-            F32(B_GRAV_OFF)[b * 3 + 1] = urange(sp.go_lo, sp.go_hi, rg.b);
-            F32(B_GRAV_OFF)[b * 3 + 2] = urange(sp.go_lo, sp.go_hi, rg.c);
+            F32(B_GRAV_OFF)[b * 3 + 0] = rp ? rp[RP_GO + 0] : urange(sp.go_lo, sp.go_hi, rg.a);
+            F32(B_GRAV_OFF)[b * 3 + 1] = rp ? rp[RP_GO + 1] : urange(sp.go_lo, sp.go_hi, rg.b);
+            F32(B_GRAV_OFF)[b * 3 + 2] = rp ? rp[RP_GO + 2] : urange(sp.go_lo, sp.go_hi, rg.c);
         }
-        I32(B_DELAY)[b] = sp.delay_lo + (int)(rg.d % (uint32_t)(sp.delay_hi - sp.delay_lo + 1));
+        I32(B_DELAY)[b] = rp ? (int)rp[RP_DELAY] : sp.delay_lo + (int)(rg.d % (uint32_t)(sp.delay_hi - sp.delay_lo + 1));
     }
     // joint + base state
     for (int j = 0; j < NHINGE; ++j) {
@@ -270,7 +272,7 @@ G2_HDN void reset_env(const Go2Model& m, const EnvConfig& cfg, const StepParams&
     for (int d = 0; d < NV; ++d) p.qvel[d] = 0.0f;
     e.base_pos = ld3(cfg.base_init_pos);
     e.base_quat = ld4(cfg.base_init_quat);
-    u4 rp = rng4(rng, SLOT_RESET + 10);
+    u4 rq = rng4(rng, SLOT_RESET + 10);
     if (cfg.kind == ENV_STAIR) {
         if (cfg.has_terrain && cfg.n_terrain_rows > 1 && !sp.lock_terrain_rows) {
             // frontier-heavy row assignment (go2_env_stair.py:809-854): 40 % on the highest accessible row, 30 % on the
@@ -286,7 +288,7 @@ G2_HDN void reset_env(const Go2Model& m, const EnvConfig& cfg, const StepParams&
                 int emax = mr >= 3 ? mr - 3 : 0;
                 row = (int)(rr.c % (uint32_t)(emax + 1));
             }
-            e.terrain_row = row;
+            e.terrain_row = rp ? (int)rp[RP_ROW] : row;
         }
         if (cfg.has_terrain) {  // spawn at the row centre, robot standing height on top (go2_env_stair.py:856-871)
             e.base_pos.x = cfg.row_center[e.terrain_row][0];
@@ -294,10 +296,11 @@ G2_HDN void reset_env(const Go2Model& m, const EnvConfig& cfg, const StepParams&
             e.base_pos.z = cfg.row_center[e.terrain_row][2] + cfg.base_init_pos[2];
         }
         // reference quirk (go2_env_stair.py:1541-1546): the drawn z is ADDED to the spawn height
-        if (cfg.has_init_z) e.base_pos.z = e.base_pos.z + urange(cfg.init_z_lo, cfg.init_z_hi, rp.a) - cfg.base_init_pos[2] + cfg.base_init_pos[2];
-    } else if (cfg.has_init_z) e.base_pos.z = urange(cfg.init_z_lo, cfg.init_z_hi, rp.a);
+        if (cfg.has_init_z) e.base_pos.z = e.base_pos.z + (rp ? rp[RP_INIT_Z] : urange(cfg.init_z_lo, cfg.init_z_hi, rq.a)) - cfg.base_init_pos[2] + cfg.base_init_pos[2];
+    } else if (cfg.has_init_z) e.base_pos.z = rp ? rp[RP_INIT_Z] : urange(cfg.init_z_lo, cfg.init_z_hi, rq.a);
     if (cfg.has_init_euler) {
-        float roll = urange(cfg.init_euler_lo, cfg.init_euler_hi, rp.b), pitch = urange(cfg.init_euler_lo, cfg.init_euler_hi, rp.c);
+        float roll = rp ? rp[RP_ROLL] : urange(cfg.init_euler_lo, cfg.init_euler_hi, rq.b);
+        float pitch = rp ? rp[RP_PITCH] : urange(cfg.init_euler_lo, cfg.init_euler_hi, rq.c);
         float cr = cosf(roll * 0.5f), sr = sinf(roll * 0.5f), cp = cosf(pitch * 0.5f), sp_ = sinf(pitch * 0.5f);
         e.base_quat = mk4(cr * cp, sr * cp, cr * sp_, -sr * sp_);  // yaw = 0
     }
@@ -328,7 +331,7 @@ G2_HDN void reset_env(const Go2Model& m, const EnvConfig& cfg, const StepParams&
         F32(B_EP_SUMS)[b * cfg.n_rew + k] = 0.0f;
     }
     e.ep_len = 0;
-    resample_commands(cfg, sp, rng, SLOT_CMD_RESET, cfg.env_offset + b, e.cmd);
+    resample_commands(cfg, sp, rng, SLOT_CMD_RESET, cfg.env_offset + b, e.cmd, rp ? rp + RP_CMD_RESET : nullptr);
 }
 
 // Scalar part of the tick BEFORE the physics (executed by one lane): loads the env-level buffers, turns the
@@ -337,6 +340,7 @@ template <class P>
 G2_HDN void env_pre(const Go2Model& m, const EnvConfig& cfg, const StepParams& sp, const Buffers& bf, const float* actions, int b,
                     P& p, EnvLocal& e, EnvStepOut& out) {
     const int A = cfg.num_actions, H = cfg.hist_size;
+    const float* rp = sp.replay_on ? F32(B_REPLAY) + (size_t)b * REPLAY_LEN : nullptr;
     Rng rng;
     rng.env = (uint32_t)(cfg.env_offset + b); rng.step = sp.step_count; rng.k0 = cfg.seed_lo; rng.k1 = cfg.seed_hi;
     out.reset = 0; out.timeout = 0; out.tracking_per_sec = 0.0f;
@@ -360,6 +364,20 @@ G2_HDN void env_pre(const Go2Model& m, const EnvConfig& cfg, const StepParams& s
     p.ext_link = -1;
     p.ext_f = mk3(0, 0, 0);
     p.ext_t = mk3(0, 0, 0);
+    p.ext2_link = -1;
+    p.ext2_f = mk3(0, 0, 0);
+    p.ext2_t = mk3(0, 0, 0);
+    if (sp.ext_on && sp.do_physics) {
+        // apply_links_external_force (abd/misc.py:655-715): world-frame force at the link origin -> force + torque about the
+        // root COM on that link for both substeps of this tick; the host clears the buffer afterwards (simulator.py:283)
+        const float* ex = F32(B_EXT_FORCE) + (size_t)b * 4;
+        int l = (int)ex[0];
+        if (l >= 0 && l < NLINK) {
+            p.ext2_link = l;
+            p.ext2_f = mk3(ex[1], ex[2], ex[3]);
+            p.ext2_t = cross(p.lpos[l] - p.root_com, p.ext2_f);
+        }
+    }
     for (int d = 0; d < NV; ++d) { p.ctrl_force[d] = 0.0f; p.ctrl_pos[d] = 0.0f; }
 
     if (sp.do_physics) {
@@ -380,6 +398,7 @@ G2_HDN void env_pre(const Go2Model& m, const EnvConfig& cfg, const StepParams& s
                     boxmuller(r.a, r.b, noise[4 * k], noise[4 * k + 1]);
                     boxmuller(r.c, r.d, noise[4 * k + 2], noise[4 * k + 3]);
                 }
+                if (rp) for (int j = 0; j < NHINGE; ++j) noise[j] = rp[RP_ACT_NOISE + j];
             }
             for (int j = 0; j < NHINGE; ++j)
                 e.target[j] = e.applied[j] * cfg.action_scale + cfg.default_dof_pos[j] + noise[j] * sp.action_noise_std;
@@ -411,10 +430,10 @@ G2_HDN void env_pre(const Go2Model& m, const EnvConfig& cfg, const StepParams& s
             if (cfg.has_push && sp.push_enable) {
                 if (sp.push_resample) {
                     u4 r = rng4(rng, SLOT_PUSH);
-                    F32(B_PUSH_FORCE)[b * 3 + 0] = urange(sp.push_lo, sp.push_hi, r.a);
-                    F32(B_PUSH_FORCE)[b * 3 + 1] = urange(sp.push_lo, sp.push_hi, r.b);
+                    F32(B_PUSH_FORCE)[b * 3 + 0] = rp ? rp[RP_PUSH] : urange(sp.push_lo, sp.push_hi, r.a);
+                    F32(B_PUSH_FORCE)[b * 3 + 1] = rp ? rp[RP_PUSH + 1] : urange(sp.push_lo, sp.push_hi, r.b);
                     F32(B_PUSH_FORCE)[b * 3 + 2] = 0.0f;
-                    I32(B_PUSH_REMAIN)[b] = cfg.push_dur_lo + (int)(r.c % (uint32_t)(cfg.push_dur_hi - cfg.push_dur_lo + 1));
+                    I32(B_PUSH_REMAIN)[b] = rp ? (int)rp[RP_PUSH + 2] : cfg.push_dur_lo + (int)(r.c % (uint32_t)(cfg.push_dur_hi - cfg.push_dur_lo + 1));
                 }
                 int rem = I32(B_PUSH_REMAIN)[b];
                 float on = rem > 0 ? 1.0f : 0.0f;
@@ -443,6 +462,8 @@ template <class P>
 G2_HDN void env_post(const Go2Model& m, const EnvConfig& cfg, const StepParams& sp, const Buffers& bf, int b, P& p, EnvLocal& e,
                      EnvStepOut& out) {
     const int A = cfg.num_actions;
+    const float* rp = sp.replay_on ? F32(B_REPLAY) + (size_t)b * REPLAY_LEN : nullptr;
+    const float* gl = F32(B_GLOBALS) + sp.parity * GLOBALS_LEN;
     Rng rng;
     rng.env = (uint32_t)(cfg.env_offset + b); rng.step = sp.step_count; rng.k0 = cfg.seed_lo; rng.k1 = cfg.seed_hi;
     if (sp.do_physics) {
@@ -459,7 +480,7 @@ G2_HDN void env_post(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
         for (int j = 0; j < NHINGE; ++j) {
             e.dof_pos[j] = p.qpos[cfg.motors_dof[j] + 1];
             e.dof_vel[j] = p.qvel[cfg.motors_dof[j]];
-            e.torque[j] = w_applied_force(m, p, cfg.motors_dof[j]);
+            e.torque[j] = applied_force(m, p, cfg.motors_dof[j]);
         }
         if (cfg.has_foot_tracking) {
             for (int i = 0; i < 4; ++i) {
@@ -467,7 +488,7 @@ G2_HDN void env_post(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
                 e.fc[i] = fabsf(p.cforce[cfg.foot_link[i]].z) > cfg.foot_contact_threshold ? 1 : 0;
             }
         }
-        if (e.ep_len % cfg.resample_steps == 0) resample_commands(cfg, sp, rng, SLOT_CMD, cfg.env_offset + b, e.cmd);
+        if (e.ep_len % cfg.resample_steps == 0) resample_commands(cfg, sp, rng, SLOT_CMD, cfg.env_offset + b, e.cmd, rp ? rp + RP_CMD : nullptr);
     } else {
         for (int i = 0; i < A; ++i) { e.act[i] = 0.0f; e.applied[i] = F32(B_APPLIED)[b * A + i]; }
         e.base_pos = ld3(F32(B_BASE_POS) + b * 3);
@@ -495,12 +516,13 @@ G2_HDN void env_post(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
         if (rst) reset_env(m, cfg, sp, bf, b, rng, p, e, out);
         if (sp.do_physics) {
             if (rst) {  // live getters see the post-reset state
-                for (int j = 0; j < NHINGE; ++j) e.torque[j] = w_applied_force(m, p, cfg.motors_dof[j]);
+                for (int j = 0; j < NHINGE; ++j) e.torque[j] = applied_force(m, p, cfg.motors_dof[j]);
             }
             for (int k = 0; k < cfg.n_rew; ++k) {
                 float r = reward_term(cfg.rew_id[k], m, cfg, p, e) * cfg.rew_scale[k];
                 rew += r;
                 F32(B_EP_SUMS)[b * cfg.n_rew + k] += r;
+                if (cfg.export_rew_terms) F32(B_REW_TERMS)[b * cfg.n_rew + k] = r;
             }
         }
     } else {
@@ -509,6 +531,7 @@ G2_HDN void env_post(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
                 float r = reward_term(cfg.rew_id[k], m, cfg, p, e) * cfg.rew_scale[k];
                 rew += r;
                 F32(B_EP_SUMS)[b * cfg.n_rew + k] += r;
+                if (cfg.export_rew_terms) F32(B_REW_TERMS)[b * cfg.n_rew + k] = r;
             }
         }
         if (rst) reset_env(m, cfg, sp, bf, b, rng, p, e, out);
@@ -538,7 +561,7 @@ G2_HDN void env_post(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
                 boxmuller(r.c, r.d, z[2], z[3]);
                 for (int j = 0; j < 4; ++j) {
                     int idx = 4 * k + j;
-                    if (idx < cfg.num_obs) o[idx] += z[j] * sp.obs_noise[idx];
+                    if (idx < cfg.num_obs) o[idx] += (rp ? rp[RP_OBS_NOISE + idx] : z[j]) * sp.obs_noise[idx];
                 }
             }
         }
@@ -548,14 +571,14 @@ G2_HDN void env_post(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
             int k = 0;
             for (int i = 0; i < cfg.num_obs; ++i) pr[k++] = o[i];
             pr[k++] = e.lin_vel.x * cfg.obs_scale_lin_vel; pr[k++] = e.lin_vel.y * cfg.obs_scale_lin_vel; pr[k++] = e.lin_vel.z * cfg.obs_scale_lin_vel;
-            pr[k++] = sp.friction;
+            pr[k++] = gl[G_FRIC_GROUND];  // patched by the post-pass kernel when this tick's resets change the global DR
             for (int j = 0; j < NHINGE; ++j) pr[k++] = F32(B_KP_FACTORS)[b * NHINGE + j];
             for (int j = 0; j < NHINGE; ++j) pr[k++] = F32(B_KD_FACTORS)[b * NHINGE + j];
             for (int j = 0; j < NHINGE; ++j) pr[k++] = F32(B_MOTOR_STRENGTH)[b * NHINGE + j];
-            pr[k++] = sp.mass_shift[0];
-            pr[k++] = sp.com_shift[0]; pr[k++] = sp.com_shift[1]; pr[k++] = sp.com_shift[2];
-            // leg mass shifts in cfg order FR, FL, RR, RL = robot links 2, 1, 4, 3
-            pr[k++] = sp.mass_shift[2]; pr[k++] = sp.mass_shift[1]; pr[k++] = sp.mass_shift[4]; pr[k++] = sp.mass_shift[3];
+            pr[k++] = gl[G_MASS_SHIFT];
+            pr[k++] = gl[G_COM_SHIFT]; pr[k++] = gl[G_COM_SHIFT + 1]; pr[k++] = gl[G_COM_SHIFT + 2];
+            // leg mass shifts in cfg order FR, FL, RR, RL (robot links 2, 1, 4, 3)
+            for (int i = 0; i < 4; ++i) pr[k++] = cfg.has_leg_mass_dr ? gl[G_MASS_SHIFT + cfg.hip_link[i]] : 0.0f;
             pr[k++] = go[0]; pr[k++] = go[1]; pr[k++] = go[2];
             pr[k++] = F32(B_CUR_PUSH)[b * 3]; pr[k++] = F32(B_CUR_PUSH)[b * 3 + 1]; pr[k++] = F32(B_CUR_PUSH)[b * 3 + 2];
             pr[k++] = cfg.max_delay > 0 ? (float)I32(B_DELAY)[b] / (float)cfg.max_delay : 0.0f;
@@ -587,6 +610,7 @@ G2_HDN void env_post(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
 
     // ---- write back
     U8(B_RESET)[b] = rst ? 1 : 0;
+    U8(B_FK_FRESH)[b] = rst ? 1 : 0;
     F32(B_TIMEOUT)[b] = tout ? 1.0f : 0.0f;
     I32(B_EP_LEN)[b] = e.ep_len;
     F32(B_LAST_X)[b] = e.last_x;
@@ -626,83 +650,8 @@ G2_HDN void env_post(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
     }
 }
 
-// Per-warp shared working set: physics + the scalar env-level locals that must survive the physics phases.
-struct WarpS {
-    EnvS s;
-    EnvLocal e;
-    EnvStepOut out;
-};
-
-// One control tick of env b by one warp.  `actions` is batch-first [B][A]; physics state is env-major.
-G2_HD void w_env_step(const Go2Model& m, const EnvConfig& cfg, const StepParams& sp, const Buffers& bf, const float* actions, int b,
-                      WarpS& w) {
-    EnvS& s = w.s;
-    LANES(l) {
-        if (l < NQ) s.qpos[l] = F32(B_QPOS)[b * NQ + l];
-        if (l < NV) {
-            s.qvel[l] = F32(B_QVEL)[b * NV + l];
-            s.qacc_ws[l] = F32(B_QACC_WS)[b * NV + l];
-            s.ctrl_force[l] = 0.0f;
-            s.ctrl_pos[l] = 0.0f;
-        }
-        if (l < NLINK) s.cforce[l] = mk3(0, 0, 0);
-        int nc = I32(B_NCACHE)[b];
-        if (l < nc) {
-            s.cache_pair[l] = I32(B_CACHE_PAIR)[b * MAX_CPAIRS + l];
-            const float* cn = F32(B_CACHE_N) + (size_t)b * MAX_CPAIRS * 3 + 3 * l;
-            s.cache_n[l] = mk3(cn[0], cn[1], cn[2]);
-        }
-        if (l == 0) {
-            s.warm = I32(B_WARM)[b];
-            s.n_cache = nc;
-            s.err = 0;
-            s.cost = 0.0f;
-            s.prev_cost = 0.0f;
-            s.n_contacts = 0;
-            s.n_rows = 0;
-            s.n_newton = 0;
-            s.ext_link = -1;
-            s.ext_f = mk3(0, 0, 0);
-            s.ext_t = mk3(0, 0, 0);
-        }
-        for (int r = l; r < W_MAXR; r += 32) s.act[r] = 0;
-    }
-    WSYNC();
-    w_kinematics(m, sp.mass_shift, sp.com_shift, s);
-    w_velocities(m, s);
-    LANES(l) {
-        if (l == 0) env_pre(m, cfg, sp, bf, actions, b, s, w.e, w.out);
-    }
-    WSYNC();
-    if (sp.do_physics) {
-        w_substep(m, s, sp.friction, sp.mass_shift, sp.com_shift);
-        w_substep(m, s, sp.friction, sp.mass_shift, sp.com_shift);
-    }
-    LANES(l) {
-        if (l == 0) env_post(m, cfg, sp, bf, b, s, w.e, w.out);
-    }
-    WSYNC();
-    LANES(l) {
-        if (l < NQ) F32(B_QPOS)[b * NQ + l] = s.qpos[l];
-        if (l < NV) {
-            F32(B_QVEL)[b * NV + l] = s.qvel[l];
-            F32(B_QACC_WS)[b * NV + l] = s.qacc_ws[l];
-        }
-        if (l < s.n_cache) {
-            I32(B_CACHE_PAIR)[b * MAX_CPAIRS + l] = s.cache_pair[l];
-            float* cn = F32(B_CACHE_N) + (size_t)b * MAX_CPAIRS * 3 + 3 * l;
-            cn[0] = s.cache_n[l].x; cn[1] = s.cache_n[l].y; cn[2] = s.cache_n[l].z;
-        }
-        if (l == 0) {
-            I32(B_WARM)[b] = s.warm;
-            I32(B_NCACHE)[b] = s.n_cache;
-        }
-    }
-    WSYNC();
-}
-
 // ---------------------------------------------------------------------------------------------------
-// Layout v3: one THREAD per env.  The whole control tick of env b runs in this thread; `p` is the thread's
+// One THREAD per env.  The whole control tick of env b runs in this thread; `p` is the thread's
 // private working set (registers + thread-local memory).  Persistent physics state is env-major in HBM.
 // ---------------------------------------------------------------------------------------------------
 G2_HD void load_phys(const Buffers& bf, int b, Phys& p) {
@@ -763,9 +712,17 @@ __device__ unsigned long long g2_phase_clk[8];
 G2_HD void t_env_step(const Go2Model& m, const EnvConfig& cfg, const StepParams& sp, const Buffers& bf, const float* actions, int b,
                       bool valid, Phys& p, EnvLocal& e, EnvStepOut& out) {
     G2_CLK_INIT();
+    const float* gl = F32(B_GLOBALS) + sp.parity * GLOBALS_LEN;  // global physics DR in force
     if (valid) {
         load_phys(bf, b, p);
-        kinematics(m, sp.mass_shift, sp.com_shift, p);
+        // The reference's substep starts from the link frames / inertias of the PREVIOUS substep's closing FK
+        // (rigid_solver.py:3155-3180), and set_mass_shift / set_COM_shift refresh nothing (rigid_solver.py:2051-2071): after a
+        // global mass / COM change the first substep still runs on inertias of the OLD values - except for envs whose state
+        // was set afterwards (reset_idx draws the global DR before set_dofs_position / set_pos, whose FK refresh sees the new
+        // values).  Same here: the tick-opening FK uses the other parity slot (= the previous tick's values) unless the env
+        // was refreshed since.
+        const float* gl0 = U8(B_FK_FRESH)[b] ? gl : F32(B_GLOBALS) + (sp.parity ^ 1) * GLOBALS_LEN;
+        kinematics(m, gl0, p);
         velocities(m, p);
         env_pre(m, cfg, sp, bf, actions, b, p, e, out);
     }
@@ -776,17 +733,17 @@ G2_HD void t_env_step(const Go2Model& m, const EnvConfig& cfg, const StepParams&
             if (valid) smooth_dynamics(m, p);
             G2_PHASE_SYNC();
             G2_CLK(1);
-            if (valid) detect_collisions(m, p, sp.friction);
+            if (valid) detect_collisions(m, p, gl[G_FRIC_GROUND], gl[G_FRIC_ROBOT]);
             G2_PHASE_SYNC();
             G2_CLK(2);
-            if (valid) assemble_constraints(m, p);
+            if (valid) assemble_constraints(m, p, cfg.solver_dense);
             G2_CLK(3);
             solve_constraints(m, p, valid);  // block-synchronous iteration loop: every thread calls it
             G2_PHASE_SYNC();
             G2_CLK(4);
             if (valid) {
                 integrate(m, p);
-                kinematics(m, sp.mass_shift, sp.com_shift, p);
+                kinematics(m, gl, p);
                 velocities(m, p);
             }
         }
@@ -798,6 +755,50 @@ G2_HD void t_env_step(const Go2Model& m, const EnvConfig& cfg, const StepParams&
         store_phys(bf, b, p);
     }
     G2_CLK(6);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Post-pass of a tick (one tiny kernel after the step kernel, csrc/go2_kernels.cu: go2_post_kernel).  The reference draws
+// the GLOBAL physics DR (Genesis keeps one friction / mass shift / COM shift for all envs) inside reset_idx, i.e. whenever
+// at least one env reset in the tick (go2_env_walk.py:737-756 friction with its reset-count throttle, :803-848 mass, COM,
+// per-leg mass), and the privileged obs of that same tick already show the new values (:1115-1141).  "Did any env
+// reset" is a grid-wide fact, so it is resolved here: the host passes this tick's candidate values in StepParams, the
+// step kernel counts the resets into B_STATS, and the post-pass puts the candidates in force (B_GLOBALS, double-buffered
+// by tick parity), patches the 9 global-DR columns of every env's privileged obs, and folds the tick's statistics into
+// the accumulator row that the host reads every `stats_sync_interval` ticks.
+// ---------------------------------------------------------------------------------------------------
+G2_HD bool post_globals(const EnvConfig& cfg, const StepParams& sp, float n_resets, const float* cur, float* next) {
+    for (int i = 0; i < GLOBALS_LEN; ++i) next[i] = cur[i];
+    if (cfg.kind == ENV_BASE || n_resets < 0.5f) return false;
+    bool changed = false;
+    if (cfg.has_friction_dr) {
+        float cnt = cur[G_DR_COUNTER] + n_resets;
+        if (cnt >= (float)cfg.global_dr_interval) {
+            cnt = 0.0f;
+            next[G_FRIC_GROUND] = next[G_FRIC_ROBOT] = sp.cand_friction;
+            changed = true;
+        }
+        next[G_DR_COUNTER] = cnt;
+    }
+    if (cfg.has_mass_dr) { next[G_MASS_SHIFT] = sp.cand_mass; changed = true; }
+    if (cfg.has_com_dr) {
+        for (int j = 0; j < 3; ++j) next[G_COM_SHIFT + j] = sp.cand_com[j];
+        changed = true;
+    }
+    if (cfg.has_leg_mass_dr) {
+        for (int i = 0; i < 4; ++i) next[G_MASS_SHIFT + cfg.hip_link[i]] = sp.cand_leg[i];
+        changed = true;
+    }
+    return changed;
+}
+// the global-DR entries of one env's privileged obs row (layout of env_post / go2_env_walk.py:1115-1141)
+G2_HD void post_patch_priv(const EnvConfig& cfg, const float* g, float* pr) {
+    int k = cfg.num_obs + 3;
+    pr[k] = g[G_FRIC_GROUND];
+    k += 1 + 3 * NHINGE;
+    pr[k++] = g[G_MASS_SHIFT];
+    pr[k++] = g[G_COM_SHIFT]; pr[k++] = g[G_COM_SHIFT + 1]; pr[k++] = g[G_COM_SHIFT + 2];
+    for (int i = 0; i < 4; ++i) pr[k++] = cfg.has_leg_mass_dr ? g[G_MASS_SHIFT + cfg.hip_link[i]] : 0.0f;
 }
 
 #undef F32

@@ -1,11 +1,10 @@
 // go2_b200 - CUDA kernels + C ABI (include/go2_b200.h) of the fused Go2 env step, sm_100a.
 //
-// Layout v3 (default): one THREAD per environment (go2_env.cuh: t_env_step).  A thread loads its env's persistent
-// state, runs the whole control tick (torque law, 2 rigid substeps incl. collision + Newton solve, rewards,
-// reset, observations) in registers / thread-local memory and writes the state back once: one launch per tick,
-// no global-memory round trips between phases.
-// Layout v2 (GO2_B200_LAYOUT=warp, kept for ablation; measured 5x slower): one WARP per env with
-// the working set in shared memory (go2_warp.cuh).
+// One THREAD per environment (go2_env.cuh: t_env_step).  A thread loads its env's persistent state, runs the whole
+// control tick (torque law, 2 rigid substeps incl. collision + Newton solve, rewards, reset, observations) in
+// registers / thread-local memory and writes the state back once: one launch per tick, no global-memory round trips
+// between phases.  A second, tiny launch (go2_post_kernel) resolves the one grid-wide dependency of a tick: "did any
+// env reset" -> global physics DR, privileged-obs patch, statistics accumulation (see go2_env.cuh: post_globals).
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -18,6 +17,8 @@
 
 using namespace go2;
 
+constexpr int N_STAT_SLOTS = 2;  // pinned host slots for asynchronous statistics reads
+
 struct go2_handle {
     int device;
     Go2Model* d_model;
@@ -29,27 +30,24 @@ struct go2_handle {
     int dtype[B_COUNT], rows[B_COUNT], cols[B_COUNT];
     char* arena;
     size_t arena_bytes;
-    float* h_stats;  // pinned
+    float* h_stats;      // pinned, [N_STAT_SLOTS][STATS_LEN]
+    cudaEvent_t stat_ev[N_STAT_SLOTS];
     long long launches;
-    int layout;  // 0 = thread per env (default), 1 = warp per env
-    int tpb, nblocks, small;  // launch shape of the thread-per-env kernel; small = the 255-register instantiation
-    int smem_pad;      // experiment knob (GO2_B200_SMEM_PAD): unused dynamic shared memory that caps the blocks per SM
+    int tpb, nblocks, small;  // launch shape of the step kernel; small = the 255-register instantiation
+    int parity;          // double-buffer index the NEXT tick uses (B_GLOBALS / B_STATS)
+    int post_pending;    // a deferred post-pass is outstanding (StepParams.defer_post)
     std::string err;
 };
-
-#ifndef GO2_WARPS
-#define GO2_WARPS 4  // envs (warps) per block
-#endif
 
 #ifndef GO2_TPB_SMALL
 #define GO2_TPB_SMALL 256
 #endif
 #ifndef GO2_TPB
-#define GO2_TPB 512  // max envs (threads) per block, thread-per-env layout; the launch picks blockDim <= GO2_TPB
+#define GO2_TPB 512  // max envs (threads) per block; the launch picks blockDim <= GO2_TPB
 #endif
 
-__device__ __forceinline__ void accumulate_stats(const EnvConfig* gcfg, const Buffers& bf, const EnvStepOut& out, int err) {
-    float* st = (float*)bf.p[B_STATS];
+__device__ __forceinline__ void accumulate_stats(const EnvConfig* gcfg, const StepParams& sp, const Buffers& bf, const EnvStepOut& out, int err) {
+    float* st = (float*)bf.p[B_STATS] + sp.parity * STATS_LEN;
     if (out.reset) {
         atomicAdd(&st[STATS_RESETS], 1.0f);
         if (out.timeout) atomicAdd(&st[STATS_TIMEOUTS], 1.0f);
@@ -68,7 +66,7 @@ __device__ __forceinline__ void step_body(const Go2Model* __restrict__ gm, const
     EnvLocal e;
     EnvStepOut out;
     t_env_step(*gm, *gcfg, sp, bf, actions, b, valid, p, e, out);
-    if (valid) accumulate_stats(gcfg, bf, out, p.err);
+    if (valid) accumulate_stats(gcfg, sp, bf, out, p.err);
 }
 // large batches: up to GO2_TPB threads per block, 128 registers (one 448-thread block per SM at 65,536 envs)
 __global__ void __launch_bounds__(GO2_TPB) go2_step_kernel(const Go2Model* __restrict__ gm, const EnvConfig* __restrict__ gcfg,
@@ -82,34 +80,44 @@ __global__ void __launch_bounds__(GO2_TPB_SMALL) go2_step_kernel_small(const Go2
     step_body(gm, gcfg, sp, bf, actions);
 }
 
-// one warp per env; the per-env working set (WarpS) lives in dynamic shared memory
-__global__ void __launch_bounds__(GO2_WARPS * 32) go2_step_warp_kernel(const Go2Model* __restrict__ gm, const EnvConfig* __restrict__ gcfg,
-                                                                  StepParams sp, Buffers bf, const float* __restrict__ actions) {
-    extern __shared__ __align__(16) unsigned char g2_smem[];
-    int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    int b = blockIdx.x * GO2_WARPS + warp;
-    if (b >= bf.B) return;
-    WarpS& w = reinterpret_cast<WarpS*>(g2_smem)[warp];
-    w_env_step(*gm, *gcfg, sp, bf, actions, b, w);
-    if (lane == 0) accumulate_stats(gcfg, bf, w.out, w.s.err);
+// Post-pass of a tick (go2_env.cuh: post_globals).  Every block recomputes the (deterministic) decision from this tick's
+// statistics row and the globals in force, and patches its envs' privileged obs; block 0 also publishes the next
+// tick's globals slot, folds the statistics into the accumulator row and clears the next tick's statistics row.
+__global__ void __launch_bounds__(256) go2_post_kernel(const EnvConfig* __restrict__ gcfg, StepParams sp, Buffers bf) {
+    const EnvConfig& cfg = *gcfg;
+    float* stats = (float*)bf.p[B_STATS];
+    const float* tick = stats + sp.parity * STATS_LEN;
+    const float* cur = (const float*)bf.p[B_GLOBALS] + sp.parity * GLOBALS_LEN;
+    float* nxt = (float*)bf.p[B_GLOBALS] + (sp.parity ^ 1) * GLOBALS_LEN;
+    float g[GLOBALS_LEN];
+    bool changed = post_globals(cfg, sp, tick[STATS_RESETS], cur, g);
+    if (changed && sp.do_physics && cfg.num_priv > 0) {
+        for (int b = blockIdx.x * blockDim.x + threadIdx.x; b < bf.B; b += gridDim.x * blockDim.x)
+            post_patch_priv(cfg, g, (float*)bf.p[B_PRIV] + (size_t)b * cfg.num_priv);
+    }
+    if (blockIdx.x == 0) {
+        if (threadIdx.x < GLOBALS_LEN) nxt[threadIdx.x] = g[threadIdx.x];
+        if (threadIdx.x < STATS_LEN) {
+            stats[2 * STATS_LEN + threadIdx.x] += tick[threadIdx.x];
+            stats[(sp.parity ^ 1) * STATS_LEN + threadIdx.x] = 0.0f;
+        }
+    }
 }
 
-__global__ void __launch_bounds__(GO2_WARPS * 32) go2_links_kernel(const Go2Model* __restrict__ gm, StepParams sp, Buffers bf) {
-    extern __shared__ __align__(16) unsigned char g2_smem[];
-    int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    int b = blockIdx.x * GO2_WARPS + warp;
+// get_links_pos / get_links_vel on demand: forward kinematics + link velocities of every env (one thread per env)
+__global__ void __launch_bounds__(128) go2_links_kernel(const Go2Model* __restrict__ gm, int parity, Buffers bf) {
+    int b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= bf.B) return;
-    EnvS& s = reinterpret_cast<WarpS*>(g2_smem)[warp].s;
-    if (lane < NQ) s.qpos[lane] = ((float*)bf.p[B_QPOS])[b * NQ + lane];
-    if (lane < NV) s.qvel[lane] = ((float*)bf.p[B_QVEL])[b * NV + lane];
-    __syncwarp();
-    w_kinematics(*gm, sp.mass_shift, sp.com_shift, s);
-    w_velocities(*gm, s);
-    if (lane < NLINK) {
-        float* lp = (float*)bf.p[B_LINK_POS] + ((size_t)b * NLINK + lane) * 3;
-        float* lv = (float*)bf.p[B_LINK_VEL] + ((size_t)b * NLINK + lane) * 3;
-        v3 v = link_vel_world(s, lane);
-        lp[0] = s.lpos[lane].x; lp[1] = s.lpos[lane].y; lp[2] = s.lpos[lane].z;
+    Phys p;
+    for (int i = 0; i < NQ; ++i) p.qpos[i] = ((const float*)bf.p[B_QPOS])[b * NQ + i];
+    for (int i = 0; i < NV; ++i) p.qvel[i] = ((const float*)bf.p[B_QVEL])[b * NV + i];
+    kinematics(*gm, (const float*)bf.p[B_GLOBALS] + parity * GLOBALS_LEN, p);
+    velocities(*gm, p);
+    for (int l = 0; l < NLINK; ++l) {
+        float* lp = (float*)bf.p[B_LINK_POS] + ((size_t)b * NLINK + l) * 3;
+        float* lv = (float*)bf.p[B_LINK_VEL] + ((size_t)b * NLINK + l) * 3;
+        v3 v = link_vel_world(p, l);
+        lp[0] = p.lpos[l].x; lp[1] = p.lpos[l].y; lp[2] = p.lpos[l].z;
         lv[0] = v.x; lv[1] = v.y; lv[2] = v.z;
     }
 }
@@ -136,8 +144,8 @@ int go2_create(const int32_t* model_iv, int n_iv, const double* model_fv, int n_
     go2_handle* h = new go2_handle();
     h->device = device;
     h->launches = 0;
-    const char* lay = getenv("GO2_B200_LAYOUT");
-    h->layout = (lay && !strcmp(lay, "warp")) ? 1 : 0;
+    h->parity = 0;
+    h->post_pending = 0;
     memcpy(&h->cfg, cfg, sizeof(EnvConfig));
     {
         // One block per SM per wave, as large as allowed: the warps of a block run phase-locked (barriers in
@@ -150,14 +158,8 @@ int go2_create(const int32_t* model_iv, int n_iv, const double* model_fv, int n_
             int t = ((B + n_sm * k - 1) / (n_sm * k) + 31) / 32 * 32;
             if (t <= GO2_TPB) { tpb = t; break; }
         }
-        const char* tp = getenv("GO2_B200_TPB");
-        if (tp && atoi(tp) >= 32 && atoi(tp) <= GO2_TPB) tpb = atoi(tp) / 32 * 32;
         h->tpb = tpb;
         h->small = (B <= GO2_TPB_SMALL * n_sm && tpb <= GO2_TPB_SMALL) ? 1 : 0;  // one wave of <= 256-thread blocks
-        const char* sm = getenv("GO2_B200_SMALL");
-        if (sm && tpb <= GO2_TPB_SMALL) h->small = atoi(sm) ? 1 : 0;
-        const char* pad = getenv("GO2_B200_SMEM_PAD");
-        h->smem_pad = pad ? atoi(pad) : 0;
         h->nblocks = (B + tpb - 1) / tpb;
     }
     const EnvConfig& c = h->cfg;
@@ -165,6 +167,7 @@ int go2_create(const int32_t* model_iv, int n_iv, const double* model_fv, int n_
     Go2Model& m = h->model;
     if (!unpack_model(m, model_iv, n_iv, model_fv, n_fv)) { delete h; return -3; }
     if (c.num_envs <= 0 || c.num_actions > NACT_MAX || c.num_obs > NOBS_MAX || c.hist_size > HIST_MAX || c.n_rew > MAX_REW) { delete h; return -4; }
+    if (c.replay_rows != 0 && c.replay_rows != c.num_envs) { delete h; return -4; }
     if (cudaSetDevice(device) != cudaSuccess) { delete h; return -5; }
     compute_layout(c, h->dtype, h->rows, h->cols);
     size_t offs[B_COUNT];
@@ -176,12 +179,10 @@ int go2_create(const int32_t* model_iv, int n_iv, const double* model_fv, int n_
     cudaMalloc(&h->d_cfg, sizeof(EnvConfig));
     cudaMemcpy(h->d_model, &m, sizeof(Go2Model), cudaMemcpyHostToDevice);
     cudaMemcpy(h->d_cfg, &h->cfg, sizeof(EnvConfig), cudaMemcpyHostToDevice);
-    cudaMallocHost(&h->h_stats, sizeof(float) * STATS_LEN);
-    cudaFuncSetAttribute(go2_step_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(GO2_WARPS * sizeof(WarpS)));
-    if (h->smem_pad > 0) cudaFuncSetAttribute(go2_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, h->smem_pad);
-    else cudaFuncSetAttribute(go2_step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 0);  // all of L1 for thread-local data
+    cudaMallocHost(&h->h_stats, sizeof(float) * STATS_LEN * N_STAT_SLOTS);
+    for (int i = 0; i < N_STAT_SLOTS; ++i) cudaEventCreateWithFlags(&h->stat_ev[i], cudaEventDisableTiming);
+    cudaFuncSetAttribute(go2_step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 0);  // all of L1 for thread-local data
     cudaFuncSetAttribute(go2_step_kernel_small, cudaFuncAttributePreferredSharedMemoryCarveout, 0);
-    cudaFuncSetAttribute(go2_links_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(GO2_WARPS * sizeof(WarpS)));
     std::string init(h->arena_bytes, 0);
     init_arena(c, offs, &init[0]);
     cudaMemcpy(h->arena, init.data(), h->arena_bytes, cudaMemcpyHostToDevice);
@@ -199,6 +200,7 @@ void go2_destroy(go2_handle* h) {
     if (h->d_hf) cudaFree(h->d_hf);
     cudaFree(h->d_cfg);
     cudaFreeHost(h->h_stats);
+    for (int i = 0; i < N_STAT_SLOTS; ++i) cudaEventDestroy(h->stat_ev[i]);
     delete h;
 }
 
@@ -213,25 +215,54 @@ int go2_buffer_info(go2_handle* h, int id, void** ptr, int* dtype, int* rows, in
     return 0;
 }
 
+static int launch_post(go2_handle* h, const StepParams& sp, cudaStream_t s) {
+    const EnvConfig& c = h->cfg;
+    // the privileged-obs patch is the only per-env work; one block is enough for the flavours without it
+    int blocks = (c.num_priv > 0 && c.kind != ENV_BASE) ? (c.num_envs + 255) / 256 : 1;
+    if (blocks > 1184) blocks = 1184;
+    go2_post_kernel<<<blocks, 256, 0, s>>>(h->d_cfg, sp, h->bf);
+    h->launches += 1;
+    h->parity ^= 1;
+    h->post_pending = 0;
+    return ck(h, cudaGetLastError(), "go2_post_kernel") ? 0 : -1;
+}
+
 static int launch_step(go2_handle* h, const float* d_actions, const void* params, int params_bytes, cudaStream_t s) {
     if (params_bytes != (int)sizeof(StepParams)) { h->err = "StepParams size mismatch"; return -2; }
+    if (h->post_pending) { h->err = "go2_post must follow a go2_step with defer_post before the next tick"; return -3; }
     StepParams sp;
     memcpy(&sp, params, sizeof(sp));
-    int B = h->cfg.num_envs;
-    if (!ck(h, cudaMemsetAsync(h->bf.p[B_STATS], 0, sizeof(float) * STATS_LEN, s), "memset stats")) return -1;
-    if (h->layout == 1)
-        go2_step_warp_kernel<<<(B + GO2_WARPS - 1) / GO2_WARPS, GO2_WARPS * 32, GO2_WARPS * sizeof(WarpS), s>>>(h->d_model, h->d_cfg, sp, h->bf, d_actions);
-    else if (h->small)
-        go2_step_kernel_small<<<h->nblocks, h->tpb, h->smem_pad, s>>>(h->d_model, h->d_cfg, sp, h->bf, d_actions);
+    sp.parity = h->parity;
+    if (sp.replay_on && h->cfg.replay_rows != h->cfg.num_envs) { h->err = "replay_on needs EnvConfig.replay_rows == num_envs"; return -4; }
+    if (cudaSetDevice(h->device) != cudaSuccess) { h->err = "cudaSetDevice"; return -1; }
+    if (h->small)
+        go2_step_kernel_small<<<h->nblocks, h->tpb, 0, s>>>(h->d_model, h->d_cfg, sp, h->bf, d_actions);
     else
-        go2_step_kernel<<<h->nblocks, h->tpb, h->smem_pad, s>>>(h->d_model, h->d_cfg, sp, h->bf, d_actions);
+        go2_step_kernel<<<h->nblocks, h->tpb, 0, s>>>(h->d_model, h->d_cfg, sp, h->bf, d_actions);
     h->launches += 1;
-    return ck(h, cudaGetLastError(), "go2_step_kernel") ? 0 : -1;
+    if (!ck(h, cudaGetLastError(), "go2_step_kernel")) return -1;
+    if (sp.defer_post) {
+        h->post_pending = 1;
+        return 0;
+    }
+    return launch_post(h, sp, s);
 }
 
 int go2_step(go2_handle* h, const float* d_actions, const void* params, int params_bytes, void* stream) {
     return launch_step(h, d_actions, params, params_bytes, (cudaStream_t)stream);
 }
+
+int go2_post(go2_handle* h, const void* params, int params_bytes, void* stream) {
+    if (params_bytes != (int)sizeof(StepParams)) { h->err = "StepParams size mismatch"; return -2; }
+    if (!h->post_pending) { h->err = "go2_post without a pending deferred post-pass"; return -3; }
+    StepParams sp;
+    memcpy(&sp, params, sizeof(sp));
+    sp.parity = h->parity;
+    if (cudaSetDevice(h->device) != cudaSuccess) { h->err = "cudaSetDevice"; return -1; }
+    return launch_post(h, sp, (cudaStream_t)stream);
+}
+
+int go2_tick_parity(go2_handle* h) { return h ? h->parity : -1; }
 
 int go2_reset_all(go2_handle* h, const void* params, int params_bytes, void* stream) {
     if (params_bytes != (int)sizeof(StepParams)) { h->err = "StepParams size mismatch"; return -2; }
@@ -247,39 +278,60 @@ int go2_step_host(go2_handle* h, const float* h_actions, const void* params, int
     cudaStream_t s = (cudaStream_t)stream;
     const EnvConfig& c = h->cfg;
     size_t B = c.num_envs;
+    if (cudaSetDevice(h->device) != cudaSuccess) { h->err = "cudaSetDevice"; return -1; }
     if (!ck(h, cudaMemcpyAsync(h->bf.p[B_ACTIONS_IN], h_actions, B * c.num_actions * 4, cudaMemcpyHostToDevice, s), "H2D actions")) return -1;
     int r = launch_step(h, (const float*)h->bf.p[B_ACTIONS_IN], params, params_bytes, s);
     if (r) return r;
-    cudaMemcpyAsync(h_obs, h->bf.p[B_OBS], B * c.num_obs * 4, cudaMemcpyDeviceToHost, s);
+    if (h->post_pending) { h->err = "go2_step_host does not support defer_post"; return -3; }
+    // the small results first: a consumer polling rew / done is not held back by the bulk rows
     cudaMemcpyAsync(h_rew, h->bf.p[B_REW], B * 4, cudaMemcpyDeviceToHost, s);
     cudaMemcpyAsync(h_done, h->bf.p[B_RESET], B, cudaMemcpyDeviceToHost, s);
-    if (h_priv && c.num_priv > 0) cudaMemcpyAsync(h_priv, h->bf.p[B_PRIV], B * c.num_priv * 4, cudaMemcpyDeviceToHost, s);
     if (h_timeouts) cudaMemcpyAsync(h_timeouts, h->bf.p[B_TIMEOUT], B * 4, cudaMemcpyDeviceToHost, s);
+    cudaMemcpyAsync(h_obs, h->bf.p[B_OBS], B * c.num_obs * 4, cudaMemcpyDeviceToHost, s);
+    if (h_priv && c.num_priv > 0) cudaMemcpyAsync(h_priv, h->bf.p[B_PRIV], B * c.num_priv * 4, cudaMemcpyDeviceToHost, s);
     return ck(h, cudaStreamSynchronize(s), "step_host sync") ? 0 : -1;
 }
 
-int go2_read_stats(go2_handle* h, float* host_out, int n, void* stream) {
+// Enqueue: accumulator row -> pinned slot, then clear the accumulator (stream-ordered after the copy).
+int go2_read_stats_async(go2_handle* h, int slot, void* stream) {
     cudaStream_t s = (cudaStream_t)stream;
+    if (slot < 0 || slot >= N_STAT_SLOTS) { h->err = "bad stats slot"; return -2; }
+    if (cudaSetDevice(h->device) != cudaSuccess) { h->err = "cudaSetDevice"; return -1; }
+    float* acc = (float*)h->bf.p[B_STATS] + 2 * STATS_LEN;
+    if (!ck(h, cudaMemcpyAsync(h->h_stats + slot * STATS_LEN, acc, sizeof(float) * STATS_LEN, cudaMemcpyDeviceToHost, s), "D2H stats")) return -1;
+    if (!ck(h, cudaMemsetAsync(acc, 0, sizeof(float) * STATS_LEN, s), "clear stats")) return -1;
+    return ck(h, cudaEventRecord(h->stat_ev[slot], s), "stats event") ? 0 : -1;
+}
+
+// Wait for the slot's copy and hand it out.  `block` = 0: returns 1 without waiting if the copy has not finished.
+int go2_stats_fetch(go2_handle* h, int slot, float* host_out, int n, int block) {
+    if (slot < 0 || slot >= N_STAT_SLOTS) { h->err = "bad stats slot"; return -2; }
+    if (!block) {
+        cudaError_t q = cudaEventQuery(h->stat_ev[slot]);
+        if (q == cudaErrorNotReady) return 1;
+        if (!ck(h, q, "stats query")) return -1;
+    } else if (!ck(h, cudaEventSynchronize(h->stat_ev[slot]), "stats wait")) return -1;
     if (n > STATS_LEN) n = STATS_LEN;
-    if (!ck(h, cudaMemcpyAsync(h->h_stats, h->bf.p[B_STATS], sizeof(float) * n, cudaMemcpyDeviceToHost, s), "D2H stats")) return -1;
-    if (!ck(h, cudaStreamSynchronize(s), "stats sync")) return -1;
-    memcpy(host_out, h->h_stats, sizeof(float) * n);
+    memcpy(host_out, h->h_stats + slot * STATS_LEN, sizeof(float) * n);
     return 0;
 }
 
-int go2_export_links(go2_handle* h, const void* params, int params_bytes, void* stream) {
-    if (params_bytes != (int)sizeof(StepParams)) { h->err = "StepParams size mismatch"; return -2; }
-    StepParams sp;
-    memcpy(&sp, params, sizeof(sp));
+int go2_read_stats(go2_handle* h, float* host_out, int n, void* stream) {
+    int r = go2_read_stats_async(h, 0, stream);
+    if (r) return r;
+    return go2_stats_fetch(h, 0, host_out, n, 1);
+}
+
+int go2_export_links(go2_handle* h, void* stream) {
     int B = h->cfg.num_envs;
-    go2_links_kernel<<<(B + GO2_WARPS - 1) / GO2_WARPS, GO2_WARPS * 32, GO2_WARPS * sizeof(WarpS), (cudaStream_t)stream>>>(h->d_model, sp, h->bf);
+    if (cudaSetDevice(h->device) != cudaSuccess) { h->err = "cudaSetDevice"; return -1; }
+    go2_links_kernel<<<(B + 127) / 128, 128, 0, (cudaStream_t)stream>>>(h->d_model, h->parity, h->bf);
     h->launches += 1;
     return ck(h, cudaGetLastError(), "go2_links_kernel") ? 0 : -1;
 }
 
 int go2_set_terrain(go2_handle* h, const float* hf_m, int rows, int cols, float h_scale, const float* origin3) {
     if (!h || !hf_m || rows < 2 || cols < 2 || h_scale <= 0.0f) return -1;
-    if (h->layout == 1) { h->err = "terrain is only implemented by the thread-per-env layout"; return -2; }
     cudaSetDevice(h->device);
     if (h->d_hf) cudaFree(h->d_hf);
     size_t n = (size_t)rows * cols;
@@ -305,6 +357,11 @@ void go2_phase_clocks(unsigned long long* out8) {
     cudaMemcpyToSymbol(go2::g2_phase_clk, z, sizeof(z));
 }
 #endif
+
+// launch shape of the step kernel: [blocks, threads per block, 255-register instantiation?]
+void go2_launch_shape(go2_handle* h, int* out3) {
+    out3[0] = h->nblocks; out3[1] = h->tpb; out3[2] = h->small;
+}
 
 long long go2_launch_count(go2_handle* h) { return h ? h->launches : 0; }
 

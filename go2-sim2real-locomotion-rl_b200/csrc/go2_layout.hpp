@@ -23,8 +23,10 @@ inline void compute_layout(const EnvConfig& c, int* dtype, int* rows, int* cols)
     set(B_FOOT_CONTACT, 2, B, 4); set(B_LAST_FOOT_CONTACT, 2, B, 4); set(B_AIR_TIME, 0, B, 4);
     set(B_EP_SUMS, 0, B, c.n_rew > 0 ? c.n_rew : 1); set(B_ERRNO, 1, B, 1);
     set(B_LINK_POS, 0, B, NLINK * 3); set(B_LINK_VEL, 0, B, NLINK * 3); set(B_CONTACT_FORCE, 0, B, NLINK * 3);
-    set(B_TORQUE, 0, B, NHINGE); set(B_STATS, 0, 1, STATS_LEN); set(B_NCONTACT, 1, B, 1); set(B_NNEWTON, 1, B, 1);
+    set(B_TORQUE, 0, B, NHINGE); set(B_STATS, 0, 3, STATS_LEN); set(B_NCONTACT, 1, B, 1); set(B_NNEWTON, 1, B, 1);
     set(B_TERRAIN_ROW, 1, B, 1); set(B_LAST_X, 0, B, 1);
+    set(B_GLOBALS, 0, 2, GLOBALS_LEN); set(B_REW_TERMS, 0, c.export_rew_terms ? B : 1, c.n_rew > 0 ? c.n_rew : 1);
+    set(B_REPLAY, 0, c.replay_rows > 0 ? c.replay_rows : 1, REPLAY_LEN); set(B_FK_FRESH, 2, B, 1); set(B_EXT_FORCE, 0, B, 4);
 }
 
 inline size_t compute_offsets(const int* dtype, const int* rows, const int* cols, size_t* offs) {
@@ -57,6 +59,12 @@ inline void init_arena(const EnvConfig& c, const size_t* offs, char* a) {
     for (int b = 0; b < B; ++b) dl[b] = 1;
     unsigned char* rb = (unsigned char*)(a + offs[B_RESET]);
     for (int b = 0; b < B; ++b) rb[b] = 1;
+    unsigned char* ff = (unsigned char*)(a + offs[B_FK_FRESH]);
+    for (int b = 0; b < B; ++b) ff[b] = 1;
+    float* gl = (float*)(a + offs[B_GLOBALS]);  // friction 1 on both entities (URDF default), no shifts
+    for (int s = 0; s < 2; ++s) gl[s * GLOBALS_LEN + G_FRIC_GROUND] = gl[s * GLOBALS_LEN + G_FRIC_ROBOT] = 1.0f;
+    float* ex = (float*)(a + offs[B_EXT_FORCE]);
+    for (int b = 0; b < B; ++b) ex[b * 4] = -1.0f;
 }
 
 }  // namespace go2

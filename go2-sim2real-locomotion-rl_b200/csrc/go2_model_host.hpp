@@ -8,10 +8,6 @@ namespace go2 {
 
 inline bool unpack_model(Go2Model& m, const int32_t* iv, int n_iv, const double* fv, int n_fv) {
     memset(&m, 0, sizeof(m));
-    {
-        const char* fd = getenv("GO2_B200_FORCE_DENSE");  // test hook: exercise the dense solver path on every env
-        m.force_dense = (fd && fd[0] == '1') ? 1 : 0;
-    }
     int k = 0, f = 0;
     int nl = iv[k++], ng = iv[k++], np = iv[k++];
     if (nl != NLINK || ng != NGEOM || np > MAX_PAIRS_STATIC) return false;

@@ -34,6 +34,8 @@ struct Phys {
     float pd_kp, pd_kv;
     v3 ext_f, ext_t;        // -cfrc_applied of the pushed link (force, torque about root COM)
     int ext_link;
+    v3 ext2_f, ext2_t;      // second slot: apply_links_external_force from the host (B_EXT_FORCE)
+    int ext2_link;
     // kinematics
     v3 lpos[NLINK];
     q4 lquat[NLINK];
@@ -91,7 +93,10 @@ struct Phys {
 // ---------------------------------------------------------------------------------------------------
 // Kinematics: link poses, root COM, composite-frame inertias, motion subspaces (cdof).
 // ---------------------------------------------------------------------------------------------------
-G2_HDN void kinematics(const Go2Model& m, const float* mass_shift, const float* com_shift, Phys& p) {
+// `gl` = the global physics DR slot in force (B_GLOBALS): link mass shifts and the base COM shift.
+G2_HDN void kinematics(const Go2Model& m, const float* __restrict__ gl, Phys& p) {
+    const float* mass_shift = gl + G_MASS_SHIFT;
+    const float* com_shift = gl + G_COM_SHIFT;
     // base (free joint): pose straight from qpos, quaternion renormalised
     p.lpos[0] = mk3(p.qpos[0], p.qpos[1], p.qpos[2]);
     p.lquat[0] = qnormalize(mk4(p.qpos[3], p.qpos[4], p.qpos[5], p.qpos[6]));
@@ -324,6 +329,10 @@ G2_HDN void smooth_dynamics(const Go2Model& m, Phys& p) {
         if (l == p.ext_link) {
             fv[l] = fv[l] - p.ext_f;
             fa[l] = fa[l] - p.ext_t;
+        }
+        if (l == p.ext2_link) {
+            fv[l] = fv[l] - p.ext2_f;
+            fa[l] = fa[l] - p.ext2_t;
         }
     }
     G2_UNROLL

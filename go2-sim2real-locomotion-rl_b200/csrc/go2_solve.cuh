@@ -242,23 +242,14 @@ G2_HDN void assemble_rows_a(const Go2Model& m, Phys& p) {
     p.n_rows = r;
 }
 
-#if defined(GO2_LS_STATS) && !defined(__CUDA_ARCH__)
-static long g_pairkind[4] = {0};  // contacts: ground-robot, base-leg, same leg, two legs
-#endif
 // Picks the row format (arrow unless two different legs touch each other) and builds the rows.
-G2_HD void assemble_constraints(const Go2Model& m, Phys& p) {
+G2_HD void assemble_constraints(const Go2Model& m, Phys& p, int force_dense) {
     int arrow = 1;
     for (int ic = 0; ic < p.n_contacts; ++ic) {
         int a = p.con[ic].la, b = p.con[ic].lb;
         if (a > 0 && b > 0 && ((a - 1) & 3) != ((b - 1) & 3)) arrow = 0;
-#if defined(GO2_LS_STATS) && !defined(__CUDA_ARCH__)
-        g_pairkind[(a < 0 || b < 0) ? 0 : (a == 0 || b == 0) ? 1 : (((a - 1) & 3) == ((b - 1) & 3)) ? 2 : 3]++;
-#endif
     }
-#ifdef G2_FORCE_DENSE
-    arrow = 0;
-#endif
-    if (m.force_dense) arrow = 0;
+    if (force_dense) arrow = 0;
     p.arrow = arrow;
     if (arrow) assemble_rows_a(m, p);
     else assemble_rows<false>(m, p);
@@ -298,22 +289,12 @@ G2_HD void update_constraint(Phys& p, const float* qacc, const float* Ma, float*
     p.cost = gauss + ccost;
 }
 
-// G2_H_REGS (experiment): the Cholesky factor lives in a function-local array of solve_constraints and the helpers are
-// force-inlined, so that with 255 registers the compiler can keep it in registers across the Newton loop.
-#ifdef G2_H_REGS
-#define G2_HSOLVE G2_HD
-#else
 #define G2_HSOLVE G2_HDN
-#endif
 
 // H = M + J^T D J over active rows, then dense Cholesky H = L L^T; assembled and factored in registers,
 // L written to p.H once.
 G2_HSOLVE void hessian_factor(Phys& p, float* Hs) {
-#ifdef G2_H_REGS
-    float* H = Hs;
-#else
     float H[NTRI];
-#endif
     G2_UNROLL_H
     for (int k = 0; k < NTRI; ++k) H[k] = p.M[k];
     int n = p.n_rows;
@@ -347,10 +328,8 @@ G2_HSOLVE void hessian_factor(Phys& p, float* Hs) {
             H[tri(j, i)] = (H[tri(j, i)] - dt) * inv;
         }
     }
-#ifndef G2_H_REGS
     G2_UNROLL_H
     for (int k = 0; k < NTRI; ++k) Hs[k] = H[k];
-#endif
 }
 
 // rank-1 up/down-date of the Cholesky factor for row c; returns false if a downdate degenerated
@@ -637,16 +616,6 @@ G2_HD void update_gradient_a(Phys& p, const float* Ma, const float* qfc, float* 
     }
 }
 
-#if defined(GO2_LS_STATS) && !defined(__CUDA_ARCH__)
-// host-only debugging counters of the line search (tests/host_emul with -DGO2_LS_STATS)
-static long g_ls_calls = 0, g_lsA[64] = {0}, g_lsB[64] = {0}, g_lsend[4] = {0};
-static long g_nfl[64] = {0}, g_refac[3] = {0};
-#define G2_LS_COUNT(nA, nB, k) (g_ls_calls++, g_lsA[nA]++, g_lsB[nB]++, g_lsend[k]++)
-#define G2_NT_COUNT(nfl, over, fail) (g_nfl[(nfl) < 63 ? (nfl) : 63]++, g_refac[0] += (over), g_refac[1] += (fail), g_refac[2]++)
-#else
-#define G2_NT_COUNT(nfl, over, fail)
-#define G2_LS_COUNT(nA, nB, k)
-#endif
 // The line search stops on |derivative| < gtol with gtol at fp32 rounding level (LS_TOL * SOLVER_TOL).  That test is
 // met through the exact cancellation of SEPARATELY rounded products; with fused multiply-adds the residual never
 // cancels and 13 % of the searches run to the 50-evaluation cap (measured, host build with -mfma: 0 % without).  The
@@ -654,17 +623,11 @@ static long g_nfl[64] = {0}, g_refac[3] = {0};
 #if defined(__CUDA_ARCH__)
 G2_HD float mul_nf(float a, float b) { return __fmul_rn(a, b); }
 G2_HD float add_nf(float a, float b) { return __fadd_rn(a, b); }
-#elif defined(G2_HOST_FMA_TEST)
-G2_HD float mul_nf(float a, float b) { volatile float r = a * b; return r; }
-G2_HD float add_nf(float a, float b) { volatile float r = a + b; return r; }
 #else
 G2_HD float mul_nf(float a, float b) { return a * b; }
 G2_HD float add_nf(float a, float b) { return a + b; }
 #endif
-#ifndef G2_LS_REG
-#define G2_LS_REG 16
-#endif
-constexpr int LS_REG = G2_LS_REG;  // rows of the line search kept in registers (16 = 4 contacts)
+constexpr int LS_REG = 16;  // rows of the line search kept in registers (16 = 4 contacts)
 struct LsPt {
     float alpha, cost, d0, d1;
 };
@@ -793,10 +756,7 @@ G2_HD float linesearch(const Go2Model& m, Phys& p, const float* search, const fl
     }
     // ---- loop B: three-point refinement of the bracket [p1, p2]
     float a[3] = {add_nf(p1.alpha, -(p1.d0 / p1.d1)), p1.alpha, mul_nf(add_nf(p1.alpha, p2.alpha), 0.5f)};
-    int nA = ls_it, nB = 0, endk = finished ? 0 : 3;
-    (void)nA; (void)nB; (void)endk;
     while (!finished && ls_it < LS_ITERS) {
-        nB++;
         float t[3][3];
         G2_UNROLL
         for (int k = 0; k < 3; ++k) { t[k][0] = g0; t[k][1] = g1; t[k][2] = g2; }
@@ -830,7 +790,6 @@ G2_HD float linesearch(const Go2Model& m, Phys& p, const float* search, const fl
         if (found) {
             result = ba;
             finished = true;
-            endk = 1;
         } else {
             float n1, n2;
             int b1 = bracket_update(p1, cand, n1);
@@ -838,13 +797,11 @@ G2_HD float linesearch(const Go2Model& m, Phys& p, const float* search, const fl
             if (b1 == 0 && b2 == 0) {
                 result = a[2];
                 finished = true;
-                endk = 2;
             } else {
                 a[0] = n1; a[1] = n2; a[2] = mul_nf(add_nf(p1.alpha, p2.alpha), 0.5f);
             }
         }
     }
-    G2_LS_COUNT(nA, nB, endk);
     if (!finished) {
         if (p1.cost <= p2.cost && p1.cost < p0.cost) result = p1.alpha;
         else if (p2.cost <= p1.cost && p2.cost < p0.cost) result = p2.alpha;
@@ -857,9 +814,7 @@ constexpr int MAX_RANK1 = 6;  // more flips than this in one Newton iteration ->
 
 // Block-wide "does any thread still iterate": keeps the warps of a block in the same Newton iteration so that
 // they share instruction fetches (the solver body is ~60 KB of straight-line code).  Host: a single env.
-#if defined(__CUDA_ARCH__) && defined(G2_WARP_ANY)
-#define G2_BLOCK_ANY(x) (__any_sync(0xffffffffu, (x)))
-#elif defined(__CUDA_ARCH__)
+#if defined(__CUDA_ARCH__)
 #define G2_BLOCK_ANY(x) (__syncthreads_or((x) ? 1 : 0) != 0)
 #else
 #define G2_BLOCK_ANY(x) (x)
@@ -873,12 +828,7 @@ template <bool AR>
 G2_HDN void solve_constraints_t(const Go2Model& m, Phys& p, bool valid) {
     const int n = valid ? p.n_rows : 0;
     float qacc[NV], Ma[NV], qfc[NV], grad[NV], Mgrad[NV], search[NV], mv[NV];
-#ifdef G2_H_REGS
-    float Hloc[NTRI];
-    float* Hs = Hloc;
-#else
     float* Hs = p.H;
-#endif
     if (valid) {
         bool ws = n > 0 && p.warm;
         G2_UNROLL
@@ -922,7 +872,6 @@ G2_HDN void solve_constraints_t(const Go2Model& m, Phys& p, bool valid) {
                     float sg = p.act[c] ? 1.0f : -1.0f;
                     if (!(AR ? hessian_rank1_a(p, c, sg) : hessian_rank1(p, Hs, c, sg))) refactor = true;
                 }
-                if (!first) G2_NT_COUNT(nfl, nfl > MAX_RANK1 ? 1 : 0, (refactor && nfl <= MAX_RANK1) ? 1 : 0);
                 if (refactor) {
                     if (AR) hessian_factor_a(p);
                     else hessian_factor(p, Hs);

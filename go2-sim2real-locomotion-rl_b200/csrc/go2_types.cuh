@@ -46,7 +46,7 @@ constexpr int LS_ITERS = 50;
 constexpr float LS_TOL = 1e-2f;
 
 enum GeomType { GEOM_SPHERE = 1, GEOM_CYLINDER = 3, GEOM_BOX = 5, GEOM_TERRAIN = 7 };
-enum ErrBits { ERR_CPAIR_OVERFLOW = 1, ERR_CONTACT_OVERFLOW = 2, ERR_NAN_FORCE = 4, ERR_NAN_ACC = 8 };
+enum ErrBits { ERR_CPAIR_OVERFLOW = 1, ERR_CONTACT_OVERFLOW = 2, ERR_NAN_FORCE = 4, ERR_NAN_ACC = 8, ERR_GJK_WANTED = 16 };
 enum EnvKind { ENV_WALK = 0, ENV_STAIR = 1, ENV_BASE = 2 };
 enum CtrlKind { CTRL_MANUAL_PLS = 0, CTRL_MANUAL_FIXED = 1, CTRL_GENESIS_PD = 2 };
 
@@ -67,7 +67,6 @@ struct Go2Model {
     int terrain_on, terrain_r, terrain_c;
     float terrain_sh, terrain_org[3], terrain_zmax, terrain_zbot;  // zbot = min(hf) - 1 (prism bottoms)
     const float* terrain_hf;
-    int force_dense;  // test hook (GO2_B200_FORCE_DENSE=1): every env uses the dense solver path (go2_solve.cuh)
 };
 
 // Reward terms (union of the walk / stair / base env zoos).
@@ -123,6 +122,13 @@ struct EnvConfig {
     int scan_nx, scan_ny;
     float scan_x0, scan_x1, scan_y0, scan_y1;
     float lin_vel_z_deadzone;
+    // global (one value for every env, Genesis semantics) physics DR applied by the post-pass kernel whenever at least one
+    // env reset in the tick (go2_env_walk.py:737-756, 803-848): which draws exist, the friction throttle, the hip links
+    int has_friction_dr, has_mass_dr, has_com_dr, has_leg_mass_dr, global_dr_interval;
+    int hip_link[4];          // robot-local link of each per-leg mass shift, cfg order FR, FL, RR, RL
+    int solver_dense;         // 1 = every env uses the dense 18x18 Newton path (diagnostic; default 0 = arrow unless legs touch)
+    int export_rew_terms;     // 1 = B_REW_TERMS receives every scaled reward term of the tick
+    int replay_rows;          // rows of B_REPLAY (0 = no replay buffer; num_envs = draws can be replayed, see StepParams.replay_on)
 };
 
 // Per-step parameters: everything the reference keeps as host-side python scalars (curriculum-driven
@@ -141,15 +147,27 @@ struct StepParams {
     float kpf_lo, kpf_hi, kdf_lo, kdf_hi, ms_lo, ms_hi, go_lo, go_hi;
     float kp_lo, kp_hi, kd_lo, kd_hi;  // fixed-gain manual PD (non-PLS) base gain ranges
     int delay_lo, delay_hi;
-    // global physics DR currently in force (Genesis semantics: one value for all envs)
-    float friction;            // applied to every geom (ground + robot)
-    float mass_shift[NLINK];   // base + the four hips used by the envs
-    float com_shift[3];        // base link COM shift
     float kp_genesis, kd_genesis;  // dofs kp/kv for CTRL_GENESIS_PD
     int do_physics;            // 0 => reset-only launch
     int force_reset_all;
     int terrain_max_row;       // stair: int(curriculum_level * (rows - 1))
     int lock_terrain_rows;     // stair eval: keep each env's row across resets
+    // candidates of the global physics DR (already lerped with this tick's t_sample); the post-pass kernel puts them in
+    // force if an env reset in this tick - B_GLOBALS holds the values in force
+    float cand_friction, cand_mass, cand_com[3], cand_leg[4];
+    int parity;                // double-buffer index of B_GLOBALS / B_STATS for this tick (filled by the library)
+    int defer_post;            // 1 = go2_step launches the step kernel only; the caller reduces B_STATS over ranks, then go2_post
+    int replay_on;             // 1 = every random draw of the tick is read from B_REPLAY instead of Philox (fixture replay)
+    int ext_on;                // 1 = B_EXT_FORCE holds external link forces for this tick (apply_links_external_force)
 };
+
+// B_GLOBALS: [2][GLOBALS_LEN] global physics DR values in force (slot = StepParams.parity)
+constexpr int G_FRIC_GROUND = 0, G_FRIC_ROBOT = 1, G_MASS_SHIFT = 2, G_COM_SHIFT = G_MASS_SHIFT + NLINK, G_DR_COUNTER = G_COM_SHIFT + 3,
+              GLOBALS_LEN = 20;
+
+// B_REPLAY row layout (one row per env): the values the reference drew in the replayed tick
+constexpr int RP_ACT_NOISE = 0, RP_OBS_NOISE = 12, RP_PUSH = 61 /* fx fy duration */, RP_CMD = 64, RP_KPF = 67, RP_KDF = 79, RP_MS = 91,
+              RP_GO = 103, RP_DELAY = 106, RP_INIT_Z = 107, RP_ROLL = 108, RP_PITCH = 109, RP_CMD_RESET = 110, RP_ROW = 113, RP_KP = 114,
+              RP_KD = 115, REPLAY_LEN = 116;
 
 }  // namespace go2

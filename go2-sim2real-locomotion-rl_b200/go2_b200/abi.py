@@ -16,8 +16,7 @@ MAX_REW, NOBS_MAX, MAX_CPAIRS = 32, 49, 24
 MAX_TERRAIN_ROWS = 16
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-# GO2_B200_LIB overrides the in-tree library (kernel-variant experiments: other block sizes / register caps)
-CUDA_LIB_PATH = os.environ.get("GO2_B200_LIB") or os.path.join(_HERE, "libgo2_b200.so")
+CUDA_LIB_PATH = os.path.join(_HERE, "libgo2_b200.so")
 
 ENV_WALK, ENV_STAIR, ENV_BASE = 0, 1, 2
 CTRL_MANUAL_PLS, CTRL_MANUAL_FIXED, CTRL_GENESIS_PD = 0, 1, 2
@@ -43,9 +42,14 @@ BUF_NAMES = [
     "base_euler", "kp_factors", "kd_factors", "motor_strength", "eff_kp", "eff_kd", "grav_off", "push_force", "cur_push",
     "push_remain", "delay", "foot_contact", "last_foot_contact", "air_time", "ep_sums", "errno", "link_pos", "link_vel",
     "contact_force", "torque", "stats", "ncontact", "nnewton", "terrain_row", "last_x",
+    "globals", "rew_terms", "replay", "fk_fresh", "ext_force",
 ]
 BUF = {n: i for i, n in enumerate(BUF_NAMES)}
 STATS_RESETS, STATS_TIMEOUTS, STATS_TRACKING, STATS_ERR, STATS_REW0 = 0, 1, 2, 3, 4
+# B_GLOBALS slot layout / B_REPLAY row layout (csrc/go2_types.cuh)
+G_FRIC_GROUND, G_FRIC_ROBOT, G_MASS_SHIFT, G_COM_SHIFT, G_DR_COUNTER, GLOBALS_LEN = 0, 1, 2, 15, 18, 20
+RP_ACT_NOISE, RP_OBS_NOISE, RP_PUSH, RP_CMD, RP_KPF, RP_KDF, RP_MS, RP_GO, RP_DELAY = 0, 12, 61, 64, 67, 79, 91, 103, 106
+RP_INIT_Z, RP_ROLL, RP_PITCH, RP_CMD_RESET, RP_ROW, RP_KP, RP_KD, REPLAY_LEN = 107, 108, 109, 110, 113, 114, 115, 116
 
 _i, _f, _u = C.c_int32, C.c_float, C.c_uint32
 
@@ -73,6 +77,8 @@ class EnvConfig(C.Structure):
         ("has_terrain", _i), ("n_terrain_rows", _i), ("row_center", (_f * 3) * MAX_TERRAIN_ROWS),
         ("scan_nx", _i), ("scan_ny", _i), ("scan_x0", _f), ("scan_x1", _f), ("scan_y0", _f), ("scan_y1", _f),
         ("lin_vel_z_deadzone", _f),
+        ("has_friction_dr", _i), ("has_mass_dr", _i), ("has_com_dr", _i), ("has_leg_mass_dr", _i), ("global_dr_interval", _i),
+        ("hip_link", _i * 4), ("solver_dense", _i), ("export_rew_terms", _i), ("replay_rows", _i),
     ]
 
 
@@ -84,14 +90,17 @@ class StepParams(C.Structure):
         ("kpf_lo", _f), ("kpf_hi", _f), ("kdf_lo", _f), ("kdf_hi", _f), ("ms_lo", _f), ("ms_hi", _f), ("go_lo", _f), ("go_hi", _f),
         ("kp_lo", _f), ("kp_hi", _f), ("kd_lo", _f), ("kd_hi", _f),
         ("delay_lo", _i), ("delay_hi", _i),
-        ("friction", _f), ("mass_shift", _f * NLINK), ("com_shift", _f * 3), ("kp_genesis", _f), ("kd_genesis", _f),
+        ("kp_genesis", _f), ("kd_genesis", _f),
         ("do_physics", _i), ("force_reset_all", _i), ("terrain_max_row", _i), ("lock_terrain_rows", _i),
+        ("cand_friction", _f), ("cand_mass", _f), ("cand_com", _f * 3), ("cand_leg", _f * 4),
+        ("parity", _i), ("defer_post", _i), ("replay_on", _i), ("ext_on", _i),
     ]
 
 
 _EXPORTS = [
     "go2_abi_sizes", "go2_create", "go2_destroy", "go2_last_error", "go2_buffer_info", "go2_step", "go2_reset_all",
     "go2_step_host", "go2_read_stats", "go2_export_links", "go2_launch_count", "go2_set_terrain",
+    "go2_post", "go2_tick_parity", "go2_read_stats_async", "go2_stats_fetch", "go2_launch_shape",
 ]
 # include/go2_policy.h (CUDA library only; the host-emulation test library has no tensor cores to emulate)
 _POLICY_EXPORTS = ["go2_mlp_create", "go2_mlp_destroy", "go2_mlp_forward", "go2_policy_act", "go2_policy_act_critic", "go2_gae"]

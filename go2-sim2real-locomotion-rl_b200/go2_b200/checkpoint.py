@@ -93,18 +93,18 @@ def save_runner_checkpoint(path, actor, critic, std, optimizer_state=None, it=0,
 # ---------------------------------------------------------------------------------------------------
 # env state (additive)
 # ---------------------------------------------------------------------------------------------------
-_HOST_ATTRS = ["_step_count", "_action_history_write_idx", "_push_counter", "_global_dr_reset_counter", "_friction", "_curr_ep_total",
-               "_curr_timeout_total", "_curr_tracking_sum", "_curr_tracking_n", "_lock_terrain_rows"]
+_HOST_ATTRS = ["_step_count", "_action_history_write_idx", "_push_counter", "_curr_ep_total", "_curr_timeout_total", "_curr_tracking_sum",
+               "_curr_tracking_n", "_lock_terrain_rows", "_ticks_since_stats"]
 
 
 def env_state_dict(env):
-    """Everything needed to continue `env.step` bit-for-bit: all device buffers + host-side scalars."""
-    st = {"buffers": {k: v.detach().cpu().clone() for k, v in env.core.buf.items() if k != "stats"},
+    """Everything needed to continue `env.step` bit-for-bit: all device buffers (they include the global physics DR in
+    force and the statistics accumulator) + the double-buffer parity + host-side scalars."""
+    env.flush_stats()
+    st = {"buffers": {k: v.detach().cpu().clone() for k, v in env.core.buf.items()},
           "host": {a: getattr(env, a) for a in _HOST_ATTRS if hasattr(env, a)},
+          "parity": env.core.tick_parity(),
           "rng": env._np_rng.bit_generator.state}
-    for a in ("_mass_shift", "_com_shift"):
-        if hasattr(env, a):
-            st["host"][a] = np.array(getattr(env, a)).tolist()
     if hasattr(env, "curriculum"):
         c = env.curriculum
         st["curriculum"] = {"level": c.level, "ema": dict(c.ema), "_ready_streak": c._ready_streak, "_hard_streak": c._hard_streak,
@@ -115,11 +115,11 @@ def env_state_dict(env):
 def load_env_state_dict(env, st):
     for k, v in st["buffers"].items():
         env.core.buf[k].copy_(v.to(env.device))
+    if st.get("parity", 0) != env.core.tick_parity():  # rows of the double-buffered tables swap roles with the parity
+        for k in ("globals", "stats"):
+            env.core.buf[k][:2] = env.core.buf[k][:2].flip(0)
     for a, v in st["host"].items():
-        if a in ("_mass_shift", "_com_shift"):
-            getattr(env, a)[:] = np.asarray(v, dtype=np.float32)
-        else:
-            setattr(env, a, v)
+        setattr(env, a, v)
     env._np_rng.bit_generator.state = st["rng"]
     if "curriculum" in st and hasattr(env, "curriculum"):
         env.curriculum.__dict__.update(st["curriculum"])

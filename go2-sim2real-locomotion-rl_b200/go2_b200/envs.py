@@ -33,11 +33,13 @@ def _lerp_range(a, b, t):
     return [_lerp(a[0], b[0], t), _lerp(a[1], b[1], t)]
 
 
-class Curriculum:
-    """Metric-gated difficulty level (behaviour of go2_env_walk.py:42-151 CurriculumManager)."""
+class CurriculumManager:
+    """Metric-gated difficulty level (behaviour of go2_env_walk.py:42-151 CurriculumManager; same constructor).
+    `rng` (optional numpy Generator) drives sample_level(); the reference draws from python's `random` module."""
 
-    def __init__(self, cfg, rng):
-        c = cfg or {}
+    def __init__(self, cfg: dict = None, rng=None):
+        self.cfg = cfg or {}
+        c = self.cfg
         g = c.get
         self.enabled = bool(g("enabled", False))
         self.level = float(g("level_init", 0.0))
@@ -49,7 +51,7 @@ class Curriculum:
         self.mix = (float(g("mix_prob_current", 0.80)), float(g("mix_level_low", 0.0)), float(g("mix_level_high", 0.6)))
         self.ema = {"timeout_rate": None, "tracking": None, "fall_rate": None}
         self._ready_streak = self._hard_streak = self._cooldown = 0
-        self._rng = rng
+        self._rng = rng if rng is not None else np.random.default_rng()
 
     def sample_level(self):
         if not self.enabled:
@@ -88,6 +90,14 @@ class Curriculum:
         return {"enabled": self.enabled, "level": float(self.level), "timeout_rate_ema": self.ema["timeout_rate"],
                 "tracking_ema": self.ema["tracking"], "fall_rate_ema": self.ema["fall_rate"]}
 
+    # attribute names of the reference class (go2_env_walk.py:58-90), read by logging code
+    timeout_rate_ema = property(lambda self: self.ema["timeout_rate"])
+    tracking_ema = property(lambda self: self.ema["tracking"])
+    fall_rate_ema = property(lambda self: self.ema["fall_rate"])
+
+
+Curriculum = CurriculumManager
+
 
 def _inv_quat(q):
     return [q[0], -q[1], -q[2], -q[3]]
@@ -108,7 +118,17 @@ class _Go2EnvBase:
     KIND = abi.ENV_WALK
 
     def __init__(self, num_envs, env_cfg, obs_cfg, reward_cfg, command_cfg, show_viewer=False, *, device=None, seed=1,
-                 env_offset=0, total_envs=None, lib_path=None, stats_sync_interval=1, sync_ranks=True):
+                 env_offset=0, total_envs=None, lib_path=None, stats_sync_interval=1, sync_ranks=True, core_cls=Go2Core,
+                 replay=False, export_reward_terms=False, solver_dense=False):
+        """Keyword-only extras (none is needed by the train / eval scripts):
+        stats_sync_interval  ticks between reads of the device-side episode statistics.  1 = read (and wait) every tick, the
+                             reference's timing for extras["episode"] and the curriculum; k > 1 = an asynchronous double-buffered
+                             read every k ticks (no tick waits for the host; the curriculum sees the numbers k ticks late).
+        sync_ranks           with torch.distributed initialised: sum the per-tick statistics over the ranks (env shards) on the
+                             device, so that every rank runs the same curriculum / global-DR state machine.
+        replay               allocate the draw-replay buffer (fixture replay, see replay_draws()).
+        export_reward_terms  keep every scaled reward term of the tick in `reward_terms` [B, n_rew].
+        solver_dense         diagnostic: every env takes the dense 18x18 Newton path."""
         if show_viewer:
             raise RuntimeError("show_viewer=True: no graphics stack on this box (viewer unavailable)")
         self.num_envs = int(num_envs)
@@ -128,9 +148,17 @@ class _Go2EnvBase:
         self._env_offset = int(env_offset)
         self._total_envs = int(total_envs) if total_envs is not None else self.num_envs
         self._lib_path = lib_path
+        self._core_cls = core_cls
         self.stats_sync_interval = int(stats_sync_interval)
         self._sync_ranks = bool(sync_ranks)
+        self._opt_replay, self._opt_rew_terms, self._opt_dense = bool(replay), bool(export_reward_terms), bool(solver_dense)
         self._step_count = 0
+        self._ticks_since_stats = 0
+        self._stats_slot = 0
+        self._stats_inflight = [False, False]
+        self._replay_next = False
+        self._ext_on = False
+        self._kernel_event_hook = None
         self.extras = {"observations": {}}
 
     # ---- cfg -> EnvConfig fields common to all flavours
@@ -178,12 +206,17 @@ class _Go2EnvBase:
         c.rp[1] = float(r.get("jump_apex_sigma", 0.05))
         c.seed_lo = self._seed & 0xFFFFFFFF
         c.seed_hi = (self._seed >> 32) & 0xFFFFFFFF
+        c.replay_rows = self.num_envs if self._opt_replay else 0
+        c.export_rew_terms = int(self._opt_rew_terms)
+        c.solver_dense = int(self._opt_dense)
 
     def _bind(self, c: abi.EnvConfig):
-        self.core = Go2Core(c, device=self.device, model=self._model, lib_path=self._lib_path)
+        self.core = self._core_cls(c, device=self.device, model=self._model, lib_path=self._lib_path)
         b = self.core.buf
         B = self.num_envs
-        self.obs_buf = b["obs"]
+        self._obs_view = b["obs"]   # the kernel's persistent output row; obs_buf is re-bound to a fresh copy every step
+        self.obs_buf = b["obs"].clone()
+        self.reward_terms = b["rew_terms"] if self._opt_rew_terms else None
         self.rew_buf = b["rew"].view(-1)
         self.reset_buf = b["reset"].view(-1).view(torch.bool)
         self._episode_length_buf = b["ep_len"].view(-1)
@@ -227,11 +260,107 @@ class _Go2EnvBase:
         """Same tick through the C ABI with HOST buffers (numpy or pinned torch CPU tensors): the action H2D copy
         and the obs / rew / done D2H copies happen inside the call, which returns after the stream is idle."""
         sp = self._make_params(physics=True)
-        self.core.step_host(h_actions, sp, h_obs, h_rew, h_done, h_priv, h_timeouts)
+        if self._multi_rank():
+            # the statistics all-reduce sits between the two launches: same copies, issued from here on the same stream
+            b = self.core.buf
+            b["actions_in"].copy_(torch.as_tensor(h_actions).reshape(b["actions_in"].shape), non_blocking=True)
+            self._launch(b["actions_in"], sp)
+            pairs = [(h_rew, b["rew"].view(-1)), (h_done, b["reset"].view(-1)), (h_timeouts, b["timeout"].view(-1)), (h_obs, b["obs"]), (h_priv, b["priv"])]
+            for dst, src in pairs:
+                if dst is not None:
+                    torch.as_tensor(dst).copy_(src, non_blocking=True)
+            torch.cuda.current_stream(self.device).synchronize()
+        else:
+            self.core.step_host(h_actions, sp, h_obs, h_rew, h_done, h_priv, h_timeouts)
+            self._after_launch()
         self.actions = self.last_actions
-        if self.stats_sync_interval > 0 and self._step_count % self.stats_sync_interval == 0:
-            self._after_resets(self._read_stats())
+        self._stats_tick()
         return h_obs, h_rew, h_done, self.extras
+
+    # ---- one tick on the device: step kernel (+ statistics all-reduce over the env shards) + post-pass kernel
+    def _multi_rank(self):
+        import torch.distributed as dist
+
+        return self._sync_ranks and dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+
+    def _launch(self, actions, sp):
+        multi, hook = self._multi_rank(), self._kernel_event_hook
+        if actions is None:
+            sp.defer_post = int(multi)
+            self.core.reset_all(sp)
+        else:
+            sp.defer_post = int(multi or hook is not None)
+            if hook is not None:  # measurement aid: events bracketing the step kernel alone
+                e0, e1 = hook()
+                e0.record()
+            self.core.step(actions, sp)
+            if hook is not None:
+                e1.record()
+        if sp.defer_post:
+            if multi:
+                import torch.distributed as dist
+
+                # this tick's statistics row, summed over the env shards on the stream (NCCL) - no host synchronisation
+                dist.all_reduce(self.core.buf["stats"][self.core.tick_parity()])
+            self.core.post(sp)
+        self._after_launch()
+
+    def _after_launch(self):
+        if self._ext_on:  # clear_external_force after the tick's substeps (simulator.py:283)
+            ex = self.core.buf["ext_force"]
+            ex.zero_()
+            ex[:, 0] = -1.0
+            self._ext_on = False
+        self._replay_next = False
+
+    def _stats_tick(self):
+        """Host side of reset_idx that needs the episode statistics (curriculum aggregates, extras['episode'])."""
+        k = self.stats_sync_interval
+        if k <= 0:
+            return
+        self._ticks_since_stats += 1
+        if self._ticks_since_stats < k:
+            return
+        self._ticks_since_stats = 0
+        if k == 1:
+            self._after_resets(self.core.read_stats())
+            return
+        # asynchronous, double-buffered: enqueue this interval's read, consume the previous interval's (long complete)
+        cur, prev = self._stats_slot, self._stats_slot ^ 1
+        self.core.read_stats_async(cur)
+        self._stats_inflight[cur] = True
+        if self._stats_inflight[prev]:
+            self._after_resets(self.core.stats_fetch(prev, block=True))
+            self._stats_inflight[prev] = False
+        self._stats_slot = prev
+
+    def flush_stats(self):
+        """Consume every outstanding statistics read (blocking) - e.g. before reading extras at the end of a rollout."""
+        for slot in (self._stats_slot, self._stats_slot ^ 1):
+            if self._stats_inflight[slot]:
+                self._after_resets(self.core.stats_fetch(slot, block=True))
+                self._stats_inflight[slot] = False
+        self._after_resets(self.core.read_stats())
+        self._ticks_since_stats = 0
+
+    def replay_draws(self, rows):
+        """Fixture replay: the NEXT step reads every random draw from `rows` ([B, REPLAY_LEN], layout abi.RP_*) instead of Philox."""
+        if not self._opt_replay:
+            raise RuntimeError("construct the env with replay=True")
+        self.core.buf["replay"].copy_(torch.as_tensor(rows, device=self.device, dtype=torch.float32))
+        self._replay_next = True
+
+    # ---- global physics DR in force (device-resident, both double-buffer slots)
+    def _set_global(self, col, value):
+        # only the slot the next tick reads: the other one keeps the values the last closing FK ran on (go2_env.cuh, t_env_step)
+        self.core.buf["globals"][self.core.tick_parity(), col] = float(value)
+
+    def global_dr_values(self):
+        """Friction / mass / COM shifts currently in force (synchronises: a small D2H read)."""
+        g = self.core.buf["globals"][self.core.tick_parity()].tolist()
+        return {"friction_ground": g[abi.G_FRIC_GROUND], "friction_robot": g[abi.G_FRIC_ROBOT],
+                "mass_shift": g[abi.G_MASS_SHIFT:abi.G_MASS_SHIFT + abi.NLINK], "com_shift": g[abi.G_COM_SHIFT:abi.G_COM_SHIFT + 3],
+                "reset_counter": g[abi.G_DR_COUNTER]}
 
     def poll_errno(self):
         """Raise like Genesis' check_errno (rigid_solver.py:1189-1213) if any env hit an error bit."""
@@ -243,15 +372,6 @@ class _Go2EnvBase:
         if bits & 1:
             raise RuntimeError("Exceeding max number of colliding geom pairs per env.")
         return bits
-
-    def _read_stats(self):
-        """Per-tick episode statistics; with several ranks (env shards) they are summed over NCCL/gloo first so
-        that every rank runs the same curriculum / global-DR state machine."""
-        import torch.distributed as dist
-
-        if self._sync_ranks and dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
-            dist.all_reduce(self.core.buf["stats"])
-        return self.core.read_stats()
 
 
 class Go2EnvWalk(_Go2EnvBase):
@@ -304,6 +424,12 @@ class Go2EnvWalk(_Go2EnvBase):
                 c.foot_link[i] = self._foot_link_indices[i]
         self._has_leg_mass_dr = "leg_mass_shift_range" in e
         self._hip_link_indices = [link_names.index(n) for n in ("FR_hip", "FL_hip", "RR_hip", "RL_hip")] if self._has_leg_mass_dr else []
+        # global physics DR (one value for every env): applied on the device by the post-pass kernel
+        c.has_friction_dr, c.has_mass_dr, c.has_com_dr = int("friction_range" in e), int("mass_shift_range" in e), int("com_shift_range" in e)
+        c.has_leg_mass_dr = int(self._has_leg_mass_dr)
+        c.global_dr_interval = int((e.get("curriculum", {}) or {}).get("global_dr_update_interval", 200))
+        for i, l in enumerate(self._hip_link_indices):
+            c.hip_link[i] = l
         # DR maxima
         self.obs_noise_components = e.get("obs_noise", None)
         self.obs_noise_level_max = float(e.get("obs_noise_level", 0.0)) if self.obs_noise_components else 0.0
@@ -362,7 +488,7 @@ class Go2EnvWalk(_Go2EnvBase):
         # curriculum + DR ranges (go2_env_walk.py:457-514)
         self.curr_cfg = e.get("curriculum", {}) or {}
         cc = self.curr_cfg
-        self.curriculum = Curriculum(cc, self._np_rng)
+        self.curriculum = CurriculumManager(cc, self._np_rng)
         self._curr_ep_total, self._curr_timeout_total, self._curr_tracking_sum, self._curr_tracking_n = 0, 0.0, 0.0, 0
         self.curr_update_every_episodes = int(cc.get("update_every_episodes", 2048))
         kp_nom, kd_nom = float(e.get("kp", 60.0)), float(e.get("kd", 2.0))
@@ -380,11 +506,7 @@ class Go2EnvWalk(_Go2EnvBase):
         self.push_start = float(cc.get("push_start", 0.30))
         self.push_interval_s_easy = float(cc.get("push_interval_easy_s", 6.0))
         self._global_dr_update_interval = int(cc.get("global_dr_update_interval", 200))
-        self._global_dr_reset_counter = 0
-        # global physics DR currently in force (Genesis semantics: one value for every env)
-        self._friction = 1.0
-        self._mass_shift = np.zeros(abi.NLINK, dtype=np.float32)
-        self._com_shift = np.zeros(3, dtype=np.float32)
+        self._cand_override = None  # fixture replay: {"friction": f, "mass": m, "com": [3], "leg": [4]} for the next tick
         self._kp_genesis, self._kd_genesis = (0.0, 0.0) if self._use_manual_pd else (kp_nom, kd_nom)
         self._obs_noise_level_cur = self._action_noise_std_cur = 0.0
         self._push_enable_cur = False
@@ -493,12 +615,28 @@ class Go2EnvWalk(_Go2EnvBase):
         sp.go_lo, sp.go_hi = _lerp_range(self.gravity_offset_easy, self.gravity_offset_hard, t)
         sp.delay_lo = self._min_delay_steps
         sp.delay_hi = max(self._min_delay_steps, min(self._delay_max_cur, self._max_delay_steps))
-        sp.friction = float(self._friction)
-        for l in range(abi.NLINK):
-            sp.mass_shift[l] = float(self._mass_shift[l])
-        for j in range(3):
-            sp.com_shift[j] = float(self._com_shift[j])
         sp.kp_genesis, sp.kd_genesis = float(self._kp_genesis), float(self._kd_genesis)
+        # candidates of the global physics DR: what reset_idx would draw if an env resets in this tick
+        # (go2_env_walk.py:737-756,803-848); the post-pass kernel decides on the device
+        e, rng, ov = self.env_cfg, self._np_rng, self._cand_override or {}
+
+        def draw(easy, hard):
+            lo, hi = _lerp_range(easy, hard, t)
+            return float((hi - lo) * rng.random() + lo)
+
+        if "friction_range" in e:
+            sp.cand_friction = float(ov["friction"]) if "friction" in ov else draw(self.friction_easy, self.friction_hard)
+        if "mass_shift_range" in e:
+            sp.cand_mass = float(ov["mass"]) if "mass" in ov else draw(self.mass_easy, self.mass_hard)
+        if "com_shift_range" in e:
+            for j in range(3):
+                sp.cand_com[j] = float(ov["com"][j]) if "com" in ov else draw(self.com_easy, self.com_hard)
+        if self._has_leg_mass_dr:
+            for j in range(4):
+                sp.cand_leg[j] = float(ov["leg"][j]) if "leg" in ov else draw(self.leg_mass_easy, self.leg_mass_hard)
+        self._cand_override = None
+        sp.replay_on = int(self._replay_next)
+        sp.ext_on = int(self._ext_on)
         self._flavour_params(sp)
         self._step_count += 1
         return sp
@@ -521,26 +659,6 @@ class Go2EnvWalk(_Go2EnvBase):
                 if self.curriculum.update(tr, float(self._curr_tracking_sum / max(1, self._curr_tracking_n)), float(1.0 - tr)):
                     self._apply_curriculum_level()
                 self._curr_ep_total, self._curr_timeout_total, self._curr_tracking_sum, self._curr_tracking_n = 0, 0.0, 0.0, 0
-        t, e, rng = self._t_sample, self.env_cfg, self._np_rng
-        dr = self.extras.setdefault("domain_randomization", {})
-        if "friction_range" in e:
-            self._global_dr_reset_counter += n
-            if self._global_dr_reset_counter >= self._global_dr_update_interval:
-                self._global_dr_reset_counter = 0
-                lo, hi = _lerp_range(self.friction_easy, self.friction_hard, t)
-                self._friction = float((hi - lo) * rng.random() + lo)
-                dr["friction"] = self._friction
-        if "mass_shift_range" in e:
-            lo, hi = _lerp_range(self.mass_easy, self.mass_hard, t)
-            self._mass_shift[0] = (hi - lo) * rng.random() + lo
-            dr["mass_shift"] = float(self._mass_shift[0])
-        if "com_shift_range" in e:
-            lo, hi = _lerp_range(self.com_easy, self.com_hard, t)
-            self._com_shift[:] = [(hi - lo) * rng.random() + lo for _ in range(3)]
-        if self._has_leg_mass_dr:
-            lo, hi = _lerp_range(self.leg_mass_easy, self.leg_mass_hard, t)
-            for l in self._hip_link_indices:
-                self._mass_shift[l] = (hi - lo) * rng.random() + lo
         self.extras["episode"] = {"rew_" + name: float(stats[abi.STATS_REW0 + k]) / n for k, name in enumerate(self._reward_names)}
 
     def _critic_obs(self):
@@ -551,17 +669,19 @@ class Go2EnvWalk(_Go2EnvBase):
 
     def step(self, actions):
         sp = self._make_params(physics=True)
-        self.core.step(actions, sp)
+        self._launch(actions, sp)
         self.actions = self.last_actions  # after the tick last_actions holds the clipped policy output
-        if self.stats_sync_interval > 0 and self._step_count % self.stats_sync_interval == 0:
-            self._after_resets(self._read_stats())
+        # a fresh tensor every step, like the reference's `self.obs_buf = torch.cat(...)` (go2_env_walk.py:1084): rsl-rl keeps
+        # the reference to obs_t across env.step() until it stores the transition
+        self.obs_buf = self._obs_view.clone()
+        self._stats_tick()
         self.extras["observations"]["critic"] = self._critic_obs()
         return self.obs_buf, self.rew_buf, self.reset_buf, self.extras
 
     def reset(self):
         sp = self._make_params(physics=False)
-        self.core.reset_all(sp)
-        self._after_resets(self._read_stats())
+        self._launch(None, sp)
+        self.flush_stats()
         return self.obs_buf, None
 
 
@@ -674,10 +794,8 @@ class Go2EnvBaseFlavour(_Go2EnvBase):
             c.torque_limit[j] = 1e30
         self._bind(c)
         self._kp_genesis, self._kd_genesis = float(env_cfg["kp"]), float(env_cfg["kd"])
-        self._friction = 1.0
-        self._mass_shift = np.zeros(abi.NLINK, dtype=np.float32)
-        self._com_shift = np.zeros(3, dtype=np.float32)
         self.robot = _RobotFacade(self)
+        self.ground = _GroundFacade(self)
         self.scene = _SceneFacade(self)
 
     def _make_params(self, physics=True):
@@ -687,13 +805,10 @@ class Go2EnvBaseFlavour(_Go2EnvBase):
         cc = self.command_cfg
         for i, k in enumerate(("lin_vel_x_range", "lin_vel_y_range", "ang_vel_range")):
             sp.cmd_lo[i], sp.cmd_hi[i] = float(cc[k][0]), float(cc[k][1])
-        sp.friction = float(self._friction)
-        for l in range(abi.NLINK):
-            sp.mass_shift[l] = float(self._mass_shift[l])
-        for j in range(3):
-            sp.com_shift[j] = float(self._com_shift[j])
         sp.kp_genesis, sp.kd_genesis = float(self._kp_genesis), float(self._kd_genesis)
         sp.delay_lo = sp.delay_hi = 0
+        sp.replay_on = int(self._replay_next)
+        sp.ext_on = int(self._ext_on)
         self._step_count += 1
         return sp
 
@@ -709,17 +824,17 @@ class Go2EnvBaseFlavour(_Go2EnvBase):
 
     def step(self, actions):
         sp = self._make_params(physics=True)
-        self.core.step(actions, sp)
+        self._launch(actions, sp)
         self.actions = self.last_actions
-        if self.stats_sync_interval > 0 and self._step_count % self.stats_sync_interval == 0:
-            self._after_resets(self._read_stats())
+        self.obs_buf = self._obs_view.clone()  # fresh tensor per step (go2_env_base.py:175 re-binds obs_buf with torch.cat)
+        self._stats_tick()
         self.extras["observations"]["critic"] = self.obs_buf
         return self.obs_buf, self.rew_buf, self.reset_buf, self.extras
 
     def reset(self):
         sp = self._make_params(physics=False)
-        self.core.reset_all(sp)
-        self._after_resets(self._read_stats())
+        self._launch(None, sp)
+        self.flush_stats()
         return self.obs_buf, None
 
 
@@ -751,8 +866,13 @@ class _RobotFacade:
         e = self._env
         return torch.arange(e.num_envs, device=e.device) if envs_idx is None else torch.as_tensor(envs_idx, device=e.device).long()
 
+    def _refreshed(self, ii):
+        self._env.core.buf["fk_fresh"][ii] = 1  # Genesis refreshes the env's FK in every state setter (rigid_solver.py:1922-1937)
+
     def zero_all_dofs_velocity(self, envs_idx=None):
-        self._env.core.buf["qvel"][self._idx(envs_idx)] = 0.0
+        ii = self._idx(envs_idx)
+        self._env.core.buf["qvel"][ii] = 0.0
+        self._refreshed(ii)
 
     def set_dofs_position(self, position, dofs_idx_local=None, zero_velocity=True, envs_idx=None):
         ii = self._idx(envs_idx)
@@ -761,6 +881,7 @@ class _RobotFacade:
         q = self._env.core.buf["qpos"]
         for k, d in enumerate(dofs):
             q[ii, d + 1] = pos[:, k]
+        self._refreshed(ii)
         if zero_velocity:
             self.zero_all_dofs_velocity(envs_idx)
 
@@ -768,6 +889,7 @@ class _RobotFacade:
         ii = self._idx(envs_idx)
         p = torch.as_tensor(pos, device=self._env.device, dtype=torch.float32).reshape(len(ii), 3)
         self._env.core.buf["qpos"][ii, 0:3] = p
+        self._refreshed(ii)
         if zero_velocity:
             self.zero_all_dofs_velocity(envs_idx)
 
@@ -775,6 +897,7 @@ class _RobotFacade:
         ii = self._idx(envs_idx)
         q = torch.as_tensor(quat, device=self._env.device, dtype=torch.float32).reshape(len(ii), 4)
         self._env.core.buf["qpos"][ii, 3:7] = q
+        self._refreshed(ii)
         if zero_velocity:
             self.zero_all_dofs_velocity(envs_idx)
 
@@ -797,8 +920,7 @@ class _RobotFacade:
         return self._env.core.buf["torque"]
 
     def _links(self):
-        self._env.core.export_links(self._env._make_params(physics=False))
-        self._env._step_count -= 1
+        self._env.core.export_links()
 
     def get_links_pos(self):
         self._links()
@@ -814,18 +936,21 @@ class _RobotFacade:
     def get_links_net_contact_force(self):
         return self._env.core.buf["contact_force"].view(self._env.num_envs, 13, 3)
 
+    # global (all envs) physics parameters, Genesis semantics (rigid_geom.py:327-336, accessor.py:337-361)
     def set_friction(self, mu):
-        self._env._friction = float(mu)
+        self._env._set_global(abi.G_FRIC_ROBOT, mu)
 
     def set_mass_shift(self, shifts, links_idx_local):
         for s, l in zip(shifts, links_idx_local):
-            self._env._mass_shift[int(l)] = float(s)
+            self._env._set_global(abi.G_MASS_SHIFT + int(l), float(s))
 
     def set_COM_shift(self, shifts, links_idx_local):
         for s, l in zip(shifts, links_idx_local):
             if int(l) != 0:
                 raise NotImplementedError("COM shift is supported for the base link only (all the envs use)")
-            self._env._com_shift[:] = np.asarray(torch.as_tensor(s).cpu(), dtype=np.float32)
+            v = np.asarray(torch.as_tensor(s).cpu(), dtype=np.float32).reshape(3)
+            for j in range(3):
+                self._env._set_global(abi.G_COM_SHIFT + j, float(v[j]))
 
     def set_dofs_kp(self, kp, dofs=None):
         self._env._kp_genesis = float(kp[0])
@@ -839,10 +964,12 @@ class _GroundFacade:
         self._env = env
 
     def set_friction(self, mu):
-        self._env._friction = float(mu)
+        self._env._set_global(abi.G_FRIC_GROUND, mu)
 
 
 class _SceneFacade:
+    """env.scene: only `sim.rigid_solver.apply_links_external_force` (both eval scripts) is meaningful on the fused step."""
+
     def __init__(self, env):
         import types
 
@@ -850,7 +977,26 @@ class _SceneFacade:
         self._env = env
 
     def apply_links_external_force(self, force, links_idx, envs_idx=None):
-        raise NotImplementedError("external forces are applied inside the fused step (env_cfg['push_force_range'])")
+        """World-frame force at the link origin for the NEXT tick's two substeps, then cleared (abd/misc.py:655-715,
+        simulator.py:283).  `links_idx`: ONE global link index (robot.links[i].idx); force [n_envs, 3] or [n_envs, 1, 3]."""
+        e = self._env
+        links = [int(l) for l in (links_idx.tolist() if hasattr(links_idx, "tolist") else list(links_idx))]
+        if len(links) != 1:
+            raise NotImplementedError("one link per apply_links_external_force call (what the envs and eval scripts use)")
+        local = links[0] - 1
+        if not 0 <= local < abi.NLINK:
+            raise ValueError(f"link index {links[0]} is not a robot link")
+        ii = torch.arange(e.num_envs, device=e.device) if envs_idx is None else torch.as_tensor(envs_idx, device=e.device).long().reshape(-1)
+        f = torch.as_tensor(force, device=e.device, dtype=torch.float32).reshape(len(ii), 3)
+        ex = e.core.buf["ext_force"]
+        if e._ext_on:
+            prev = ex[ii, 0]
+            if bool(((prev >= 0) & (prev != float(local))).any()):
+                raise NotImplementedError("external forces on two different links of one env in the same tick")
+            f = f + ex[ii, 1:4] * (prev >= 0).unsqueeze(1).float()  # forces accumulate until the step clears them
+        ex[ii, 0] = float(local)
+        ex[ii, 1:4] = f
+        e._ext_on = True
 
     def step(self):
         raise NotImplementedError("scene.step() is fused into Go2Env.step()")

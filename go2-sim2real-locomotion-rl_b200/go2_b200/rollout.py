@@ -17,18 +17,23 @@ import torch
 from . import abi
 
 
+_LIB = None
+
+
 def _lib():
-    lib = abi.Go2Lib(abi.CUDA_LIB_PATH).lib
-    lib.go2_mlp_create.restype = C.c_int
-    return lib
+    global _LIB
+    if _LIB is None:  # one dlopen per process
+        _LIB = abi.Go2Lib(abi.CUDA_LIB_PATH).lib
+        _LIB.go2_mlp_create.restype = C.c_int
+    return _LIB
 
 
 def _ptr(t):
     return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
 
 
-def _stream():
-    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+def _stream(device=None):
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
 
 
 def _linear_layers(module_or_list):
@@ -50,7 +55,7 @@ class FusedMLP:
         self._lib = _lib()
         self._h = C.c_void_p()
         dims = (C.c_int32 * len(self.dims))(*self.dims)
-        rc = self._lib.go2_mlp_create(dims, len(layers), flat.ctypes.data_as(C.c_void_p), self.device.index or 0, C.byref(self._h))
+        rc = self._lib.go2_mlp_create(dims, len(layers), flat.ctypes.data_as(C.c_void_p), self.device.index if self.device.index is not None else torch.cuda.current_device(), C.byref(self._h))
         if rc != 0:
             raise RuntimeError(f"go2_mlp_create failed rc={rc} for dims {self.dims}")
 
@@ -70,7 +75,7 @@ class FusedMLP:
         B = x.shape[0]
         if out is None:
             out = torch.empty((B, self.dims[-1]), device=self.device, dtype=torch.float32)
-        rc = self._lib.go2_mlp_forward(self._h, _ptr(x), B, _ptr(out), _stream())
+        rc = self._lib.go2_mlp_forward(self._h, _ptr(x), B, _ptr(out), _stream(self.device))
         if rc != 0:
             raise RuntimeError(f"go2_mlp_forward failed rc={rc}")
         return out
@@ -108,7 +113,7 @@ class FusedActorCritic:
         mk = lambda t, shape: t if t is not None else torch.empty(shape, device=self.device, dtype=torch.float32)  # noqa: E731
         actions, mu, sigma, logp = mk(actions, (B, A)), mk(mu, (B, A)), mk(sigma, (B, A)), mk(logp, (B, 1))
         rc = self.actor._lib.go2_policy_act(self.actor._h, _ptr(obs), B, _ptr(self.std), C.c_uint64(self.seed), C.c_uint32(int(step)),
-                                            C.c_uint32(self.env_offset), _ptr(actions), _ptr(mu), _ptr(sigma), _ptr(logp), _stream())
+                                            C.c_uint32(self.env_offset), _ptr(actions), _ptr(mu), _ptr(sigma), _ptr(logp), _stream(self.device))
         if rc != 0:
             raise RuntimeError(f"go2_policy_act failed rc={rc}")
         return actions, mu, sigma, logp
@@ -120,7 +125,7 @@ class FusedActorCritic:
         self.critic._check(critic_obs)
         rc = self.actor._lib.go2_policy_act_critic(self.actor._h, self.critic._h, _ptr(obs), _ptr(critic_obs), obs.shape[0], _ptr(self.std),
                                                    C.c_uint64(self.seed), C.c_uint32(int(step)), C.c_uint32(self.env_offset), _ptr(actions),
-                                                   _ptr(mu), _ptr(sigma), _ptr(logp), _ptr(values), _stream())
+                                                   _ptr(mu), _ptr(sigma), _ptr(logp), _ptr(values), _stream(self.device))
         if rc != 0:
             raise RuntimeError(f"go2_policy_act_critic failed rc={rc}")
         return actions, values
@@ -131,7 +136,7 @@ def gae(rewards, dones, values, last_values, gamma, lam):
     T, B = rewards.shape[:2]
     ret, adv = torch.empty_like(rewards), torch.empty_like(rewards)
     rc = _lib().go2_gae(_ptr(rewards), _ptr(dones), _ptr(values), _ptr(last_values), T, B, C.c_float(gamma), C.c_float(lam), _ptr(ret), _ptr(adv),
-                        _stream())
+                        _stream(rewards.device))
     if rc != 0:
         raise RuntimeError(f"go2_gae failed rc={rc}")
     return ret, adv

@@ -37,8 +37,15 @@ int go2_buffer_info(go2_handle* h, int buf_id, void** dev_ptr, int* dtype, int* 
 
 /* One control tick for every env: replaces Go2Env.step (go2_env_walk.py:985-1109 /
  * go2_env_base.py:123-192) including scene.step() (2 substeps).  `d_actions`: device f32 [B][A].
- * `params` points to a StepParams.  Asynchronous on `stream` (a cudaStream_t, 0 = default stream). */
+ * `params` points to a StepParams.  Asynchronous on `stream` (a cudaStream_t, 0 = default stream).
+ * Two launches: the fused step kernel and the post-pass kernel (global physics DR of reset_idx,
+ * go2_env_walk.py:737-756,803-848, + statistics accumulation).  With StepParams.defer_post = 1 only the
+ * step kernel is launched, so that a multi-rank caller can all-reduce this tick's statistics row
+ * (B_STATS row go2_tick_parity()) before it calls go2_post with the same StepParams. */
 int go2_step(go2_handle* h, const float* d_actions, const void* params, int params_bytes, void* stream);
+int go2_post(go2_handle* h, const void* params, int params_bytes, void* stream);
+/* Double-buffer index (B_STATS / B_GLOBALS row) the next step launch - or a pending deferred post-pass - uses. */
+int go2_tick_parity(go2_handle* h);
 
 /* Replaces Go2Env.reset() -> reset_idx(all envs) (go2_env_walk.py:1242-1245). */
 int go2_reset_all(go2_handle* h, const void* params, int params_bytes, void* stream);
@@ -48,14 +55,23 @@ int go2_reset_all(go2_handle* h, const void* params, int params_bytes, void* str
 int go2_step_host(go2_handle* h, const float* h_actions, const void* params, int params_bytes, float* h_obs, float* h_rew,
                   uint8_t* h_done, float* h_priv, float* h_timeouts, void* stream);
 
-/* Episode statistics accumulated by the last step's resets (n_resets, n_timeouts, sum tracking/sec,
- * errno OR, then the per-reward-term sums): replaces the per-key `.mean().item()` host syncs of
- * reset_idx (go2_env_walk.py:1228-1235) and the curriculum aggregates (:688-729).  Synchronises. */
+/* Episode statistics accumulated on the device since the previous read (n_resets, n_timeouts, sum
+ * tracking/sec, number of env-ticks with an errno bit, then the per-reward-term sums): replaces the per-key
+ * `.mean().item()` host syncs of reset_idx (go2_env_walk.py:1228-1235) and the curriculum aggregates
+ * (:688-729).  go2_read_stats copies the accumulator to the host, clears it and synchronises.  The async
+ * pair does the same without stalling the tick: go2_read_stats_async enqueues copy + clear into pinned slot
+ * 0 or 1; go2_stats_fetch returns 0 and the numbers once that copy has completed (block = 1 waits,
+ * block = 0 returns 1 if it has not). */
 int go2_read_stats(go2_handle* h, float* host_out, int n, void* stream);
+int go2_read_stats_async(go2_handle* h, int slot, void* stream);
+int go2_stats_fetch(go2_handle* h, int slot, float* host_out, int n, int block);
 
 /* Recompute link poses / velocities of every env into B_LINK_POS / B_LINK_VEL
  * (replaces RigidEntity.get_links_pos / get_links_vel, rigid_entity.py:2241-2406). */
-int go2_export_links(go2_handle* h, const void* params, int params_bytes, void* stream);
+int go2_export_links(go2_handle* h, void* stream);
+
+/* Launch shape of the step kernel: out3 = {blocks, threads per block, 1 if the 255-register instantiation}. */
+void go2_launch_shape(go2_handle* h, int* out3);
 
 /* Replace the ground box by a heightfield terrain shared by all envs: replaces
  * scene.add_entity(gs.morphs.Terrain(height_field, horizontal_scale, vertical_scale, pos))

@@ -25,7 +25,7 @@ def _worker(rank, world, lib, port, q):
     for _ in range(70):
         _, _, done, _ = env.step(0.8 * torch.randn(B, 16, generator=g))
         n_resets += int(done.sum())
-    q.put((rank, n_resets, env._curr_ep_total, env._curr_timeout_total, float(env._friction), env._step_count,
+    q.put((rank, n_resets, env._curr_ep_total, env._curr_timeout_total, env.global_dr_values()["friction_ground"], env._step_count,
            env.core.buf["commands"][0].tolist()))
     dist.destroy_process_group()
 

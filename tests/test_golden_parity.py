@@ -70,13 +70,12 @@ def test_free_running_prefix(name, kind, horizon, backend, hostemu_lib):
 
 
 @pytest.mark.parametrize("backend", BACKENDS)
-def test_dense_solver_path_matches_too(backend, hostemu_lib, monkeypatch):
+def test_dense_solver_path_matches_too(backend, hostemu_lib):
     """Envs whose legs touch each other use the dense 18x18 Newton path instead of the arrow factorisation
     (go2_solve.cuh); the fixtures never produce such contacts, so the path is forced on every env here."""
-    monkeypatch.setenv("GO2_B200_FORCE_DENSE", "1")
     g, cfgs = load_golden("walk_det")
     T, B = g["actions"].shape[:2]
-    env = make_env("walk", cfgs, B, backend, hostemu_lib)
+    env = make_env("walk", cfgs, B, backend, hostemu_lib, solver_dense=True)
     env.reset()
     bad = total = 0
     for t in range(0, T, 3):

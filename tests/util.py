@@ -22,7 +22,9 @@ def make_env(kind, cfgs, B, backend, hostemu_lib=None, **kw):
     cls = {"walk": Go2EnvWalk, "stair": Go2EnvStair}.get(kind, Go2EnvBaseFlavour)
     cfgs = json.loads(json.dumps(cfgs))
     if backend == "hostemu":
-        return cls(B, *cfgs, device="cpu", lib_path=hostemu_lib, **kw)
+        from hostemu_core import HostEmuCore
+
+        return cls(B, *cfgs, device="cpu", lib_path=hostemu_lib, core_cls=HostEmuCore, **kw)
     return cls(B, *cfgs, device="cuda:0", **kw)
 
 
@@ -78,3 +80,109 @@ def close(a, b, atol, rtol):
 
 def np_(x):
     return x.detach().cpu().numpy()
+
+
+# ---------------------------------------------------------------------------------------------------
+# DR-on fixtures (oracle/gen_golden_dr.py): teacher forcing + replay of the reference's random draws
+# ---------------------------------------------------------------------------------------------------
+class Derived:
+    """Env-level buffers the DR fixtures leave out because they follow exactly from the stored arrays (the generator
+    asserts bit-equality with the reference env's own buffers at every tick): last_actions, the action-delay ring and the
+    episode sums.  Advanced tick by tick with the FIXTURE's actions / resets / reward terms."""
+
+    def __init__(self, g, kind, clip):
+        T, B, A = g["actions"].shape
+        self.kind, self.clip = kind, float(clip)
+        self.last_actions = np.zeros((B, A), np.float32)
+        self.ep_sums = np.zeros((B, g["o_rew_terms"].shape[2]), np.float32)
+        self.hist = None
+
+    def start(self, hist_slots):
+        if self.kind != "base":
+            self.hist = np.zeros((self.last_actions.shape[0], hist_slots, self.last_actions.shape[1]), np.float32)
+
+    def advance(self, g, t):
+        a = np.clip(g["actions"][t], -self.clip, self.clip).astype(np.float32)
+        done = g["o_reset"][t].astype(bool)
+        terms = g["o_rew_terms"][t]
+        self.last_actions = a.copy()
+        if self.kind != "base":
+            self.hist[:, int(g["hist_idx"][t])] = a
+            self.hist[done] = 0.0
+            self.ep_sums = (self.ep_sums + terms).astype(np.float32)
+            self.ep_sums[done] = 0.0
+        else:
+            self.ep_sums[done] = 0.0
+            self.ep_sums = (self.ep_sums + terms).astype(np.float32)
+
+
+def pre(g, key, t):
+    """Pre-state array of tick t; t == T reads the state after the last tick."""
+    return g[key][t] if t < g[key].shape[0] else g["final_" + key]
+
+
+def force_state_dr(env, g, t, kind, der):
+    """Overwrite the env's persistent state (device buffers, global DR in force, host counters) with the fixture's state
+    before tick t, and queue the fixture's random draws / global-DR candidates of tick t for replay."""
+    from go2_b200 import abi
+
+    b = env.core.buf
+    B = env.num_envs
+    md = list(env.motors_dof_idx)
+    qpos, qvel = g["qpos"][t], g["qvel"][t]
+    b["qpos"].copy_(_t(env, qpos))
+    b["qvel"].copy_(_t(env, qvel))
+    b["qacc_ws"].copy_(_t(env, g["qacc_ws"][t]))
+    b["warm"].copy_(_t(env, g["warm"][t][:, None], torch.int32))
+    ids = g["cache_pair"][t].astype(np.int32)
+    b["ncache"].copy_(_t(env, (ids >= 0).sum(1)[:, None], torch.int32))
+    b["cache_pair"].copy_(_t(env, np.maximum(ids, 0), torch.int32))
+    b["cache_n"].copy_(_t(env, g["cache_n"][t].reshape(B, -1)))
+    b["last_actions"].copy_(_t(env, der.last_actions))
+    b["last_dof_vel"].copy_(_t(env, qvel[:, md]))
+    b["dof_vel"].copy_(_t(env, qvel[:, md]))
+    b["dof_pos"].copy_(_t(env, qpos[:, [d + 1 for d in md]]))
+    b["commands"].copy_(_t(env, g["commands"][t]))
+    b["ep_len"].copy_(_t(env, g["ep_len"][t][:, None], torch.int32))
+    if der.ep_sums.shape[1] > 0:
+        b["ep_sums"].copy_(_t(env, der.ep_sums))
+    if kind in ("walk", "stair"):
+        b["hist"].copy_(_t(env, der.hist.reshape(B, -1)))
+        env._action_history_write_idx = int(g["hist_idx"][t])
+        b["delay"].copy_(_t(env, g["delay"][t][:, None], torch.int32))
+        b["air_time"].copy_(_t(env, g["air_time"][t]))
+        b["foot_contact"].copy_(_t(env, g["foot_contact"][t], torch.uint8))
+        for name in ("kp_factors", "kd_factors", "motor_strength", "grav_off"):
+            b[name].copy_(_t(env, g[name][t]))
+        if "push_force" in g:
+            b["push_force"].copy_(_t(env, g["push_force"][t]))
+            b["push_remain"].copy_(_t(env, g["push_remain"][t][:, None], torch.int32))
+            env._push_counter = int(g["push_counter"][t])
+        if float(g["level"][t]) != float(env.curriculum.level):
+            env.curriculum.level = float(g["level"][t])
+            env._apply_curriculum_level(force=True)
+        # global physics DR in force + the values the reference's reset_idx draws in this tick (used if an env resets)
+        gl = np.zeros(abi.GLOBALS_LEN, np.float32)
+        gl[abi.G_FRIC_GROUND] = gl[abi.G_FRIC_ROBOT] = g["g_friction"][t]
+        gl[abi.G_MASS_SHIFT] = g["g_mass"][t]
+        gl[abi.G_COM_SHIFT:abi.G_COM_SHIFT + 3] = g["g_com"][t]
+        for i, l in enumerate(env._hip_link_indices):
+            gl[abi.G_MASS_SHIFT + l] = g["g_leg"][t][i]
+        gl[abi.G_DR_COUNTER] = g["g_counter"][t]
+        # the other parity slot = the values of the previous tick (what the previous closing FK ran on); an env reset in the
+        # previous tick had its FK refreshed with the new values
+        gp = gl.copy()
+        if t > 0:
+            gp[abi.G_MASS_SHIFT] = g["g_mass"][t - 1]
+            gp[abi.G_COM_SHIFT:abi.G_COM_SHIFT + 3] = g["g_com"][t - 1]
+            for i, l in enumerate(env._hip_link_indices):
+                gp[abi.G_MASS_SHIFT + l] = g["g_leg"][t - 1][i]
+        par = env.core.tick_parity()
+        b["globals"].copy_(_t(env, np.stack([gl, gp] if par == 0 else [gp, gl])))
+        b["fk_fresh"].copy_(_t(env, (g["o_reset"][t - 1] if t > 0 else np.ones(B))[:, None], torch.uint8))
+        env._cand_override = {"friction": float(pre(g, "g_friction", t + 1)), "mass": float(pre(g, "g_mass", t + 1)),
+                              "com": [float(x) for x in pre(g, "g_com", t + 1)], "leg": [float(x) for x in pre(g, "g_leg", t + 1)]}
+    if kind == "stair":
+        b["terrain_row"].copy_(_t(env, g["terrain_row"][t][:, None], torch.int32))
+        b["last_x"].copy_(_t(env, g["last_x"][t][:, None]))
+    env.replay_draws(g["replay"][t])
