@@ -78,7 +78,7 @@ class EnvConfig(C.Structure):
         ("scan_nx", _i), ("scan_ny", _i), ("scan_x0", _f), ("scan_x1", _f), ("scan_y0", _f), ("scan_y1", _f),
         ("lin_vel_z_deadzone", _f),
         ("has_friction_dr", _i), ("has_mass_dr", _i), ("has_com_dr", _i), ("has_leg_mass_dr", _i), ("global_dr_interval", _i),
-        ("hip_link", _i * 4), ("solver_dense", _i), ("export_rew_terms", _i), ("replay_rows", _i),
+        ("hip_link", _i * 4), ("solver_dense", _i), ("export_rew_terms", _i),  ("replay_rows", _i),
     ]
 
 
