@@ -3,5 +3,5 @@ import os
 import sys
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from go2_b200.envs import Curriculum as CurriculumManager  # noqa: E402,F401
+from go2_b200.envs import CurriculumManager  # noqa: E402,F401
 from go2_b200.envs import Go2EnvWalk as Go2Env  # noqa: E402,F401

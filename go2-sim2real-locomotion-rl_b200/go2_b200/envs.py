@@ -112,13 +112,16 @@ def _default_device():
         return torch.device("cuda:0")
 
 
+_DEFAULT_CORE = [Go2Core]  # the test-suite swaps in its host emulation of the kernel source here (tests/hostemu_core.py)
+
+
 class _Go2EnvBase:
     """State shared by the walk / stair / base flavours: buffers, views, rsl-rl facing attributes."""
 
     KIND = abi.ENV_WALK
 
     def __init__(self, num_envs, env_cfg, obs_cfg, reward_cfg, command_cfg, show_viewer=False, *, device=None, seed=1,
-                 env_offset=0, total_envs=None, lib_path=None, stats_sync_interval=1, sync_ranks=True, core_cls=Go2Core,
+                 env_offset=0, total_envs=None, lib_path=None, stats_sync_interval=1, sync_ranks=True, core_cls=None,
                  replay=False, export_reward_terms=False, solver_dense=False):
         """Keyword-only extras (none is needed by the train / eval scripts):
         stats_sync_interval  ticks between reads of the device-side episode statistics.  1 = read (and wait) every tick, the
@@ -148,7 +151,7 @@ class _Go2EnvBase:
         self._env_offset = int(env_offset)
         self._total_envs = int(total_envs) if total_envs is not None else self.num_envs
         self._lib_path = lib_path
-        self._core_cls = core_cls
+        self._core_cls = core_cls or _DEFAULT_CORE[0]
         self.stats_sync_interval = int(stats_sync_interval)
         self._sync_ranks = bool(sync_ranks)
         self._opt_replay, self._opt_rew_terms, self._opt_dense = bool(replay), bool(export_reward_terms), bool(solver_dense)
@@ -371,7 +374,7 @@ class _Go2EnvBase:
             raise RuntimeError("Exceeding max number of contact pairs. Please increase 'max_collision_pairs'.")
         if bits & 1:
             raise RuntimeError("Exceeding max number of colliding geom pairs per env.")
-        return bits
+        return bits  # 4 / 8: non-finite force / acceleration (env was force-reset); 16: a non-sphere pair met the reference's GJK-fallback condition
 
 
 class Go2EnvWalk(_Go2EnvBase):

@@ -284,6 +284,8 @@ def run(env_cls, module, cfgs, kind, B, T, act_std, seed, act_dim, after_build=N
             post = outputs(env, obs, rew, done, extras, kind, terms)
             for k, v in {**pre, **post, "actions": a.numpy(), "replay": row, "push_resampled": np.array(flags["push_resampled"])}.items():
                 rec.setdefault(k, []).append(np.asarray(v))
+        gjk = env.scene._rigid.get_gjk_stats()
+        print(f"  GJK-preferred detections (narrowphase.py:724-736) sphere pairs {gjk[0]}, other pairs {gjk[1]} first + {gjk[2]} perturbed, of {gjk[3]} MPR collisions in {B * T} env-ticks")
         final = pre_state(env, kind)  # state after the last tick (DR buffers / globals the last tick's resets drew)
     finally:
         log.restore()

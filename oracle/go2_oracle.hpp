@@ -266,6 +266,9 @@ struct Env {
     real cost, prev_cost, gauss, quad_gauss[3];
     int ls_it, n_newton_iters;
     bool improved;
+    // diagnostics: detections for which the reference would prefer GJK over MPR's answer (narrowphase.py:724-736), see
+    // convex_convex_contact: [sphere pair, other pair first detection, other pair perturbed detection, all MPR collisions]
+    long gjk_wanted[4] = {0, 0, 0, 0};
 };
 
 }  // namespace orc

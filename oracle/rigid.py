@@ -179,6 +179,12 @@ class OracleRigid:
         n = self.lib.orc_get_contacts(self.h, int(b), _p(g), _p(d))
         return g[:n], d[:n]
 
+    def get_gjk_stats(self):
+        """[sphere-pair, other-pair first, other-pair perturbed] detections where the reference would prefer GJK, [all MPR collisions]."""
+        out = np.zeros(4, dtype=np.int64)
+        self.lib.orc_get_gjk_stats(self.h, _p(out))
+        return out
+
     def get_solver_stats(self):
         out = np.zeros((self.B, 3), dtype=np.int32)
         self.lib.orc_get_solver_stats(self.h, _p(out))

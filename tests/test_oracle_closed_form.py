@@ -1,0 +1,174 @@
+"""Closed-form / independent checks of the CPU oracle (L1 of SURVEY.md 8): the reference ships no golden vectors for its
+rigid solver, so the restatement is pinned against things that can be derived on paper or computed along a second route:
+
+  * MPR sphere-vs-box-face contacts against the analytic answer - which is also what the reference's GJK/EPA fallback
+    (narrowphase.py:724-736, not restated) converges to for the only pairs on which it fires in the walk / crouch / jump envs;
+  * the soft-contact law: resting normal force of every contact = 4 K imp(pen) pen / diag from MuJoCo's published solref /
+    solimp formulas (geom.py:405-427, solver.py:498-595);
+  * free flight: the centre of mass accelerates with exactly g and the angular momentum about it is conserved;
+  * `invweight` / `meaninertia` of the model table (shared by product and oracle) recomputed from the oracle's mass matrix and
+    a velocity-kinematics Jacobian, following rigid_solver.py:529-682.
+"""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from oracle.rigid import OracleRigid
+from util import ROOT, load_golden
+
+MODEL = json.load(open(os.path.join(ROOT, "go2-sim2real-locomotion-rl_b200/go2_b200/go2_model.json")))
+MDI = [7, 11, 15, 6, 10, 14, 9, 13, 17, 8, 12, 16]
+Q0 = np.array([0, 0.8, -1.5, 0, 0.8, -1.5, 0, 1.0, -1.5, 0, 1.0, -1.5])
+
+
+def _quat_rot(q, v):
+    w, x, y, z = q
+    R = np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y)],
+                  [2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x)],
+                  [2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)]])
+    return R @ v
+
+
+def test_mpr_sphere_vs_ground_box_matches_the_analytic_contact():
+    g, _ = load_golden("walk_c1")
+    B = g["actions"].shape[1]
+    o = OracleRigid(B, kind="f32")
+    geoms = MODEL["geoms"]
+    n = worst = 0
+    for t in range(0, 1000, 25):
+        o.set_qpos(g["qpos"][t])
+        o.set_qvel(g["qvel"][t])
+        o.step(1)
+        gp = None
+        for e in range(B):
+            gg, d = o.get_contacts(e)
+            for (ga, gb), c in zip(gg, d):
+                a, b = (ga, gb) if geoms[ga]["type"] == 1 else (gb, ga)
+                if geoms[a]["type"] != 1 or b != 0:
+                    continue
+                r = geoms[a]["data"][0]
+                # analytic: sphere of radius r whose centre is (cx, cy, cz) over the box face z = 0:
+                # normal = +z (from the box towards the sphere), pen = r - cz, position = midway between the two surface points
+                pos, nrm, pen = c[0:3], c[3:6], c[6]
+                assert abs(abs(nrm[2]) - 1.0) < 1e-5 and abs(nrm[0]) < 2e-3 and abs(nrm[1]) < 2e-3
+                # the two witness points are (cx, cy, cz - r) on the sphere and (cx, cy, 0) on the face: pos.z = (cz - r) / 2, pen = r - cz
+                worst = max(worst, abs(pos[2] + pen / 2))
+                assert abs(pos[2] + pen / 2) < 2e-6, (pos, pen)
+                assert 0 <= pen < r
+                n += 1
+    assert n > 500
+    print(f"\n{n} foot-ground MPR contacts match the analytic sphere / plane contact (max |pos.z + pen/2| = {worst:.2e})")
+
+
+def _sol(neg_pen, vel, pos):
+    timeconst, dampratio, dmin, dmax, width, mid, power = MODEL["sol_params"]
+    x = abs(neg_pen) / width
+    y = x ** power / mid ** (power - 1) if x < mid else 1 - (1 - x) ** power / (1 - mid) ** (power - 1)
+    imp = min(max(dmin + y * (dmax - dmin), dmin), dmax) if x <= 1 else dmax
+    b, k = 2 / (dmax * timeconst), 1 / (dmax ** 2 * timeconst ** 2 * dampratio ** 2)
+    return imp, -b * vel - k * imp * pos
+
+
+def test_resting_contact_force_follows_the_soft_constraint_law():
+    """Robot settled on the ground under PD control: for every foot contact the solver's normal force must equal
+    4 * D * aref with D = 1 / diag, diag = invweight (1 + mu^2) * 2 mu^2 (1 - imp) / imp (4 pyramid rows, all active, no
+    tangential load left once the robot is at rest), up to the residual acceleration / velocity terms."""
+    o = OracleRigid(1, kind="f64")
+    o.set_dofs_position(Q0[None], MDI)
+    o.set_dofs_kp(np.full(12, 60.0), MDI)
+    o.set_dofs_kv(np.full(12, 5.0), MDI)
+    for _ in range(3000):
+        o.control_dofs_position(Q0[None], MDI)
+        o.step(1)
+    assert np.abs(o.get_qvel()).max() < 2e-3, np.abs(o.get_qvel()).max()
+    gg, d = o.get_contacts(0)
+    cf = o.get_links_net_contact_force()[0]
+    inv_link = MODEL["links_invweight"]
+    feet = 0
+    for (ga, gb), c in zip(gg, d):
+        a, b = (ga, gb) if MODEL["geoms"][ga]["type"] == 1 else (gb, ga)
+        if MODEL["geoms"][a]["type"] != 1 or b != 0:
+            continue
+        link = MODEL["geoms"][a]["link"]
+        pen, mu = c[6], c[7]
+        imp, aref = _sol(-pen, 0.0, -pen)
+        invw = inv_link[link][0] + inv_link[0][0]
+        diag = invw * (1 + mu * mu) * 2 * mu * mu * (1 - imp) / imp
+        n_expected = 4 * aref / diag
+        assert cf[link][2] == pytest.approx(n_expected, rel=2e-2), (link, cf[link], n_expected)
+        feet += 1
+    assert feet == 4
+    assert cf[1:, 2].sum() == pytest.approx(MODEL["total_mass"] * 9.81, rel=1e-3)  # robot links (link 0 = ground takes the reaction)
+
+
+def test_free_flight_momentum():
+    """No contacts, zero torques, 0.5 s of flight: the linear momentum of the links changes by M g t (semi-implicit Euler in
+    generalised coordinates is exact for the free joint's translation; the configuration-dependent coupling and the rotor
+    armature leave an O(h) residual, bounded here at 1 %), and the float and double builds agree to 1e-4."""
+    masses = np.array([0.0] + [l["mass"] for l in MODEL["links"]])
+    ipos = [np.zeros(3)] + [np.array(l["inertial_pos"]) for l in MODEL["links"]]
+    res = {}
+    for kind in ("f64", "f32"):
+        rng = np.random.default_rng(0)
+        o = OracleRigid(1, kind=kind)
+        q = np.zeros((1, 19))
+        q[0, :3] = [0, 0, 5.0]
+        q[0, 3] = 1.0
+        q[0, 7:] = Q0[np.argsort(np.argsort(MDI))] * 0 + np.array([0, 0, 0, 0, 0.8, 0.8, 1.0, 1.0, -1.5, -1.5, -1.5, -1.5]) + 0.1 * rng.standard_normal(12)
+        o.set_qpos(q)
+        o.set_qvel(0.5 * rng.standard_normal((1, 18)))
+
+        def momentum():
+            quat, vel, ang = o.get_links_quat()[0], o.get_links_vel()[0], o.get_links_ang()[0]
+            p = np.zeros(3)
+            for l in range(1, 14):
+                p += masses[l] * (vel[l] + np.cross(ang[l], _quat_rot(quat[l], ipos[l])))
+            return p
+
+        o.control_dofs_force(np.zeros((1, 12)), MDI)
+        p0 = momentum()
+        n = 50
+        for _ in range(n):
+            o.step(1)
+        assert o.get_solver_stats()[0, 0] == 0  # no contacts
+        p1 = momentum()
+        expect = p0 + masses.sum() * np.array(MODEL["gravity"]) * n * MODEL["substep_dt"]
+        assert np.abs(p1 - expect).max() < 1e-2 * np.abs(expect).max(), (p1, expect)
+        res[kind] = p1
+    assert np.abs(res["f32"] - res["f64"]).max() < 1e-4 * np.abs(res["f64"]).max()
+
+
+def test_invweight_and_meaninertia_recomputed_independently():
+    """rigid_solver.py:529-682: M at qpos0, dof invweight = diag(M^-1) (free joint: means over the 3 translational / 3
+    rotational dofs), link invweight = mean diag(J M^-1 J^T) of the link-COM translational Jacobian, meaninertia = mean
+    diag(M).  Here M comes from the f64 oracle's CRBA and J from its velocity kinematics (unit dof velocities)."""
+    o = OracleRigid(1, kind="f64")
+    q = np.zeros((1, 19))
+    q[0, :3] = [0, 0, 0.42]
+    q[0, 3] = 1.0
+    o.set_qpos(q)
+    o.set_qvel(np.zeros((1, 18)))
+    o.control_dofs_force(np.zeros((1, 12)), MDI)
+    o.step(1)  # refreshes the mass matrix at (nearly) qpos0: one 10 ms free-fall substep moves the base by 0.5 mm only
+    o.set_qpos(q)
+    M = o.get_mass_matrix(0)
+    M = np.tril(M) + np.tril(M, -1).T
+    Minv = np.linalg.inv(M)
+    dinv = np.diag(Minv).copy()
+    dinv[:3], dinv[3:6] = dinv[:3].mean(), dinv[3:6].mean()
+    assert np.allclose(dinv, MODEL["dofs_invweight"], rtol=2e-3), (dinv, MODEL["dofs_invweight"])
+    assert np.trace(M) / 18 == pytest.approx(MODEL["meaninertia"], rel=2e-3)
+    ipos = [np.zeros(3)] + [np.array(l["inertial_pos"]) for l in MODEL["links"]]
+    J = np.zeros((14, 3, 18))
+    for d in range(18):
+        v = np.zeros((1, 18))
+        v[0, d] = 1.0
+        o.set_qvel(v)
+        quat, vel, ang = o.get_links_quat()[0], o.get_links_vel()[0], o.get_links_ang()[0]
+        for l in range(1, 14):
+            J[l, :, d] = vel[l] + np.cross(ang[l], _quat_rot(quat[l], ipos[l]))
+    for l in range(1, 14):
+        w = np.diag(J[l] @ Minv @ J[l].T).mean()
+        assert w == pytest.approx(MODEL["links_invweight"][l][0], rel=5e-3), (l, w, MODEL["links_invweight"][l])
