@@ -10,6 +10,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include <string>
+#include <vector>
 #include "../../include/go2_b200.h"
 #include "go2_env.cuh"
 #include "go2_model_host.hpp"
@@ -24,6 +25,7 @@ struct go2_handle {
     Go2Model* d_model;
     Go2Model model;      // host copy (patched by go2_set_terrain)
     float* d_hf;         // terrain heightfield (metres), shared by all envs
+    float* d_mip;        // its 4 x 4-block max level
     EnvConfig* d_cfg;
     EnvConfig cfg;
     Buffers bf;
@@ -164,6 +166,7 @@ int go2_create(const int32_t* model_iv, int n_iv, const double* model_fv, int n_
     }
     const EnvConfig& c = h->cfg;
     h->d_hf = nullptr;
+    h->d_mip = nullptr;
     Go2Model& m = h->model;
     if (!unpack_model(m, model_iv, n_iv, model_fv, n_fv)) { delete h; return -3; }
     if (c.num_envs <= 0 || c.num_actions > NACT_MAX || c.num_obs > NOBS_MAX || c.hist_size > HIST_MAX || c.n_rew > MAX_REW) { delete h; return -4; }
@@ -198,6 +201,7 @@ void go2_destroy(go2_handle* h) {
     cudaFree(h->arena);
     cudaFree(h->d_model);
     if (h->d_hf) cudaFree(h->d_hf);
+    if (h->d_mip) cudaFree(h->d_mip);
     cudaFree(h->d_cfg);
     cudaFreeHost(h->h_stats);
     for (int i = 0; i < N_STAT_SLOTS; ++i) cudaEventDestroy(h->stat_ev[i]);
@@ -344,6 +348,14 @@ int go2_set_terrain(go2_handle* h, const float* hf_m, int rows, int cols, float 
     for (int j = 0; j < 3; ++j) m.terrain_org[j] = origin3[j];
     m.terrain_zmax = zmax; m.terrain_zbot = zmin - 1.0f;  // collider.py:386-389 terrain_xyz_maxmin
     m.terrain_hf = h->d_hf;
+    {
+        std::vector<float> mip;
+        build_terrain_mip(hf_m, rows, cols, mip, m.terrain_mip_r, m.terrain_mip_c);
+        if (h->d_mip) cudaFree(h->d_mip);
+        if (!ck(h, cudaMalloc(&h->d_mip, mip.size() * sizeof(float)), "terrain mip alloc")) return -1;
+        if (!ck(h, cudaMemcpy(h->d_mip, mip.data(), mip.size() * sizeof(float), cudaMemcpyHostToDevice), "terrain mip upload")) return -1;
+        m.terrain_mip = h->d_mip;
+    }
     m.g_type[0] = GEOM_TERRAIN;
     return ck(h, cudaMemcpy(h->d_model, &m, sizeof(Go2Model), cudaMemcpyHostToDevice), "model upload") ? 0 : -1;
 }

@@ -3,6 +3,7 @@
 #pragma once
 #include "go2_buffers.cuh"
 #include <stddef.h>
+#include <vector>
 
 namespace go2 {
 
@@ -27,6 +28,20 @@ inline void compute_layout(const EnvConfig& c, int* dtype, int* rows, int* cols)
     set(B_TERRAIN_ROW, 1, B, 1); set(B_LAST_X, 0, B, 1);
     set(B_GLOBALS, 0, 2, GLOBALS_LEN); set(B_REW_TERMS, 0, c.export_rew_terms ? B : 1, c.n_rew > 0 ? c.n_rew : 1);
     set(B_REPLAY, 0, c.replay_rows > 0 ? c.replay_rows : 1, REPLAY_LEN); set(B_FK_FRESH, 2, B, 1); set(B_EXT_FORCE, 0, B, 4);
+}
+
+// max-height level of the heightfield (terrain_contacts' conservative cull): one value per 4 x 4 block of cells
+inline void build_terrain_mip(const float* hf, int rows, int cols, std::vector<float>& mip, int& mr, int& mc) {
+    const int bs = 1 << TERRAIN_MIP_SHIFT;
+    mr = (rows + bs - 1) / bs;
+    mc = (cols + bs - 1) / bs;
+    mip.assign((size_t)mr * mc, -1e30f);
+    for (int r = 0; r < rows; ++r)
+        for (int c = 0; c < cols; ++c) {
+            float& t = mip[(size_t)(r >> TERRAIN_MIP_SHIFT) * mc + (c >> TERRAIN_MIP_SHIFT)];
+            float v = hf[(size_t)r * cols + c];
+            t = v > t ? v : t;
+        }
 }
 
 inline size_t compute_offsets(const int* dtype, const int* rows, const int* cols, size_t* offs) {

@@ -31,6 +31,29 @@ inline bool unpack_model(Go2Model& m, const int32_t* iv, int n_iv, const double*
         m.pair_b[p] = (uint8_t)iv[k++];
     }
     if (k != n_iv) return false;
+    // link-pair table + runs for the two-level broad phase (go2_collide.cuh: detect_collisions)
+    m.n_lp = 0;
+    m.n_run = 0;
+    for (int p = 0; p < np; ++p) {
+        int la = m.g_link[m.pair_a[p]] + 1, lb = m.g_link[m.pair_b[p]] + 1;
+        int id = -1;
+        for (int q = 0; q < m.n_lp; ++q)
+            if (m.lp_a[q] == la && m.lp_b[q] == lb) id = q;
+        if (id < 0) {
+            if (m.n_lp >= MAX_LINK_PAIRS) return false;
+            id = m.n_lp++;
+            m.lp_a[id] = (uint8_t)la;
+            m.lp_b[id] = (uint8_t)lb;
+        }
+        if (m.n_run > 0 && m.run_lp[m.n_run - 1] == id) {
+            m.run_end[m.n_run - 1] = (uint16_t)(p + 1);
+        } else {
+            if (m.n_run >= MAX_PAIR_RUNS) return false;
+            m.run_lp[m.n_run] = (uint8_t)id;
+            m.run_end[m.n_run] = (uint16_t)(p + 1);
+            m.n_run++;
+        }
+    }
     for (int d = 0; d < NV; ++d) {
         m.limit_lo[d] = -1e30f; m.limit_hi[d] = 1e30f; m.frange[d] = 1e30f; m.armature[d] = 0.0f;
     }

@@ -65,6 +65,7 @@ struct Phys {
         };
         struct {
             v3 g_c[NGEOM], g_h[NGEOM];  // world AABB centre / half extents
+            v3 lk_lo[NLINK + 1], lk_hi[NLINK + 1];  // union of the geom boxes of the ground (0) and of each robot link (l + 1)
         };
         struct {
             uint8_t act[MAX_ROWS];

@@ -366,7 +366,11 @@ int go2_mlp_create(const int32_t* dims, int n_layers, const float* params, int d
     const float* p = params;
     for (int l = 0; l < n_layers; ++l) {
         const int kr = dims[l], nr = dims[l + 1];
-        const int K = pad_to(kr, KPAD), N = (l + 1 < n_layers) ? pad_to(nr, KPAD) : 16;
+        // hidden widths are padded with zero units (ELU(0) = 0 feeds zero weights of the next layer): to a multiple of KPAD, and
+        // to exactly 2 * NCHUNK when wider than one N-chunk - the kernel's chunk loop runs whole NCHUNK-wide chunks
+        int N = (l + 1 < n_layers) ? pad_to(nr, KPAD) : 16;
+        if (N > NCHUNK) N = 2 * NCHUNK;
+        const int K = l == 0 ? pad_to(kr, KPAD) : d.N[l - 1];
         d.K[l] = K;
         d.N[l] = N;
         const float* W = p;          // [nr][kr] row-major (torch.nn.Linear.weight)

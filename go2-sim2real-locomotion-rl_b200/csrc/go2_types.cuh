@@ -22,6 +22,7 @@ constexpr int NQ = 19;
 constexpr int NHINGE = 12;
 constexpr int NGEOM = 28;   // geom 0 = ground box, 1..27 robot
 constexpr int MAX_PAIRS_STATIC = 352;
+constexpr int MAX_LINK_PAIRS = 96, MAX_PAIR_RUNS = 160;  // 3 x 32-bit overlap masks
 constexpr int MAX_CPAIRS = 24;   // colliding geom pairs kept per env (contact-normal cache entries)
 constexpr int MAX_CONTACTS = 32; // contacts per env kept for the solve (reference cap: 150; overflow -> errno bit)
 constexpr int MAX_ROWS = 4 * MAX_CONTACTS + NHINGE;
@@ -32,6 +33,7 @@ constexpr int HIST_MAX = 4;      // action-delay ring slots (max_delay_steps + 1
 constexpr int NOBS_MAX = 49;
 constexpr int SCAN_MAX = 77;
 constexpr int MAX_TERRAIN_ROWS = 16;  // difficulty rows of the stair terrain (go2_env_stair.py:61)
+constexpr int TERRAIN_MIP_SHIFT = 2;      // 4 x 4 cells per block of the max-height level
 constexpr int TERRAIN_PAIR_CONTACTS = 5;  // n_contacts_per_pair (collider.py)
 
 constexpr float EPSF = 1.1920929e-07f;  // gs.EPS for precision="32" (genesis/__init__.py:229)
@@ -62,11 +64,19 @@ struct Go2Model {
     float g_pos[NGEOM][3], g_quat[NGEOM][4], g_size[NGEOM][3], g_half[NGEOM][3];
     int npairs;
     uint8_t pair_a[MAX_PAIRS_STATIC], pair_b[MAX_PAIRS_STATIC];
+    // two-level broad phase (built by unpack_model from the pair table): the distinct (link, link) pairs behind the geom pairs
+    // (box index 0 = ground, l + 1 = robot link l) and the runs of consecutive geom pairs that share one of them
+    int n_lp, n_run;
+    uint8_t lp_a[MAX_LINK_PAIRS], lp_b[MAX_LINK_PAIRS], run_lp[MAX_PAIR_RUNS];
+    uint16_t run_end[MAX_PAIR_RUNS];
     // Heightfield terrain replacing the ground box (stair env; go2_set_terrain).  hf is [terrain_r][terrain_c] metres,
     // shared by all envs; cell (r, c) sits at terrain_org + (r, c) * terrain_sh  (collider.py:374-394).
     int terrain_on, terrain_r, terrain_c;
     float terrain_sh, terrain_org[3], terrain_zmax, terrain_zbot;  // zbot = min(hf) - 1 (prism bottoms)
     const float* terrain_hf;
+    // max-height pyramid level of the heightfield: mip[(r >> TERRAIN_MIP_SHIFT)][(c >> TERRAIN_MIP_SHIFT)] = max of the block's cells
+    const float* terrain_mip;
+    int terrain_mip_r, terrain_mip_c;
 };
 
 // Reward terms (union of the walk / stair / base env zoos).

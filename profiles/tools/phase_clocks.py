@@ -7,7 +7,7 @@ from go2_b200.envs import Go2EnvStair, Go2EnvWalk
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 65536
 wl = sys.argv[2] if len(sys.argv) > 2 else "walk"
 cfgs = json.load(open(f"go2-sim2real-locomotion-rl_b200/go2_b200/cfgs/{wl}.json"))
-env = (Go2EnvStair if wl == "stair" else Go2EnvWalk)(B, *cfgs, device="cuda:0", seed=1)
+env = (Go2EnvStair if wl == "stair" else Go2EnvWalk)(B, *cfgs, device="cuda:0", seed=1, lib_path=os.environ["GO2_B200_LIB"], stats_sync_interval=24)
 env.reset()
 g = torch.Generator(device="cuda").manual_seed(1234)
 acts = [0.5 * torch.randn(B, env.num_actions, device="cuda", generator=g) for _ in range(8)]

@@ -21,7 +21,7 @@ struct go2_handle {
     Buffers bf;
     int dtype[B_COUNT], rows[B_COUNT], cols[B_COUNT];
     std::vector<char> arena;
-    std::vector<float> hf;
+    std::vector<float> hf, mip;
     long long launches;
     int parity, post_pending;
     std::string err;
@@ -196,6 +196,8 @@ int go2_set_terrain(go2_handle* h, const float* hf_m, int rows, int cols, float 
     for (int j = 0; j < 3; ++j) m.terrain_org[j] = origin3[j];
     m.terrain_zmax = zmax; m.terrain_zbot = zmin - 1.0f;
     m.terrain_hf = h->hf.data();
+    build_terrain_mip(h->hf.data(), rows, cols, h->mip, m.terrain_mip_r, m.terrain_mip_c);
+    m.terrain_mip = h->mip.data();
     m.g_type[0] = GEOM_TERRAIN;
     return 0;
 }

@@ -27,6 +27,7 @@ def mlp(dims, seed):
 
 
 @pytest.mark.parametrize("dims,B", [([49, 512, 256, 128, 16], 300), ([104, 512, 256, 128, 1], 128), ([45, 512, 256, 128, 12], 1000),
+                                     ([49, 400, 200, 100, 16], 200), ([182, 300, 272, 16], 130),
                                     ([182, 512, 256, 128, 1], 4096), ([49, 128, 16], 77)])
 def test_fused_mlp_matches_torch_fp32(dims, B):
     from go2_b200.rollout import FusedMLP
