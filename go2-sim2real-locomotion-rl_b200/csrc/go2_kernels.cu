@@ -69,6 +69,23 @@ __device__ __forceinline__ void step_body(const Go2Model* __restrict__ gm, const
     EnvStepOut out;
     t_env_step(*gm, *gcfg, sp, bf, actions, b, valid, p, e, out);
     if (valid) accumulate_stats(gcfg, sp, bf, out, p.err);
+    if (sp.host_obs) {
+        // Host-buffer call with pinned result buffers: the 32 envs of a warp own one contiguous block of the env-major obs /
+        // rew / done arrays, so a finished warp re-reads its block (L2) and streams it to the mapped host buffers with
+        // full 128-byte stores - the PCIe writes of early warps overlap the late warps' compute, no D2H copy follows.
+        __syncwarp();
+        const int lane = threadIdx.x & 31, b0 = b - lane, nv = min(32, bf.B - b0);
+        if (nv > 0) {
+            const int no = gcfg->num_obs;
+            const float* src = (const float*)bf.p[B_OBS] + (size_t)b0 * no;
+            float* dst = sp.host_obs + (size_t)b0 * no;
+            for (int w = lane; w < nv * no; w += 32) dst[w] = __ldcg(src + w);
+            if (lane < nv) {
+                sp.host_rew[b0 + lane] = __ldcg((const float*)bf.p[B_REW] + b0 + lane);
+                sp.host_done[b0 + lane] = __ldcg((const uint8_t*)bf.p[B_RESET] + b0 + lane);
+            }
+        }
+    }
 }
 // large batches: up to GO2_TPB threads per block, 128 registers (one 448-thread block per SM at 65,536 envs)
 __global__ void __launch_bounds__(GO2_TPB) go2_step_kernel(const Go2Model* __restrict__ gm, const EnvConfig* __restrict__ gcfg,
@@ -231,12 +248,13 @@ static int launch_post(go2_handle* h, const StepParams& sp, cudaStream_t s) {
     return ck(h, cudaGetLastError(), "go2_post_kernel") ? 0 : -1;
 }
 
-static int launch_step(go2_handle* h, const float* d_actions, const void* params, int params_bytes, cudaStream_t s) {
+static int launch_step(go2_handle* h, const float* d_actions, const void* params, int params_bytes, cudaStream_t s, bool host_call = false) {
     if (params_bytes != (int)sizeof(StepParams)) { h->err = "StepParams size mismatch"; return -2; }
     if (h->post_pending) { h->err = "go2_post must follow a go2_step with defer_post before the next tick"; return -3; }
     StepParams sp;
     memcpy(&sp, params, sizeof(sp));
     sp.parity = h->parity;
+    if (!host_call) sp.host_obs = nullptr, sp.host_rew = nullptr, sp.host_done = nullptr;  // only go2_step_host* sets them
     if (sp.replay_on && h->cfg.replay_rows != h->cfg.num_envs) { h->err = "replay_on needs EnvConfig.replay_rows == num_envs"; return -4; }
     if (cudaSetDevice(h->device) != cudaSuccess) { h->err = "cudaSetDevice"; return -1; }
     if (h->small)
@@ -277,21 +295,55 @@ int go2_reset_all(go2_handle* h, const void* params, int params_bytes, void* str
     return launch_step(h, (const float*)h->bf.p[B_ACTIONS_IN], &sp, sizeof(sp), (cudaStream_t)stream);
 }
 
+// the device address of a host buffer the kernels may write directly (pinned memory under unified addressing), else null
+static void* mapped(const void* hp) {
+    if (!hp) return nullptr;
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, hp) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return at.type == cudaMemoryTypeHost ? at.devicePointer : nullptr;
+}
+
+// H2D actions + step kernel (+ post-pass unless StepParams.defer_post).  Result buffers that are pinned are written by the
+// step kernel itself; *staged = 1 tells the caller that obs / rew / done still need device-to-host copies.
+static int step_host_begin(go2_handle* h, const float* h_actions, const void* params, int params_bytes, float* h_obs, float* h_rew,
+                           uint8_t* h_done, cudaStream_t s, int* staged) {
+    const EnvConfig& c = h->cfg;
+    size_t B = c.num_envs;
+    if (params_bytes != (int)sizeof(StepParams)) { h->err = "StepParams size mismatch"; return -2; }
+    if (cudaSetDevice(h->device) != cudaSuccess) { h->err = "cudaSetDevice"; return -1; }
+    StepParams sp;
+    memcpy(&sp, params, sizeof(sp));
+    void *mo = mapped(h_obs), *mr = mapped(h_rew), *md = mapped(h_done);
+    const bool direct = mo && mr && md;
+    sp.host_obs = direct ? (float*)mo : nullptr;
+    sp.host_rew = direct ? (float*)mr : nullptr;
+    sp.host_done = direct ? (uint8_t*)md : nullptr;
+    *staged = direct ? 0 : 1;
+    if (!ck(h, cudaMemcpyAsync(h->bf.p[B_ACTIONS_IN], h_actions, B * c.num_actions * 4, cudaMemcpyHostToDevice, s), "H2D actions")) return -1;
+    return launch_step(h, (const float*)h->bf.p[B_ACTIONS_IN], &sp, sizeof(sp), s, true);
+}
+
+int go2_step_host_begin(go2_handle* h, const float* h_actions, const void* params, int params_bytes, float* h_obs, float* h_rew,
+                        uint8_t* h_done, void* stream, int* staged) {
+    return step_host_begin(h, h_actions, params, params_bytes, h_obs, h_rew, h_done, (cudaStream_t)stream, staged);
+}
+
 int go2_step_host(go2_handle* h, const float* h_actions, const void* params, int params_bytes, float* h_obs, float* h_rew,
                   uint8_t* h_done, float* h_priv, float* h_timeouts, void* stream) {
     cudaStream_t s = (cudaStream_t)stream;
     const EnvConfig& c = h->cfg;
     size_t B = c.num_envs;
-    if (cudaSetDevice(h->device) != cudaSuccess) { h->err = "cudaSetDevice"; return -1; }
-    if (!ck(h, cudaMemcpyAsync(h->bf.p[B_ACTIONS_IN], h_actions, B * c.num_actions * 4, cudaMemcpyHostToDevice, s), "H2D actions")) return -1;
-    int r = launch_step(h, (const float*)h->bf.p[B_ACTIONS_IN], params, params_bytes, s);
+    int staged = 1;
+    int r = step_host_begin(h, h_actions, params, params_bytes, h_obs, h_rew, h_done, s, &staged);
     if (r) return r;
-    if (h->post_pending) { h->err = "go2_step_host does not support defer_post"; return -3; }
-    // the small results first: a consumer polling rew / done is not held back by the bulk rows
-    cudaMemcpyAsync(h_rew, h->bf.p[B_REW], B * 4, cudaMemcpyDeviceToHost, s);
-    cudaMemcpyAsync(h_done, h->bf.p[B_RESET], B, cudaMemcpyDeviceToHost, s);
+    if (h->post_pending) { h->err = "go2_step_host does not support defer_post (use go2_step_host_begin + go2_post)"; return -3; }
+    if (staged) {
+        // the small results first: a consumer polling rew / done is not held back by the bulk rows
+        cudaMemcpyAsync(h_rew, h->bf.p[B_REW], B * 4, cudaMemcpyDeviceToHost, s);
+        cudaMemcpyAsync(h_done, h->bf.p[B_RESET], B, cudaMemcpyDeviceToHost, s);
+        cudaMemcpyAsync(h_obs, h->bf.p[B_OBS], B * c.num_obs * 4, cudaMemcpyDeviceToHost, s);
+    }
     if (h_timeouts) cudaMemcpyAsync(h_timeouts, h->bf.p[B_TIMEOUT], B * 4, cudaMemcpyDeviceToHost, s);
-    cudaMemcpyAsync(h_obs, h->bf.p[B_OBS], B * c.num_obs * 4, cudaMemcpyDeviceToHost, s);
     if (h_priv && c.num_priv > 0) cudaMemcpyAsync(h_priv, h->bf.p[B_PRIV], B * c.num_priv * 4, cudaMemcpyDeviceToHost, s);
     return ck(h, cudaStreamSynchronize(s), "step_host sync") ? 0 : -1;
 }

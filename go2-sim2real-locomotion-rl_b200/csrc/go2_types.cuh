@@ -169,6 +169,11 @@ struct StepParams {
     int defer_post;            // 1 = go2_step launches the step kernel only; the caller reduces B_STATS over ranks, then go2_post
     int replay_on;             // 1 = every random draw of the tick is read from B_REPLAY instead of Philox (fixture replay)
     int ext_on;                // 1 = B_EXT_FORCE holds external link forces for this tick (apply_links_external_force)
+    // go2_step_host with pinned (device-mappable) result buffers: the step kernel streams obs / rew / done of finished warps
+    // straight into host memory (filled by the library; the host leaves them 0)
+    float* host_obs;
+    float* host_rew;
+    uint8_t* host_done;
 };
 
 // B_GLOBALS: [2][GLOBALS_LEN] global physics DR values in force (slot = StepParams.parity)

@@ -94,13 +94,14 @@ class StepParams(C.Structure):
         ("do_physics", _i), ("force_reset_all", _i), ("terrain_max_row", _i), ("lock_terrain_rows", _i),
         ("cand_friction", _f), ("cand_mass", _f), ("cand_com", _f * 3), ("cand_leg", _f * 4),
         ("parity", _i), ("defer_post", _i), ("replay_on", _i), ("ext_on", _i),
+        ("host_obs", C.c_void_p), ("host_rew", C.c_void_p), ("host_done", C.c_void_p),
     ]
 
 
 _EXPORTS = [
     "go2_abi_sizes", "go2_create", "go2_destroy", "go2_last_error", "go2_buffer_info", "go2_step", "go2_reset_all",
     "go2_step_host", "go2_read_stats", "go2_export_links", "go2_launch_count", "go2_set_terrain",
-    "go2_post", "go2_tick_parity", "go2_read_stats_async", "go2_stats_fetch", "go2_launch_shape",
+    "go2_post", "go2_tick_parity", "go2_step_host_begin", "go2_read_stats_async", "go2_stats_fetch", "go2_launch_shape",
 ]
 # include/go2_policy.h (CUDA library only; the host-emulation test library has no tensor cores to emulate)
 _POLICY_EXPORTS = ["go2_mlp_create", "go2_mlp_destroy", "go2_mlp_forward", "go2_policy_act", "go2_policy_act_critic", "go2_gae"]

@@ -93,6 +93,17 @@ class Go2Core:
         self.L.check(self.h, self.lib.go2_step_host(self.h, p(h_actions), C.byref(sp), C.sizeof(sp), p(h_obs), p(h_rew), p(h_done),
                                                     p(h_priv), p(h_timeouts), self._stream()), "go2_step_host")
 
+    def step_host_begin(self, h_actions, sp, h_obs, h_rew, h_done):
+        """H2D actions + step kernel (sp.defer_post decides about the post-pass); returns True if obs / rew / done still have to
+        be copied from the device buffers (pageable host buffers), False if the kernel writes them itself (pinned buffers)."""
+        def p(x):
+            return C.c_void_p(x.ctypes.data) if isinstance(x, np.ndarray) else C.c_void_p(x.data_ptr())
+
+        staged = C.c_int(1)
+        self.L.check(self.h, self.lib.go2_step_host_begin(self.h, p(h_actions), C.byref(sp), C.sizeof(sp), p(h_obs), p(h_rew), p(h_done),
+                                                          self._stream(), C.byref(staged)), "go2_step_host_begin")
+        return bool(staged.value)
+
     def reset_all(self, sp: abi.StepParams):
         self.L.check(self.h, self.lib.go2_reset_all(self.h, C.byref(sp), C.sizeof(sp), self._stream()), "go2_reset_all")
 

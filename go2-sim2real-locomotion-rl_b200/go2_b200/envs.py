@@ -264,15 +264,22 @@ class _Go2EnvBase:
         and the obs / rew / done D2H copies happen inside the call, which returns after the stream is idle."""
         sp = self._make_params(physics=True)
         if self._multi_rank():
-            # the statistics all-reduce sits between the two launches: same copies, issued from here on the same stream
+            # the statistics all-reduce sits between the step and the post-pass launch
+            import torch.distributed as dist
+
             b = self.core.buf
-            b["actions_in"].copy_(torch.as_tensor(h_actions).reshape(b["actions_in"].shape), non_blocking=True)
-            self._launch(b["actions_in"], sp)
-            pairs = [(h_rew, b["rew"].view(-1)), (h_done, b["reset"].view(-1)), (h_timeouts, b["timeout"].view(-1)), (h_obs, b["obs"]), (h_priv, b["priv"])]
+            sp.defer_post = 1
+            staged = self.core.step_host_begin(h_actions, sp, h_obs, h_rew, h_done)
+            dist.all_reduce(b["stats"][self.core.tick_parity()])
+            self.core.post(sp)
+            pairs = [(h_timeouts, b["timeout"].view(-1)), (h_priv, b["priv"])]
+            if staged:
+                pairs = [(h_rew, b["rew"].view(-1)), (h_done, b["reset"].view(-1)), (h_obs, b["obs"])] + pairs
             for dst, src in pairs:
                 if dst is not None:
                     torch.as_tensor(dst).copy_(src, non_blocking=True)
             torch.cuda.current_stream(self.device).synchronize()
+            self._after_launch()
         else:
             self.core.step_host(h_actions, sp, h_obs, h_rew, h_done, h_priv, h_timeouts)
             self._after_launch()

@@ -50,10 +50,17 @@ int go2_tick_parity(go2_handle* h);
 /* Replaces Go2Env.reset() -> reset_idx(all envs) (go2_env_walk.py:1242-1245). */
 int go2_reset_all(go2_handle* h, const void* params, int params_bytes, void* stream);
 
-/* Same tick with HOST buffers: copies actions H2D, steps, copies obs / rew / done (and, if non-NULL,
- * privileged obs and time_outs) D2H, and synchronises the stream before returning. */
+/* Same tick with HOST buffers: copies actions H2D, steps, delivers obs / rew / done (and, if non-NULL, privileged obs and
+ * time_outs) to the host buffers and synchronises the stream before returning.  Pinned obs / rew / done buffers are written
+ * directly by the step kernel (mapped host memory, overlapped with the kernel); pageable ones are staged through D2H copies. */
 int go2_step_host(go2_handle* h, const float* h_actions, const void* params, int params_bytes, float* h_obs, float* h_rew,
                   uint8_t* h_done, float* h_priv, float* h_timeouts, void* stream);
+/* First half of go2_step_host for callers that insert work between the step and the post-pass (StepParams.defer_post: the
+ * multi-rank statistics all-reduce): H2D of the actions + step kernel.  If h_obs / h_rew / h_done are pinned (device-mappable)
+ * the step kernel writes them itself as its warps finish - no device-to-host copy - and *staged = 0; otherwise *staged = 1 and
+ * the caller copies B_OBS / B_REW / B_RESET.  The results are complete once `stream` has been synchronised. */
+int go2_step_host_begin(go2_handle* h, const float* h_actions, const void* params, int params_bytes, float* h_obs, float* h_rew,
+                        uint8_t* h_done, void* stream, int* staged);
 
 /* Episode statistics accumulated on the device since the previous read (n_resets, n_timeouts, sum
  * tracking/sec, number of env-ticks with an errno bit, then the per-reward-term sums): replaces the per-key

@@ -160,6 +160,13 @@ int go2_stats_fetch(go2_handle* h, int slot, float* host_out, int n, int block) 
     memcpy(host_out, g_stat_slots[slot & 1], sizeof(float) * n);
     return 0;
 }
+int go2_step_host_begin(go2_handle* h, const float* h_actions, const void* params, int params_bytes, float* h_obs, float* h_rew,
+                        uint8_t* h_done, void* stream, int* staged) {
+    (void)h_obs; (void)h_rew; (void)h_done;
+    *staged = 1;
+    memcpy(h->bf.p[B_ACTIONS_IN], h_actions, (size_t)h->cfg.num_envs * h->cfg.num_actions * 4);
+    return go2_step(h, (const float*)h->bf.p[B_ACTIONS_IN], params, params_bytes, stream);
+}
 int go2_read_stats(go2_handle* h, float* host_out, int n, void* stream) {
     go2_read_stats_async(h, 0, stream);
     return go2_stats_fetch(h, 0, host_out, n, 1);

@@ -124,7 +124,9 @@ def test_env_state_resume_is_bit_exact_on_cuda():
             assert torch.equal(u, v)
 
 
-def test_step_host_matches_device_step():
+@pytest.mark.parametrize("pinned", [False, True])
+def test_step_host_matches_device_step(pinned):
+    """Pageable host buffers take the staged path (D2H copies), pinned ones are written by the step kernel itself."""
     B = 300
     cfgs = _cfgs("walk")
     a_env = make_env("walk", cfgs, B, "cuda", seed=5)
@@ -132,9 +134,13 @@ def test_step_host_matches_device_step():
     a_env.reset()
     b_env.reset()
     g = torch.Generator().manual_seed(9)
-    h_obs = np.empty((B, a_env.num_obs), dtype=np.float32)
-    h_rew = np.empty((B,), dtype=np.float32)
-    h_done = np.empty((B,), dtype=np.uint8)
+    if pinned:
+        t_obs, t_rew, t_done = (torch.zeros(s, dtype=d).pin_memory() for s, d in (((B, a_env.num_obs), torch.float32), ((B,), torch.float32), ((B,), torch.uint8)))
+        h_obs, h_rew, h_done = t_obs.numpy(), t_rew.numpy(), t_done.numpy()
+    else:
+        h_obs = np.empty((B, a_env.num_obs), dtype=np.float32)
+        h_rew = np.empty((B,), dtype=np.float32)
+        h_done = np.empty((B,), dtype=np.uint8)
     h_priv = np.empty((B, a_env.num_privileged_obs), dtype=np.float32)
     h_to = np.empty((B,), dtype=np.float32)
     for _ in range(6):
