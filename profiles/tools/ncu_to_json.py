@@ -17,7 +17,7 @@ def get(k):
     i = h.index(k)
     x = float(v[i].replace(",", ""))
     unit = u[i]
-    scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0, "msecond": 1e-3, "usecond": 1e-6, "second": 1.0, "nsecond": 1e-9}.get(unit, 1.0)
+    scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0, "msecond": 1e-3, "usecond": 1e-6, "second": 1.0, "nsecond": 1e-9, "ms": 1e-3, "us": 1e-6, "s": 1.0, "ns": 1e-9}.get(unit, 1.0)
     return x * scale
 
 
