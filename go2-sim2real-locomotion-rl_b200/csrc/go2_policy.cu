@@ -22,10 +22,16 @@
 #include <stdint.h>
 #include <string.h>
 
+#include <stdarg.h>
+#include <stdio.h>
+
+#include <mutex>
 #include <string>
 #include <vector>
 
 #include "go2_math.cuh"
+
+#define GO2_NOALLOC_MAX_DEVICES 64
 
 namespace go2pol {
 
@@ -327,6 +333,45 @@ __global__ void go2_gae_kernel(const float* __restrict__ rew, const uint8_t* __r
     }
 }
 
+
+// ---- no-allocation variant of the MLP forward (go2_mlp_forward_noalloc) --------------------------------------------------------------
+// go2_mlp_create packs the weights on the host into cudaMalloc'ed buffers.  Callers that may not allocate (CUDA graph capture, tight
+// serving loops) get the same kernel fed from ONE file-scope device array: a small kernel packs the f32 torch-layout parameters (device
+// memory of the caller) into it, zero padding included, and go2_mlp_kernel streams the packed image from there.  Every GPU that loads
+// the library holds the array until exit; all calls share it (calls that overlap on the GPU race).
+constexpr size_t NOALLOC_SCRATCH_BYTES = 1u << 20;  // = GO2_MLP_NOALLOC_SCRATCH_BYTES of include/go2_policy.h
+// 1 MiB: the reference's actor (49-512-256-128-12) needs 401,152 B, its critic (104-...-1) 466,688 B
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_SCRATCH_BYTES];
+
+struct PackLayer {
+    const float* W;         // [nr][kr] row-major (torch.nn.Linear.weight), device
+    const float* bias;      // [nr], device
+    __nv_bfloat16* w_out;   // packed [n_chunk][K/8][ncw][8] (the layout go2_mlp_create produces)
+    float* b_out;           // [N] zero padded
+    int kr, nr, K, N, ncw;
+};
+struct PackJob {
+    PackLayer l[MAX_LAYERS];
+};
+// blockIdx.y = layer; every element of the padded image is written (stale contents of an earlier call never survive)
+__global__ void __launch_bounds__(256) go2_mlp_pack_kernel(PackJob j) {
+    const PackLayer& L = j.l[blockIdx.y];
+    const size_t total = (size_t)L.K * L.N, stride = (size_t)gridDim.x * blockDim.x;
+    const int k8 = L.K / 8;
+    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += stride) {
+        const int e = (int)(idx & 7);
+        size_t r = idx >> 3;
+        const int n = (int)(r % L.ncw);
+        r /= L.ncw;
+        const int kc = (int)(r % k8), nc = (int)(r / k8);
+        const int gn = nc * L.ncw + n, gk = kc * 8 + e;
+        const float v = (gn < L.nr && gk < L.kr) ? L.W[(size_t)gn * L.kr + gk] : 0.0f;
+        L.w_out[idx] = __float2bfloat16_rn(v);
+    }
+    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < (size_t)L.N; idx += stride)
+        L.b_out[idx] = (int)idx < L.nr ? L.bias[idx] : 0.0f;
+}
+
 }  // namespace go2pol
 
 // ---- host side + C ABI (declared in include/go2_b200.h) -------------------------------------------------------
@@ -467,6 +512,101 @@ int go2_gae(const float* d_rewards, const uint8_t* d_dones, const float* d_value
     go2_gae_kernel<<<(B + 255) / 256, 256, 0, (cudaStream_t)stream>>>(d_rewards, d_dones, d_values, d_last_values, T, B, gamma, lam, d_returns,
                                                                       d_advantages);
     return cudaGetLastError() == cudaSuccess ? 0 : 7;
+}
+
+}  // extern "C"
+
+// ---- go2_mlp_forward_noalloc: no cudaMalloc / cudaFree / allocating library call anywhere on this path ----------------------------------
+static std::mutex g_na_mu;
+static unsigned char* g_na_ptr[GO2_NOALLOC_MAX_DEVICES] = {nullptr};  // DEVICE address of g_noalloc_scratch, per device
+
+static int na_fail(char* err, int err_len, int rc, const char* fmt, ...) {
+    if (err && err_len > 0) {
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(err, (size_t)err_len, fmt, ap);
+        va_end(ap);
+    }
+    return rc;
+}
+
+// In host code `g_noalloc_scratch` is only a stand-in symbol: its device address is looked up once per device, with that device current.
+static int na_device_scratch(int device, unsigned char** out, char* err, int err_len) {
+    if (device < 0 || device >= GO2_NOALLOC_MAX_DEVICES) return na_fail(err, err_len, 3, "device %d outside [0, %d)", device, GO2_NOALLOC_MAX_DEVICES);
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return na_fail(err, err_len, 3, "cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
+    std::lock_guard<std::mutex> lk(g_na_mu);
+    if (!g_na_ptr[device]) {
+        unsigned char* ptr = nullptr;
+        e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch);
+        if (e != cudaSuccess || !ptr) return na_fail(err, err_len, 9, "cudaGetSymbolAddress(scratch) on device %d: %s", device, cudaGetErrorString(e));
+        e = cudaFuncSetAttribute(go2_mlp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+        if (e != cudaSuccess) return na_fail(err, err_len, 6, "cudaFuncSetAttribute(go2_mlp_kernel): %s", cudaGetErrorString(e));
+        g_na_ptr[device] = ptr;
+    }
+    *out = g_na_ptr[device];
+    return 0;
+}
+
+extern "C" {
+
+int go2_mlp_forward_noalloc(const int32_t* dims, int n_layers, const float* d_params, int device, const float* d_in, int B, float* d_out,
+                            void* stream, char* err, int err_len) {
+    if (err && err_len > 0) err[0] = 0;
+    if (!dims || !d_params || !d_in || !d_out || B <= 0) return na_fail(err, err_len, 1, "null pointer or B <= 0");
+    if (n_layers < 1 || n_layers > MAX_LAYERS) return na_fail(err, err_len, 1, "n_layers %d outside [1, %d]", n_layers, MAX_LAYERS);
+    if (dims[n_layers] > 16 || dims[n_layers] < 1 || dims[0] > 512 || dims[0] < 1)
+        return na_fail(err, err_len, 2, "input width %d (max 512) / output width %d (max 16) not supported", dims[0], dims[n_layers]);
+    for (int l = 1; l < n_layers; ++l)
+        if (dims[l] > 512 || dims[l] < 1) return na_fail(err, err_len, 2, "hidden width %d of layer %d not in [1, 512]", dims[l], l);
+    // the padding rules of go2_mlp_create, and the scratch carve-up (256-byte aligned pieces)
+    MlpJob j;
+    memset(&j, 0, sizeof(j));
+    PackJob pj;
+    memset(&pj, 0, sizeof(pj));
+    size_t off[MAX_LAYERS][2], need = 0, max_elems = 0;
+    const float* p = d_params;
+    j.d.n_layers = n_layers;
+    j.d.n_in = dims[0];
+    j.d.n_out = dims[n_layers];
+    for (int l = 0; l < n_layers; ++l) {
+        const int kr = dims[l], nr = dims[l + 1];
+        int N = (l + 1 < n_layers) ? pad_to(nr, KPAD) : 16;
+        if (N > NCHUNK) N = 2 * NCHUNK;
+        const int K = l == 0 ? pad_to(kr, KPAD) : j.d.N[l - 1];
+        j.d.K[l] = K;
+        j.d.N[l] = N;
+        off[l][0] = need;
+        need += ((size_t)K * N * 2 + 255) / 256 * 256;
+        off[l][1] = need;
+        need += ((size_t)N * 4 + 255) / 256 * 256;
+        PackLayer& L = pj.l[l];
+        L.W = p;
+        L.bias = p + (size_t)nr * kr;
+        p += (size_t)nr * kr + nr;
+        L.kr = kr; L.nr = nr; L.K = K; L.N = N; L.ncw = N < NCHUNK ? N : NCHUNK;
+        if ((size_t)K * N > max_elems) max_elems = (size_t)K * N;
+    }
+    if (need > NOALLOC_SCRATCH_BYTES)
+        return na_fail(err, err_len, 8, "network needs %zu bytes of packed weights, the static scratch array holds %zu (use go2_mlp_create + go2_mlp_forward)",
+                       need, (size_t)NOALLOC_SCRATCH_BYTES);
+    unsigned char* scratch = nullptr;
+    if (int rc = na_device_scratch(device, &scratch, err, err_len)) return rc;
+    for (int l = 0; l < n_layers; ++l) {
+        pj.l[l].w_out = (__nv_bfloat16*)(scratch + off[l][0]);
+        pj.l[l].b_out = (float*)(scratch + off[l][1]);
+        j.d.w[l] = pj.l[l].w_out;
+        j.d.b[l] = pj.l[l].b_out;
+    }
+    j.in = d_in;
+    j.o.out = d_out;
+    cudaStream_t st = (cudaStream_t)stream;
+    int pack_blocks = (int)((max_elems + 256 * 8 - 1) / (256 * 8));
+    go2_mlp_pack_kernel<<<dim3(pack_blocks, n_layers), 256, 0, st>>>(pj);
+    go2_mlp_kernel<<<dim3((B + TILE_M - 1) / TILE_M, 1), NTHREADS, SMEM_BYTES, st>>>(j, j, B);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return na_fail(err, err_len, 7, "kernel launch: %s", cudaGetErrorString(e));
+    return 0;
 }
 
 }  // extern "C"

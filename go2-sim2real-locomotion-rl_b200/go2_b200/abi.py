@@ -104,7 +104,7 @@ _EXPORTS = [
     "go2_post", "go2_tick_parity", "go2_step_host_begin", "go2_read_stats_async", "go2_stats_fetch", "go2_launch_shape",
 ]
 # include/go2_policy.h (CUDA library only; the host-emulation test library has no tensor cores to emulate)
-_POLICY_EXPORTS = ["go2_mlp_create", "go2_mlp_destroy", "go2_mlp_forward", "go2_policy_act", "go2_policy_act_critic", "go2_gae"]
+_POLICY_EXPORTS = ["go2_mlp_create", "go2_mlp_destroy", "go2_mlp_forward", "go2_policy_act", "go2_policy_act_critic", "go2_gae", "go2_mlp_forward_noalloc"]
 _DTYPES = {0: np.float32, 1: np.int32, 2: np.uint8}
 
 

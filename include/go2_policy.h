@@ -6,6 +6,7 @@
  */
 #ifndef GO2_POLICY_H
 #define GO2_POLICY_H
+#include <stddef.h>
 #include <stdint.h>
 #ifdef __cplusplus
 extern "C" {
@@ -39,6 +40,21 @@ int go2_policy_act_critic(go2_mlp* actor, go2_mlp* critic, const float* d_obs, c
  * rewards / values / returns / advantages are [T][B] f32, dones [T][B] u8, last_values [B]. */
 int go2_gae(const float* d_rewards, const uint8_t* d_dones, const float* d_values, const float* d_last_values, int T, int B, float gamma,
             float lam, float* d_returns, float* d_advantages, void* stream);
+
+/* go2_mlp_forward without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * d_out[B][dims[n_layers]] = mlp(d_in[B][dims[0]]) like go2_mlp_create + go2_mlp_forward, but `d_params` is DEVICE f32 memory of the
+ * caller in the layout go2_mlp_create takes on the host (per layer: Linear weight [out][in] row-major, then bias [out]); it is packed
+ * on the device into a file-scope `static __device__` array of GO2_MLP_NOALLOC_SCRATCH_BYTES = 1 MiB that every GPU loading the
+ * library holds until exit, and the same tcgen05 kernel runs from there.  The call performs no cudaMalloc / cudaFree / allocating
+ * library routine; the first call on a device looks up the array's device address (cudaGetSymbolAddress) and sets the kernel's
+ * shared-memory attribute - make it once outside a graph capture.  A network whose packed image exceeds the array is rejected with
+ * rc 8 and a message in `err` (NUL-terminated, may be NULL).  All calls on a device share the array: two calls that overlap on the
+ * GPU (different streams, no ordering) race; calls on one stream are safe, each call rewrites every byte it reads.
+ * rc: 0 ok, 1 bad argument, 2 unsupported widths, 3 device, 6 / 9 set-up, 7 launch, 8 scratch too small. */
+#define GO2_MLP_NOALLOC_SCRATCH_BYTES (1u << 20)
+int go2_mlp_forward_noalloc(const int32_t* dims, int n_layers, const float* d_params, int device, const float* d_in, int B, float* d_out,
+                            void* stream, char* err, int err_len);
 
 #ifdef __cplusplus
 }
