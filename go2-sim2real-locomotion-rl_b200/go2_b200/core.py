@@ -74,6 +74,8 @@ class Go2Core:
     # ---- the tick
     def step(self, actions: torch.Tensor, sp: abi.StepParams):
         a = actions
+        if a.numel() != self.B * self.cfg.num_actions:  # the kernel reads num_actions floats per env: a short tensor would be read past its end
+            raise ValueError(f"actions must be [{self.B}, {self.cfg.num_actions}], got {tuple(a.shape)}")
         if a.dtype != torch.float32 or not a.is_contiguous() or a.device != self.device:
             a = a.to(device=self.device, dtype=torch.float32).contiguous()
         self._last_actions_ref = a  # keep alive until the next call

@@ -31,7 +31,7 @@ def test_eval_scenario_pushes_payload_friction_and_respawn(hostemu_lib):
     assert "push_force_range" not in cfgs[0] and cfgs[0]["curriculum"]["enabled"] is False and cfgs[2]["reward_scales"] == {}
     assert cfgs[1]["num_privileged_obs"] is None and cfgs[0]["termination_if_roll_greater_than"] == 1e9
     B = 6
-    zeros = torch.zeros(B, 12)
+    zeros = torch.zeros(B, 16)  # walk cfg: 12 position + 4 stiffness actions
 
     def run(scn, steps=30, seed=5):
         env = make_env("walk", cfgs, B, "hostemu", hostemu_lib, seed=seed)
@@ -78,3 +78,15 @@ def test_eval_scenario_pushes_payload_friction_and_respawn(hostemu_lib):
     env5.base_pos[torch.tensor([1, 4]), 2] = 0.05
     assert scn.after_step(env5) == 2 and scn.respawns == 2
     assert torch.allclose(env5.core.buf["qpos"][torch.tensor([1, 4]), 2], env5.base_init_pos[2].expand(2))
+
+
+def test_step_rejects_a_short_action_tensor(hostemu_lib):
+    """The kernel reads num_actions floats per env; a [B, 12] tensor on the 16-action walk env must not be read past its end."""
+    import pytest
+    from util import make_env
+
+    cfgs = json.load(open(os.path.join(ROOT, "go2-sim2real-locomotion-rl_b200/go2_b200/cfgs/walk.json")))
+    env = make_env("walk", cfgs, 4, "hostemu", hostemu_lib, seed=1)
+    env.reset()
+    with pytest.raises(ValueError, match="actions must be"):
+        env.step(torch.zeros(4, 12))
