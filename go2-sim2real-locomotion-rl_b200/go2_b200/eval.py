@@ -55,6 +55,40 @@ def eval_cfgs(cfgs, terminate=False, kp=None, kd=None):
     return env_cfg, obs_cfg, reward_cfg, command_cfg
 
 
+def respawn(env, envs_idx, terrain_row=None):
+    """Put the given envs back on their spawn point with the default pose and cleared action buffers: `respawn_at_start` of
+    go2_eval_stairs.py:314-361 (spawn = centre of the env's terrain row + base height) and the flat-ground branch of
+    `respawn_on_tile` of go2_eval_walk.py:399-413,471-488, for any set of envs.  `terrain_row` moves them to that row first."""
+    ii = torch.as_tensor(envs_idx, device=env.device).long().reshape(-1)
+    n = int(ii.numel())
+    if n == 0:
+        return
+    spawn = env.base_init_pos.expand(n, 3).clone()
+    if getattr(env, "_use_terrain", False):
+        if terrain_row is not None:
+            env._env_terrain_row[ii] = int(terrain_row)
+        centers = torch.tensor(env._terrain_row_centers, device=env.device, dtype=torch.float32)
+        spawn = centers[env._env_terrain_row[ii].long()].clone()
+        spawn[:, 2] += env.base_init_pos[2]
+    env.dof_pos[ii] = env.default_dof_pos
+    env.dof_vel[ii] = 0.0
+    env.robot.set_dofs_position(env.default_dof_pos.expand(n, 12), env.motors_dof_idx, zero_velocity=True, envs_idx=ii)
+    env.base_pos[ii] = spawn
+    env.base_quat[ii] = env.base_init_quat
+    env.robot.set_pos(spawn, zero_velocity=False, envs_idx=ii)
+    env.robot.set_quat(env.base_init_quat.expand(n, 4), zero_velocity=False, envs_idx=ii)
+    env.robot.zero_all_dofs_velocity(ii)
+    for name in ("last_actions", "last_dof_vel", "_applied_actions", "base_lin_vel", "base_ang_vel"):
+        b = getattr(env, name, None)
+        if b is not None:
+            b[ii] = 0.0
+    if getattr(env, "_action_history", None) is not None:
+        env._action_history[ii] = 0.0
+    env.episode_length_buf[ii] = 0
+    if hasattr(env, "_last_base_pos_x"):
+        env._last_base_pos_x[ii] = spawn[:, 0]
+
+
 class EvalScenario:
     """The eval-time disturbance knobs of go2_eval_walk.py:31-112, batched over all envs (the script runs one env).
 
@@ -148,20 +182,20 @@ class EvalScenario:
             a = self.delay_line[0]
         return a
 
+    @staticmethod
+    def _ground_z(env):
+        if getattr(env, "_use_terrain", False):
+            return env._get_terrain_height(env.base_pos[:, 0], env.base_pos[:, 1])
+        return 0.0
+
     def after_step(self, env):
         """Put fallen envs back on their spawn pose (the R key of the eval scripts); returns how many."""
         if not self.respawn_on_fall:
             return 0
-        fallen = torch.nonzero(env.base_pos[:, 2] < self.fall_height).flatten()
+        fallen = torch.nonzero(env.base_pos[:, 2] - self._ground_z(env) < self.fall_height).flatten()
         n = int(fallen.numel())
         if n:
-            env.robot.set_pos(env.base_init_pos.expand(n, 3), zero_velocity=False, envs_idx=fallen)
-            env.robot.set_quat(env.base_init_quat.expand(n, 4), zero_velocity=False, envs_idx=fallen)
-            env.robot.set_dofs_position(env.default_dof_pos.expand(n, 12), list(range(6, 18)), zero_velocity=True, envs_idx=fallen)
-            for name in ("last_actions", "actions"):
-                b = getattr(env, name, None)
-                if b is not None:
-                    b[fallen] = 0.0
+            respawn(env, fallen)
             for line in self.delay_line:
                 line[fallen] = 0.0
             self.respawns += n

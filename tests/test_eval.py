@@ -90,3 +90,29 @@ def test_step_rejects_a_short_action_tensor(hostemu_lib):
     env.reset()
     with pytest.raises(ValueError, match="actions must be"):
         env.step(torch.zeros(4, 12))
+
+
+def test_respawn_on_a_terrain_row_of_the_stair_env(hostemu_lib):
+    """respawn() = respawn_at_start of go2_eval_stairs.py:314-361: row centre + base height, default pose, cleared action buffers."""
+    from util import make_env
+
+    cfgs = g2eval.eval_cfgs(json.load(open(os.path.join(ROOT, "go2-sim2real-locomotion-rl_b200/go2_b200/cfgs/stair.json"))))
+    env = make_env("stair", cfgs, 4, "hostemu", hostemu_lib, seed=2)
+    env._lock_terrain_rows = True
+    env.reset()
+    a = 0.3 * torch.ones(4, env.num_actions)
+    for _ in range(5):
+        env.step(a)
+    assert float(env.last_actions.abs().max()) > 0
+    g2eval.respawn(env, [1, 3], terrain_row=5)
+    cx, cy, cz = env._terrain_row_centers[5]
+    q = env.core.buf["qpos"]
+    for e in (1, 3):
+        assert int(env._env_terrain_row[e]) == 5
+        assert torch.allclose(q[e, :3], torch.tensor([cx, cy, cz + float(env.base_init_pos[2])]), atol=1e-6)
+        assert torch.allclose(q[e, 3:7], env.base_init_quat) and float(env.core.buf["qvel"][e].abs().max()) == 0.0
+        assert float(env.last_actions[e].abs().max()) == 0.0 and float(env._action_history[e].abs().max()) == 0.0
+        assert int(env.episode_length_buf[e]) == 0 and abs(float(env._last_base_pos_x[e]) - cx) < 1e-6
+    assert float(env.last_actions[0].abs().max()) > 0  # the other envs are untouched
+    obs, rew, done, _ = env.step(torch.zeros(4, env.num_actions))
+    assert torch.isfinite(obs).all() and not bool(done[1]) and not bool(done[3])
