@@ -30,6 +30,26 @@ struct Rng {
 G2_HD u4 rng4(const Rng& r, uint32_t slot) { return philox(r.env, r.step, slot, 0u, r.k0, r.k1); }
 G2_HD float urange(float lo, float hi, uint32_t x) { return (hi - lo) * u01(x) + lo; }
 
+// Stair difficulty row of a reset env (go2_env_stair.py:809-854).  The reference splits the n envs reset in a tick into
+// int(0.4 n) frontier rows, int(0.3 n) near-frontier rows and the rest easy rows, then shuffles: a reset env is on the frontier
+// with probability int(0.4 n) / n etc.  (n = 1 or 2: always an easy row; large n: 40 / 30 / 30).  Drawn per env with exactly
+// those probabilities: same expected counts for every n, counts multinomial instead of fixed.  n <= 0: the large-n limit.
+G2_HD int stair_pick_row(u4 rr, int mr, int n) {
+    float pf = 0.4f, pn = 0.3f;
+    if (n > 0) {
+        pf = (float)(int)((double)n * 0.40) / (float)n;
+        pn = (float)(int)((double)n * 0.30) / (float)n;
+    }
+    float u = u01(rr.a);
+    if (u < pf) return mr;
+    if (u < pf + pn) {
+        if (mr >= 2) { int lo = mr - 2, hi = mr - 1; return lo + (int)(rr.b % (uint32_t)(hi - lo + 1)); }
+        return mr;
+    }
+    int emax = mr >= 3 ? mr - 3 : 0;
+    return (int)(rr.c % (uint32_t)(emax + 1));
+}
+
 // quaternion -> extrinsic roll/pitch/yaw in degrees (genesis/utils/geom.py:718-775 with rpy=True)
 G2_HD v3 quat_to_rpy_deg(q4 q) {
     float ww = q.w * q.w, wx = q.w * q.x, wy = q.w * q.y, wz = q.w * q.z;
@@ -275,19 +295,9 @@ G2_HDN void reset_env(const Go2Model& m, const EnvConfig& cfg, const StepParams&
     u4 rq = rng4(rng, SLOT_RESET + 10);
     if (cfg.kind == ENV_STAIR) {
         if (cfg.has_terrain && cfg.n_terrain_rows > 1 && !sp.lock_terrain_rows) {
-            // frontier-heavy row assignment (go2_env_stair.py:809-854): 40 % on the highest accessible row, 30 % on the
-            // two rows below it, 30 % on the easy rows - drawn per env instead of by exact counts + permutation
-            u4 rr = rng4(rng, SLOT_RESET + 12);
-            int mr = sp.terrain_max_row, row;
-            float u = u01(rr.a);
-            if (u < 0.4f) row = mr;
-            else if (u < 0.7f) {
-                if (mr >= 2) { int lo = mr - 2, hi = mr - 1; row = lo + (int)(rr.b % (uint32_t)(hi - lo + 1)); }
-                else row = mr;
-            } else {
-                int emax = mr >= 3 ? mr - 3 : 0;
-                row = (int)(rr.c % (uint32_t)(emax + 1));
-            }
+            // provisional when the number of resets of this tick is not known yet (n_resets_hint = 0): the post-pass redraws
+            // with the true count (post_stair_rows)
+            int row = stair_pick_row(rng4(rng, SLOT_RESET + 12), sp.terrain_max_row, sp.n_resets_hint);
             e.terrain_row = rp ? (int)rp[RP_ROW] : row;
         }
         if (cfg.has_terrain) {  // spawn at the row centre, robot standing height on top (go2_env_stair.py:856-871)
@@ -458,6 +468,28 @@ G2_HDN void env_pre(const Go2Model& m, const EnvConfig& cfg, const StepParams& s
 
 // Scalar part of the tick AFTER the physics: read-back, foot contacts, command resampling, termination,
 // rewards, reset (+ DR draws), observations, write-back of the env-level buffers.
+// tail of the stair env's privileged obs (go2_env_stair.py:1466-1484): terrain difficulty of the env's row, then the body-frame
+// height scan around the base; `k` = first index of the tail (num_obs + 55)
+G2_HD void stair_priv_tail(const Go2Model& m, const EnvConfig& cfg, float* pr, int k, int terrain_row, v3 base_pos, q4 q) {
+    if (k < cfg.num_priv) {
+        int den = cfg.n_terrain_rows - 1 > 1 ? cfg.n_terrain_rows - 1 : 1;
+        pr[k++] = cfg.has_terrain ? (float)terrain_row / (float)den : 0.0f;
+    }
+    int ns = cfg.scan_nx * cfg.scan_ny;
+    if (ns > 0 && k + ns <= cfg.num_priv) {
+        float yaw = atan2f(2.0f * (q.w * q.z + q.x * q.y), 1.0f - 2.0f * (q.y * q.y + q.z * q.z));
+        float cy = cosf(yaw), sy = sinf(yaw);
+        for (int ix = 0; ix < cfg.scan_nx; ++ix) {
+            float lx = cfg.scan_nx > 1 ? cfg.scan_x0 + (cfg.scan_x1 - cfg.scan_x0) * (float)ix / (float)(cfg.scan_nx - 1) : cfg.scan_x0;
+            for (int iy = 0; iy < cfg.scan_ny; ++iy) {
+                float ly = cfg.scan_ny > 1 ? cfg.scan_y0 + (cfg.scan_y1 - cfg.scan_y0) * (float)iy / (float)(cfg.scan_ny - 1) : cfg.scan_y0;
+                float wx = base_pos.x + cy * lx - sy * ly, wy = base_pos.y + sy * lx + cy * ly;
+                pr[k++] = cfg.has_terrain ? terrain_height(m, wx, wy) - base_pos.z : 0.0f;
+            }
+        }
+    }
+}
+
 template <class P>
 G2_HDN void env_post(const Go2Model& m, const EnvConfig& cfg, const StepParams& sp, const Buffers& bf, int b, P& p, EnvLocal& e,
                      EnvStepOut& out) {
@@ -582,26 +614,7 @@ G2_HDN void env_post(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
             pr[k++] = go[0]; pr[k++] = go[1]; pr[k++] = go[2];
             pr[k++] = F32(B_CUR_PUSH)[b * 3]; pr[k++] = F32(B_CUR_PUSH)[b * 3 + 1]; pr[k++] = F32(B_CUR_PUSH)[b * 3 + 2];
             pr[k++] = cfg.max_delay > 0 ? (float)I32(B_DELAY)[b] / (float)cfg.max_delay : 0.0f;
-            if (cfg.kind == ENV_STAIR) {  // go2_env_stair.py:1466-1484: terrain difficulty, then the height scan
-                if (k < cfg.num_priv) {
-                    int den = cfg.n_terrain_rows - 1 > 1 ? cfg.n_terrain_rows - 1 : 1;
-                    pr[k++] = cfg.has_terrain ? (float)e.terrain_row / (float)den : 0.0f;
-                }
-                int ns = cfg.scan_nx * cfg.scan_ny;
-                if (ns > 0 && k + ns <= cfg.num_priv) {
-                    q4 q = e.base_quat;
-                    float yaw = atan2f(2.0f * (q.w * q.z + q.x * q.y), 1.0f - 2.0f * (q.y * q.y + q.z * q.z));
-                    float cy = cosf(yaw), sy = sinf(yaw);
-                    for (int ix = 0; ix < cfg.scan_nx; ++ix) {
-                        float lx = cfg.scan_nx > 1 ? cfg.scan_x0 + (cfg.scan_x1 - cfg.scan_x0) * (float)ix / (float)(cfg.scan_nx - 1) : cfg.scan_x0;
-                        for (int iy = 0; iy < cfg.scan_ny; ++iy) {
-                            float ly = cfg.scan_ny > 1 ? cfg.scan_y0 + (cfg.scan_y1 - cfg.scan_y0) * (float)iy / (float)(cfg.scan_ny - 1) : cfg.scan_y0;
-                            float wx = e.base_pos.x + cy * lx - sy * ly, wy = e.base_pos.y + sy * lx + cy * ly;
-                            pr[k++] = cfg.has_terrain ? terrain_height(m, wx, wy) - e.base_pos.z : 0.0f;
-                        }
-                    }
-                }
-            }
+            if (cfg.kind == ENV_STAIR) stair_priv_tail(m, cfg, pr, k, e.terrain_row, e.base_pos, e.base_quat);
         }
         F32(B_REW)[b] = rew;
         for (int i = 0; i < A; ++i) e.last_act[i] = e.act[i];
@@ -799,6 +812,32 @@ G2_HD void post_patch_priv(const EnvConfig& cfg, const float* g, float* pr) {
     pr[k++] = g[G_MASS_SHIFT];
     pr[k++] = g[G_COM_SHIFT]; pr[k++] = g[G_COM_SHIFT + 1]; pr[k++] = g[G_COM_SHIFT + 2];
     for (int i = 0; i < 4; ++i) pr[k++] = cfg.has_leg_mass_dr ? g[G_MASS_SHIFT + cfg.hip_link[i]] : 0.0f;
+}
+
+// Post-pass, stair env: the row of every env reset in this tick is redrawn with the tick's true reset count n (all ranks) -
+// the step kernel could only draw provisionally (stair_pick_row) - and everything the spawn point feeds is redone exactly as
+// reset_env does it: qpos xyz, the base_pos / last_x / terrain_row buffers and the tail of the privileged obs.
+G2_HD bool post_stair_rows_due(const EnvConfig& cfg, const StepParams& sp, float n_resets) {
+    return cfg.kind == ENV_STAIR && cfg.has_terrain && cfg.n_terrain_rows > 1 && !sp.lock_terrain_rows && !sp.replay_on &&
+           !sp.force_reset_all && sp.n_resets_hint == 0 && n_resets >= 0.5f;
+}
+G2_HD void post_stair_rows(const Go2Model& m, const EnvConfig& cfg, const StepParams& sp, const Buffers& bf, int b, int n) {
+    if (!U8(B_RESET)[b]) return;
+    Rng rng;
+    rng.env = (uint32_t)(cfg.env_offset + b); rng.step = sp.step_count; rng.k0 = cfg.seed_lo; rng.k1 = cfg.seed_hi;
+    int row = stair_pick_row(rng4(rng, SLOT_RESET + 12), sp.terrain_max_row, n);
+    if (row == I32(B_TERRAIN_ROW)[b]) return;
+    v3 pos = mk3(cfg.row_center[row][0], cfg.row_center[row][1], cfg.row_center[row][2] + cfg.base_init_pos[2]);
+    if (cfg.has_init_z) {
+        u4 rq = rng4(rng, SLOT_RESET + 10);
+        pos.z = pos.z + urange(cfg.init_z_lo, cfg.init_z_hi, rq.a) - cfg.base_init_pos[2] + cfg.base_init_pos[2];
+    }
+    I32(B_TERRAIN_ROW)[b] = row;
+    F32(B_QPOS)[b * NQ] = pos.x; F32(B_QPOS)[b * NQ + 1] = pos.y; F32(B_QPOS)[b * NQ + 2] = pos.z;
+    F32(B_BASE_POS)[b * 3] = pos.x; F32(B_BASE_POS)[b * 3 + 1] = pos.y; F32(B_BASE_POS)[b * 3 + 2] = pos.z;
+    F32(B_LAST_X)[b] = pos.x;
+    if (cfg.num_priv > 0)
+        stair_priv_tail(m, cfg, F32(B_PRIV) + (size_t)b * cfg.num_priv, cfg.num_obs + 55, row, pos, ld4(F32(B_BASE_QUAT) + b * 4));
 }
 
 #undef F32

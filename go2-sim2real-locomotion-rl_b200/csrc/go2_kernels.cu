@@ -102,7 +102,8 @@ __global__ void __launch_bounds__(GO2_TPB_SMALL) go2_step_kernel_small(const Go2
 // Post-pass of a tick (go2_env.cuh: post_globals).  Every block recomputes the (deterministic) decision from this tick's
 // statistics row and the globals in force, and patches its envs' privileged obs; block 0 also publishes the next
 // tick's globals slot, folds the statistics into the accumulator row and clears the next tick's statistics row.
-__global__ void __launch_bounds__(256) go2_post_kernel(const EnvConfig* __restrict__ gcfg, StepParams sp, Buffers bf) {
+__global__ void __launch_bounds__(256) go2_post_kernel(const Go2Model* __restrict__ gm, const EnvConfig* __restrict__ gcfg, StepParams sp,
+                                                       Buffers bf) {
     const EnvConfig& cfg = *gcfg;
     float* stats = (float*)bf.p[B_STATS];
     const float* tick = stats + sp.parity * STATS_LEN;
@@ -113,6 +114,10 @@ __global__ void __launch_bounds__(256) go2_post_kernel(const EnvConfig* __restri
     if (changed && sp.do_physics && cfg.num_priv > 0) {
         for (int b = blockIdx.x * blockDim.x + threadIdx.x; b < bf.B; b += gridDim.x * blockDim.x)
             post_patch_priv(cfg, g, (float*)bf.p[B_PRIV] + (size_t)b * cfg.num_priv);
+    }
+    if (post_stair_rows_due(cfg, sp, tick[STATS_RESETS])) {  // stair: rows of the envs reset in this tick, with the true reset count
+        const int n = (int)(tick[STATS_RESETS] + 0.5f);
+        for (int b = blockIdx.x * blockDim.x + threadIdx.x; b < bf.B; b += gridDim.x * blockDim.x) post_stair_rows(*gm, cfg, sp, bf, b, n);
     }
     if (blockIdx.x == 0) {
         if (threadIdx.x < GLOBALS_LEN) nxt[threadIdx.x] = g[threadIdx.x];
@@ -239,9 +244,9 @@ int go2_buffer_info(go2_handle* h, int id, void** ptr, int* dtype, int* rows, in
 static int launch_post(go2_handle* h, const StepParams& sp, cudaStream_t s) {
     const EnvConfig& c = h->cfg;
     // the privileged-obs patch is the only per-env work; one block is enough for the flavours without it
-    int blocks = (c.num_priv > 0 && c.kind != ENV_BASE) ? (c.num_envs + 255) / 256 : 1;
+    int blocks = ((c.num_priv > 0 && c.kind != ENV_BASE) || c.kind == ENV_STAIR) ? (c.num_envs + 255) / 256 : 1;
     if (blocks > 1184) blocks = 1184;
-    go2_post_kernel<<<blocks, 256, 0, s>>>(h->d_cfg, sp, h->bf);
+    go2_post_kernel<<<blocks, 256, 0, s>>>(h->d_model, h->d_cfg, sp, h->bf);
     h->launches += 1;
     h->parity ^= 1;
     h->post_pending = 0;

@@ -162,6 +162,7 @@ struct StepParams {
     int force_reset_all;
     int terrain_max_row;       // stair: int(curriculum_level * (rows - 1))
     int lock_terrain_rows;     // stair eval: keep each env's row across resets
+    int n_resets_hint;         // stair: number of envs (all ranks) this launch resets when the host knows it (reset of all envs), else 0
     // candidates of the global physics DR (already lerped with this tick's t_sample); the post-pass kernel puts them in
     // force if an env reset in this tick - B_GLOBALS holds the values in force
     float cand_friction, cand_mass, cand_com[3], cand_leg[4];

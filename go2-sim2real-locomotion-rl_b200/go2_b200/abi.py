@@ -91,7 +91,7 @@ class StepParams(C.Structure):
         ("kp_lo", _f), ("kp_hi", _f), ("kd_lo", _f), ("kd_hi", _f),
         ("delay_lo", _i), ("delay_hi", _i),
         ("kp_genesis", _f), ("kd_genesis", _f),
-        ("do_physics", _i), ("force_reset_all", _i), ("terrain_max_row", _i), ("lock_terrain_rows", _i),
+        ("do_physics", _i), ("force_reset_all", _i), ("terrain_max_row", _i), ("lock_terrain_rows", _i), ("n_resets_hint", _i),
         ("cand_friction", _f), ("cand_mass", _f), ("cand_com", _f * 3), ("cand_leg", _f * 4),
         ("parity", _i), ("defer_post", _i), ("replay_on", _i), ("ext_on", _i),
         ("host_obs", C.c_void_p), ("host_rew", C.c_void_p), ("host_done", C.c_void_p),

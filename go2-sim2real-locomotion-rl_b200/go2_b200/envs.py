@@ -768,6 +768,9 @@ class Go2EnvStair(Go2EnvWalk):
         mr = int(lvl * (self._num_terrain_rows - 1))
         sp.terrain_max_row = max(0, min(mr, self._num_terrain_rows - 1))
         sp.lock_terrain_rows = int(self._lock_terrain_rows)
+        # reset(): every env of every rank resets, the count the row split depends on is known up front; in a regular tick the
+        # post-pass kernel redraws the rows of the reset envs once the tick's (all-rank) reset count is known
+        sp.n_resets_hint = 0 if sp.do_physics else self._total_envs
 
     def _after_resets(self, stats):
         super()._after_resets(stats)

@@ -73,6 +73,10 @@ static void post(go2_handle* h, const StepParams& sp) {
     bool changed = post_globals(cfg, sp, tick[STATS_RESETS], cur, g);
     if (changed && sp.do_physics && cfg.num_priv > 0)
         for (int b = 0; b < cfg.num_envs; ++b) post_patch_priv(cfg, g, (float*)h->bf.p[B_PRIV] + (size_t)b * cfg.num_priv);
+    if (post_stair_rows_due(cfg, sp, tick[STATS_RESETS])) {
+        const int n = (int)(tick[STATS_RESETS] + 0.5f);
+        for (int b = 0; b < cfg.num_envs; ++b) post_stair_rows(h->model, cfg, sp, h->bf, b, n);
+    }
     for (int i = 0; i < GLOBALS_LEN; ++i) nxt[i] = g[i];
     for (int i = 0; i < STATS_LEN; ++i) {
         stats[2 * STATS_LEN + i] += tick[i];
