@@ -67,6 +67,7 @@ enum BufId {
     B_REPLAY,        // f32 [B][REPLAY_LEN] replayed random draws (cfg.replay_rows, StepParams.replay_on)
     B_FK_FRESH,      // u8  [B]  1 = the env's kinematics were refreshed (reset / state setter) after the last global mass / COM change
     B_EXT_FORCE,     // f32 [B][4]  external force of the tick: robot-local link (as float), fx, fy, fz (world frame, at the link origin)
+    B_ACTOR_SCAN,    // f32 [B][n_actor_scan]  lidar variant: the actor scan in the obs (kept: a stale scan is replayed on "latency")
     B_COUNT
 };
 

@@ -12,11 +12,17 @@
 
 namespace go2 {
 
+// -DG2_NO_LIDAR: A/B build without the lidar variant's code paths (profiles/r02_experiments.md)
+#ifdef G2_NO_LIDAR
+#define G2_LIDAR_ON(cfg) false
+#else
+#define G2_LIDAR_ON(cfg) ((cfg).lidar_on != 0)
+#endif
 #define F32(id) ((float*)bf.p[id])
 #define I32(id) ((int*)bf.p[id])
 #define U8(id) ((uint8_t*)bf.p[id])
 
-enum RngSlot { SLOT_ACT_NOISE = 0, SLOT_OBS_NOISE = 8, SLOT_PUSH = 32, SLOT_CMD = 33, SLOT_CMD_RESET = 34, SLOT_RESET = 40 };
+enum RngSlot { SLOT_ACT_NOISE = 0, SLOT_OBS_NOISE = 8, SLOT_PUSH = 32, SLOT_CMD = 33, SLOT_CMD_RESET = 34, SLOT_RESET = 40, SLOT_LIDAR = 56 };
 
 struct EnvStepOut {
     int reset, timeout;
@@ -330,6 +336,8 @@ G2_HDN void reset_env(const Go2Model& m, const EnvConfig& cfg, const StepParams&
         }
         for (int i = 0; i < 4; ++i) { e.air[i] = 0.0f; e.fc[i] = 0; e.lfc[i] = 0; }
         e.last_x = e.base_pos.x;  // stair: forward_progress restarts at the spawn (go2_env_stair.py:1568)
+        if (G2_LIDAR_ON(cfg))  // go2_env_stair_lidar.py: reset_idx zeroes the scan buffers of the reset envs
+            for (int i = 0; i < cfg.n_actor_scan; ++i) F32(B_ACTOR_SCAN)[(size_t)b * cfg.n_actor_scan + i] = 0.0f;
     }
     // episode statistics, then clear the sums
     float ep_s = fmaxf((float)e.ep_len, 1.0f) * dt;
@@ -468,17 +476,74 @@ G2_HDN void env_pre(const Go2Model& m, const EnvConfig& cfg, const StepParams& s
 
 // Scalar part of the tick AFTER the physics: read-back, foot contacts, command resampling, termination,
 // rewards, reset (+ DR draws), observations, write-back of the env-level buffers.
+// one simulated-lidar sample: terrain height under the body-frame point (lx, ly) of a base at `pos` with yaw (cy, sy), relative to
+// the base (go2_env_stair_lidar.py:895-937 _compute_lidar_scan; zeros without terrain)
+G2_HD float lidar_point(const Go2Model& m, const EnvConfig& cfg, v3 pos, float cy, float sy, float lx, float ly) {
+    if (!cfg.has_terrain) return 0.0f;
+    return terrain_height(m, pos.x + cy * lx - sy * ly, pos.y + sy * lx + cy * ly) - pos.z;
+}
+G2_HD void yaw_cs(q4 q, float& cy, float& sy) {
+    float yaw = atan2f(2.0f * (q.w * q.z + q.x * q.y), 1.0f - 2.0f * (q.y * q.y + q.z * q.z));
+    cy = cosf(yaw); sy = sinf(yaw);
+}
+// Actor lidar scan of the tick with the sim-to-real noise model, in the reference's order (go2_env_stair_lidar.py:939-1002):
+// per-cell Gaussian noise, per-cell dropout (-> 0 = base height), per-env vertical offset, per-env latency (the previous tick's scan
+// is replayed), per-env blackout (-> 0), clip, scale.  All probabilities / stds scale with the DR level (lidar_noise_level).
+// B_ACTOR_SCAN holds the previous scan on entry and the new one on exit.
+G2_HDN void lidar_update(const Go2Model& m, const EnvConfig& cfg, const StepParams& sp, const Buffers& bf, int b, const Rng& rng,
+                         const float* rp, v3 pos, q4 q) {
+    const int n = cfg.n_actor_scan;
+    if (n <= 0) return;
+    float* buf = F32(B_ACTOR_SCAN) + (size_t)b * n;
+    const float lvl = sp.lidar_noise_level;
+    float cy, sy;
+    yaw_cs(q, cy, sy);
+    u4 rv = rng4(rng, SLOT_LIDAR + 16);
+    float zv, zv2;
+    boxmuller(rv.a, rv.b, zv, zv2);
+    const float v = rp ? rp[RP_LIDAR_V] : zv;
+    const float ulat = rp ? rp[RP_LIDAR_V + 1] : u01(rv.c), ublk = rp ? rp[RP_LIDAR_V + 2] : u01(rv.d);
+    const bool on = lvl > 0.0f;
+    const bool lat = on && cfg.lidar_latency > 0.0f && ulat < cfg.lidar_latency * lvl;
+    const bool blk = on && cfg.lidar_blackout > 0.0f && ublk < cfg.lidar_blackout * lvl;
+    for (int i0 = 0; i0 < n; i0 += 4) {
+        u4 rn = rng4(rng, SLOT_LIDAR + (i0 >> 2)), ru = rng4(rng, SLOT_LIDAR + 8 + (i0 >> 2));
+        float z[4];
+        boxmuller(rn.a, rn.b, z[0], z[1]);
+        boxmuller(rn.c, rn.d, z[2], z[3]);
+        const float u[4] = {u01(ru.a), u01(ru.b), u01(ru.c), u01(ru.d)};
+        for (int j = 0; j < 4 && i0 + j < n; ++j) {
+            const int i = i0 + j;
+            float raw = lidar_point(m, cfg, pos, cy, sy, cfg.actor_lx[i], cfg.actor_ly[i]);
+            if (on && cfg.lidar_noise_std > 0.0f) raw = raw + ((rp ? rp[RP_LIDAR_N + i] : z[j]) * cfg.lidar_noise_std) * lvl;
+            if (on && cfg.lidar_dropout > 0.0f && (rp ? rp[RP_LIDAR_U + i] : u[j]) < cfg.lidar_dropout * lvl) raw = 0.0f;
+            if (on && cfg.lidar_voffset_std > 0.0f) raw = raw + (v * cfg.lidar_voffset_std) * lvl;
+            if (lat) raw = buf[i];
+            if (blk) raw = 0.0f;
+            buf[i] = clampf(raw, -cfg.lidar_clip, cfg.lidar_clip) * cfg.lidar_scale;
+        }
+    }
+}
+
 // tail of the stair env's privileged obs (go2_env_stair.py:1466-1484): terrain difficulty of the env's row, then the body-frame
-// height scan around the base; `k` = first index of the tail (num_obs + 55)
-G2_HD void stair_priv_tail(const Go2Model& m, const EnvConfig& cfg, float* pr, int k, int terrain_row, v3 base_pos, q4 q) {
+// height scan around the base - or, in the lidar variant, the clean critic lidar scan of the tick's pre-reset pose (zeros for an
+// env reset in this tick, go2_env_stair_lidar.py:1004-1015,1689-1692); `k` = first index of the tail (num_obs + 55)
+G2_HD void stair_priv_tail(const Go2Model& m, const EnvConfig& cfg, float* pr, int k, int terrain_row, v3 base_pos, q4 q, bool was_reset) {
     if (k < cfg.num_priv) {
         int den = cfg.n_terrain_rows - 1 > 1 ? cfg.n_terrain_rows - 1 : 1;
         pr[k++] = cfg.has_terrain ? (float)terrain_row / (float)den : 0.0f;
     }
+    float cy, sy;
+    yaw_cs(q, cy, sy);
+    if (G2_LIDAR_ON(cfg)) {
+        if (cfg.n_critic_scan > 0 && k + cfg.n_critic_scan <= cfg.num_priv)
+            for (int i = 0; i < cfg.n_critic_scan; ++i)
+                pr[k++] = was_reset ? 0.0f
+                                    : clampf(lidar_point(m, cfg, base_pos, cy, sy, cfg.critic_lx[i], cfg.critic_ly[i]), -cfg.lidar_clip, cfg.lidar_clip) * cfg.lidar_scale;
+        return;
+    }
     int ns = cfg.scan_nx * cfg.scan_ny;
     if (ns > 0 && k + ns <= cfg.num_priv) {
-        float yaw = atan2f(2.0f * (q.w * q.z + q.x * q.y), 1.0f - 2.0f * (q.y * q.y + q.z * q.z));
-        float cy = cosf(yaw), sy = sinf(yaw);
         for (int ix = 0; ix < cfg.scan_nx; ++ix) {
             float lx = cfg.scan_nx > 1 ? cfg.scan_x0 + (cfg.scan_x1 - cfg.scan_x0) * (float)ix / (float)(cfg.scan_nx - 1) : cfg.scan_x0;
             for (int iy = 0; iy < cfg.scan_ny; ++iy) {
@@ -520,6 +585,7 @@ G2_HDN void env_post(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
                 e.fc[i] = fabsf(p.cforce[cfg.foot_link[i]].z) > cfg.foot_contact_threshold ? 1 : 0;
             }
         }
+        if (G2_LIDAR_ON(cfg)) lidar_update(m, cfg, sp, bf, b, rng, rp, e.base_pos, e.base_quat);
         if (e.ep_len % cfg.resample_steps == 0) resample_commands(cfg, sp, rng, SLOT_CMD, cfg.env_offset + b, e.cmd, rp ? rp + RP_CMD : nullptr);
     } else {
         for (int i = 0; i < A; ++i) { e.act[i] = 0.0f; e.applied[i] = F32(B_APPLIED)[b * A + i]; }
@@ -532,6 +598,8 @@ G2_HDN void env_post(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
         e.vel_world = mk3(0, 0, 0);
     }
 
+    const v3 lid_pos = e.base_pos;  // pose the lidar scans of this tick were taken from (before a reset moves the base)
+    const q4 lid_q = e.base_quat;
     // ---- termination
     bool tout = e.ep_len > cfg.max_episode_length;
     bool rst = tout;
@@ -593,15 +661,17 @@ G2_HDN void env_post(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
                 boxmuller(r.c, r.d, z[2], z[3]);
                 for (int j = 0; j < 4; ++j) {
                     int idx = 4 * k + j;
-                    if (idx < cfg.num_obs) o[idx] += (rp ? rp[RP_OBS_NOISE + idx] : z[j]) * sp.obs_noise[idx];
+                    if (idx < cfg.num_obs && idx < NOBS_MAX) o[idx] += (rp ? rp[RP_OBS_NOISE + idx] : z[j]) * sp.obs_noise[idx];
                 }
             }
         }
-        for (int i = 0; i < cfg.num_obs; ++i) obs[i] = o[i];
+        const int n_scan = G2_LIDAR_ON(cfg) ? cfg.n_actor_scan : 0, n_prop = cfg.num_obs - n_scan;
+        for (int i = 0; i < n_prop; ++i) obs[i] = o[i];
+        for (int i = 0; i < n_scan; ++i) obs[n_prop + i] = F32(B_ACTOR_SCAN)[(size_t)b * n_scan + i];  // go2_env_stair_lidar.py:1626-1627
         if (cfg.num_priv > 0) {  // go2_env_walk.py:1115-1141
             float* pr = F32(B_PRIV) + (size_t)b * cfg.num_priv;
             int k = 0;
-            for (int i = 0; i < cfg.num_obs; ++i) pr[k++] = o[i];
+            for (int i = 0; i < cfg.num_obs; ++i) pr[k++] = obs[i];
             pr[k++] = e.lin_vel.x * cfg.obs_scale_lin_vel; pr[k++] = e.lin_vel.y * cfg.obs_scale_lin_vel; pr[k++] = e.lin_vel.z * cfg.obs_scale_lin_vel;
             pr[k++] = gl[G_FRIC_GROUND];  // patched by the post-pass kernel when this tick's resets change the global DR
             for (int j = 0; j < NHINGE; ++j) pr[k++] = F32(B_KP_FACTORS)[b * NHINGE + j];
@@ -614,7 +684,8 @@ G2_HDN void env_post(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
             pr[k++] = go[0]; pr[k++] = go[1]; pr[k++] = go[2];
             pr[k++] = F32(B_CUR_PUSH)[b * 3]; pr[k++] = F32(B_CUR_PUSH)[b * 3 + 1]; pr[k++] = F32(B_CUR_PUSH)[b * 3 + 2];
             pr[k++] = cfg.max_delay > 0 ? (float)I32(B_DELAY)[b] / (float)cfg.max_delay : 0.0f;
-            if (cfg.kind == ENV_STAIR) stair_priv_tail(m, cfg, pr, k, e.terrain_row, e.base_pos, e.base_quat);
+            if (cfg.kind == ENV_STAIR)
+                stair_priv_tail(m, cfg, pr, k, e.terrain_row, G2_LIDAR_ON(cfg) ? lid_pos : e.base_pos, G2_LIDAR_ON(cfg) ? lid_q : e.base_quat, rst);
         }
         F32(B_REW)[b] = rew;
         for (int i = 0; i < A; ++i) e.last_act[i] = e.act[i];
@@ -837,7 +908,7 @@ G2_HD void post_stair_rows(const Go2Model& m, const EnvConfig& cfg, const StepPa
     F32(B_BASE_POS)[b * 3] = pos.x; F32(B_BASE_POS)[b * 3 + 1] = pos.y; F32(B_BASE_POS)[b * 3 + 2] = pos.z;
     F32(B_LAST_X)[b] = pos.x;
     if (cfg.num_priv > 0)
-        stair_priv_tail(m, cfg, F32(B_PRIV) + (size_t)b * cfg.num_priv, cfg.num_obs + 55, row, pos, ld4(F32(B_BASE_QUAT) + b * 4));
+        stair_priv_tail(m, cfg, F32(B_PRIV) + (size_t)b * cfg.num_priv, cfg.num_obs + 55, row, pos, ld4(F32(B_BASE_QUAT) + b * 4), true);
 }
 
 #undef F32

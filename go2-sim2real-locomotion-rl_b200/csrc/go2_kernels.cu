@@ -191,7 +191,7 @@ int go2_create(const int32_t* model_iv, int n_iv, const double* model_fv, int n_
     h->d_mip = nullptr;
     Go2Model& m = h->model;
     if (!unpack_model(m, model_iv, n_iv, model_fv, n_fv)) { delete h; return -3; }
-    if (c.num_envs <= 0 || c.num_actions > NACT_MAX || c.num_obs > NOBS_MAX || c.hist_size > HIST_MAX || c.n_rew > MAX_REW) { delete h; return -4; }
+    if (c.num_envs <= 0 || c.num_actions > NACT_MAX || c.num_obs - (c.lidar_on ? c.n_actor_scan : 0) > NOBS_MAX || c.n_actor_scan > MAX_ACTOR_SCAN || c.n_critic_scan > MAX_CRITIC_SCAN || c.hist_size > HIST_MAX || c.n_rew > MAX_REW) { delete h; return -4; }
     if (c.replay_rows != 0 && c.replay_rows != c.num_envs) { delete h; return -4; }
     if (cudaSetDevice(device) != cudaSuccess) { delete h; return -5; }
     compute_layout(c, h->dtype, h->rows, h->cols);

@@ -30,7 +30,8 @@ constexpr int NTRI = NV * (NV + 1) / 2;  // packed lower triangle
 constexpr int MAX_REW = 32;      // reward terms
 constexpr int NACT_MAX = 16;
 constexpr int HIST_MAX = 4;      // action-delay ring slots (max_delay_steps + 1 <= 4)
-constexpr int NOBS_MAX = 49;
+constexpr int NOBS_MAX = 49;     // proprioceptive obs entries (the lidar variant appends up to MAX_ACTOR_SCAN heights after them)
+constexpr int MAX_ACTOR_SCAN = 32, MAX_CRITIC_SCAN = 96;  // simulated-lidar height grids (go2_env_stair_lidar.py LidarScanConfig)
 constexpr int SCAN_MAX = 77;
 constexpr int MAX_TERRAIN_ROWS = 16;  // difficulty rows of the stair terrain (go2_env_stair.py:61)
 constexpr int TERRAIN_MIP_SHIFT = 2;      // 4 x 4 cells per block of the max-height level
@@ -139,6 +140,11 @@ struct EnvConfig {
     int solver_dense;         // 1 = every env uses the dense 18x18 Newton path (diagnostic; default 0 = arrow unless legs touch)
     int export_rew_terms;     // 1 = B_REW_TERMS receives every scaled reward term of the tick
     int replay_rows;          // rows of B_REPLAY (0 = no replay buffer; num_envs = draws can be replayed, see StepParams.replay_on)
+    // simulated lidar of examples/locomotion/go2_env_stair_lidar.py: body-frame sample points of the actor scan (appended to the obs,
+    // with the sim-to-real noise model) and of the clean critic scan (tail of the privileged obs instead of the height scan)
+    int lidar_on, n_actor_scan, n_critic_scan;
+    float actor_lx[MAX_ACTOR_SCAN], actor_ly[MAX_ACTOR_SCAN], critic_lx[MAX_CRITIC_SCAN], critic_ly[MAX_CRITIC_SCAN];
+    float lidar_noise_std, lidar_dropout, lidar_blackout, lidar_latency, lidar_voffset_std, lidar_clip, lidar_scale;
 };
 
 // Per-step parameters: everything the reference keeps as host-side python scalars (curriculum-driven
@@ -162,6 +168,7 @@ struct StepParams {
     int force_reset_all;
     int terrain_max_row;       // stair: int(curriculum_level * (rows - 1))
     int lock_terrain_rows;     // stair eval: keep each env's row across resets
+    float lidar_noise_level;   // lidar variant: the DR level scaling the scan noise model (_lidar_noise_level)
     int n_resets_hint;         // stair: number of envs (all ranks) this launch resets when the host knows it (reset of all envs), else 0
     // candidates of the global physics DR (already lerped with this tick's t_sample); the post-pass kernel puts them in
     // force if an env reset in this tick - B_GLOBALS holds the values in force
@@ -184,6 +191,7 @@ constexpr int G_FRIC_GROUND = 0, G_FRIC_ROBOT = 1, G_MASS_SHIFT = 2, G_COM_SHIFT
 // B_REPLAY row layout (one row per env): the values the reference drew in the replayed tick
 constexpr int RP_ACT_NOISE = 0, RP_OBS_NOISE = 12, RP_PUSH = 61 /* fx fy duration */, RP_CMD = 64, RP_KPF = 67, RP_KDF = 79, RP_MS = 91,
               RP_GO = 103, RP_DELAY = 106, RP_INIT_Z = 107, RP_ROLL = 108, RP_PITCH = 109, RP_CMD_RESET = 110, RP_ROW = 113, RP_KP = 114,
-              RP_KD = 115, REPLAY_LEN = 116;
+              RP_KD = 115, RP_LIDAR_N = 116 /* per-cell normals */, RP_LIDAR_U = 116 + MAX_ACTOR_SCAN /* per-cell uniforms */,
+              RP_LIDAR_V = 116 + 2 * MAX_ACTOR_SCAN /* offset normal, latency u, blackout u */, REPLAY_LEN = RP_LIDAR_V + 3;
 
 }  // namespace go2

@@ -14,6 +14,7 @@ import numpy as np
 NLINK, NV, NQ, NHINGE = 13, 18, 19, 12
 MAX_REW, NOBS_MAX, MAX_CPAIRS = 32, 49, 24
 MAX_TERRAIN_ROWS = 16
+MAX_ACTOR_SCAN, MAX_CRITIC_SCAN = 32, 96
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CUDA_LIB_PATH = os.path.join(_HERE, "libgo2_b200.so")
@@ -42,14 +43,16 @@ BUF_NAMES = [
     "base_euler", "kp_factors", "kd_factors", "motor_strength", "eff_kp", "eff_kd", "grav_off", "push_force", "cur_push",
     "push_remain", "delay", "foot_contact", "last_foot_contact", "air_time", "ep_sums", "errno", "link_pos", "link_vel",
     "contact_force", "torque", "stats", "ncontact", "nnewton", "terrain_row", "last_x",
-    "globals", "rew_terms", "replay", "fk_fresh", "ext_force",
+    "globals", "rew_terms", "replay", "fk_fresh", "ext_force", "actor_scan",
 ]
 BUF = {n: i for i, n in enumerate(BUF_NAMES)}
 STATS_RESETS, STATS_TIMEOUTS, STATS_TRACKING, STATS_ERR, STATS_REW0 = 0, 1, 2, 3, 4
 # B_GLOBALS slot layout / B_REPLAY row layout (csrc/go2_types.cuh)
 G_FRIC_GROUND, G_FRIC_ROBOT, G_MASS_SHIFT, G_COM_SHIFT, G_DR_COUNTER, GLOBALS_LEN = 0, 1, 2, 15, 18, 20
 RP_ACT_NOISE, RP_OBS_NOISE, RP_PUSH, RP_CMD, RP_KPF, RP_KDF, RP_MS, RP_GO, RP_DELAY = 0, 12, 61, 64, 67, 79, 91, 103, 106
-RP_INIT_Z, RP_ROLL, RP_PITCH, RP_CMD_RESET, RP_ROW, RP_KP, RP_KD, REPLAY_LEN = 107, 108, 109, 110, 113, 114, 115, 116
+RP_INIT_Z, RP_ROLL, RP_PITCH, RP_CMD_RESET, RP_ROW, RP_KP, RP_KD = 107, 108, 109, 110, 113, 114, 115
+RP_LIDAR_N, RP_LIDAR_U, RP_LIDAR_V = 116, 116 + MAX_ACTOR_SCAN, 116 + 2 * MAX_ACTOR_SCAN  # lidar variant: cell normals, cell uniforms, (offset, latency, blackout)
+REPLAY_LEN = RP_LIDAR_V + 3
 
 _i, _f, _u = C.c_int32, C.c_float, C.c_uint32
 
@@ -79,6 +82,10 @@ class EnvConfig(C.Structure):
         ("lin_vel_z_deadzone", _f),
         ("has_friction_dr", _i), ("has_mass_dr", _i), ("has_com_dr", _i), ("has_leg_mass_dr", _i), ("global_dr_interval", _i),
         ("hip_link", _i * 4), ("solver_dense", _i), ("export_rew_terms", _i),  ("replay_rows", _i),
+        ("lidar_on", _i), ("n_actor_scan", _i), ("n_critic_scan", _i),
+        ("actor_lx", _f * MAX_ACTOR_SCAN), ("actor_ly", _f * MAX_ACTOR_SCAN), ("critic_lx", _f * MAX_CRITIC_SCAN), ("critic_ly", _f * MAX_CRITIC_SCAN),
+        ("lidar_noise_std", _f), ("lidar_dropout", _f), ("lidar_blackout", _f), ("lidar_latency", _f), ("lidar_voffset_std", _f),
+        ("lidar_clip", _f), ("lidar_scale", _f),
     ]
 
 
@@ -91,7 +98,7 @@ class StepParams(C.Structure):
         ("kp_lo", _f), ("kp_hi", _f), ("kd_lo", _f), ("kd_hi", _f),
         ("delay_lo", _i), ("delay_hi", _i),
         ("kp_genesis", _f), ("kd_genesis", _f),
-        ("do_physics", _i), ("force_reset_all", _i), ("terrain_max_row", _i), ("lock_terrain_rows", _i), ("n_resets_hint", _i),
+        ("do_physics", _i), ("force_reset_all", _i), ("terrain_max_row", _i), ("lock_terrain_rows", _i), ("lidar_noise_level", _f), ("n_resets_hint", _i),
         ("cand_friction", _f), ("cand_mass", _f), ("cand_com", _f * 3), ("cand_leg", _f * 4),
         ("parity", _i), ("defer_post", _i), ("replay_on", _i), ("ext_on", _i),
         ("host_obs", C.c_void_p), ("host_rew", C.c_void_p), ("host_done", C.c_void_p),

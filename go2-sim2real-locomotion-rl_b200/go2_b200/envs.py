@@ -357,7 +357,8 @@ class _Go2EnvBase:
         """Fixture replay: the NEXT step reads every random draw from `rows` ([B, REPLAY_LEN], layout abi.RP_*) instead of Philox."""
         if not self._opt_replay:
             raise RuntimeError("construct the env with replay=True")
-        self.core.buf["replay"].copy_(torch.as_tensor(rows, device=self.device, dtype=torch.float32))
+        rows = torch.as_tensor(rows, device=self.device, dtype=torch.float32)
+        self.core.buf["replay"][:, :rows.shape[1]].copy_(rows)  # (fixtures recorded before a layout extension are narrower)
         self._replay_next = True
 
     # ---- global physics DR in force (device-resident, both double-buffer slots)
@@ -612,7 +613,7 @@ class Go2EnvWalk(_Go2EnvBase):
         sp.action_noise_std = float(self._action_noise_std_cur)
         if self.obs_noise_vec is not None:
             sp.obs_noise_on = 1
-            for i in range(self.num_obs):
+            for i in range(min(self.num_obs, abi.NOBS_MAX)):  # (a lidar scan appended to the obs carries its own noise model)
                 sp.obs_noise[i] = float(self.obs_noise_vec[i])
         for i, k in enumerate(("lin_vel_x", "lin_vel_y", "ang_vel")):
             sp.cmd_lo[i], sp.cmd_hi[i] = float(self._cmd_cur_ranges[k][0]), float(self._cmd_cur_ranges[k][1])
@@ -785,6 +786,89 @@ class Go2EnvStair(Go2EnvWalk):
         col = ((x - ox) / self._h_scale).long().clamp(0, self._hf_heights.shape[0] - 1)
         row = ((y - oy) / self._h_scale).long().clamp(0, self._hf_heights.shape[1] - 1)
         return self._hf_heights[col, row]
+
+
+class LidarScanConfig:
+    """Body-frame sample points and noise parameters of the simulated lidar (go2_env_stair_lidar.py:298-383, same cfg keys and
+    attribute names): `actor_scan` = explicit `x_points` / `y_points` or `num_x` / `num_y` / `x_range` / `y_range` (default 5 x 3,
+    forward-biased), `critic_scan` = dense surround grid (default 9 x 5), `noise`, `height_clip`, `height_scale`."""
+
+    def __init__(self, cfg: dict, device=None):
+        self.device = device
+        self.enabled = bool(cfg.get("enabled", True))
+        self.num_actor_scan = self.num_critic_scan = 0
+        if not self.enabled:
+            return
+        a = cfg.get("actor_scan", {})
+        if "x_points" in a:
+            ax, ay = np.asarray(a["x_points"], np.float32), np.asarray(a["y_points"], np.float32)
+        else:
+            xr, yr = a.get("x_range", [0.0, 0.8]), a.get("y_range", [-0.15, 0.15])
+            ax = torch.linspace(float(xr[0]), float(xr[1]), int(a.get("num_x", 5))).numpy()
+            ay = torch.linspace(float(yr[0]), float(yr[1]), int(a.get("num_y", 3))).numpy()
+        self._actor_nx, self._actor_ny = len(ax), len(ay)
+        gx, gy = np.meshgrid(ax, ay, indexing="ij")
+        self.actor_local_x, self.actor_local_y = gx.reshape(-1).astype(np.float32), gy.reshape(-1).astype(np.float32)
+        self.num_actor_scan = self._actor_nx * self._actor_ny
+        c = cfg.get("critic_scan", {})
+        self._critic_nx, self._critic_ny = int(c.get("num_x", 9)), int(c.get("num_y", 5))
+        xr, yr = c.get("x_range", [-0.4, 0.8]), c.get("y_range", [-0.3, 0.3])
+        cx = torch.linspace(float(xr[0]), float(xr[1]), self._critic_nx).numpy()  # torch.linspace like the reference (f32 rounding)
+        cy = torch.linspace(float(yr[0]), float(yr[1]), self._critic_ny).numpy()
+        gx, gy = np.meshgrid(cx, cy, indexing="ij")
+        self.critic_local_x, self.critic_local_y = gx.reshape(-1).astype(np.float32), gy.reshape(-1).astype(np.float32)
+        self.num_critic_scan = self._critic_nx * self._critic_ny
+        n = cfg.get("noise", {})
+        self.height_noise_std = float(n.get("height_noise_std", 0.02))
+        self.dropout_prob = float(n.get("dropout_prob", 0.15))
+        self.full_blackout_prob = float(n.get("full_blackout_prob", 0.05))
+        self.latency_prob = float(n.get("latency_prob", 0.1))
+        self.vertical_offset_std = float(n.get("vertical_offset_std", 0.01))
+        self.height_clip = float(cfg.get("height_clip", 1.0))
+        self.height_scale = float(cfg.get("height_scale", 1.0))
+
+
+class Go2EnvStairLidar(Go2EnvStair):
+    """Stair env with the simulated lidar of examples/locomotion/go2_env_stair_lidar.py: a sparse forward-biased height
+    grid with a sim-to-real noise model appended to the ACTOR obs (49 + 15 = 64), a clean dense grid at the tail of the critic's
+    privileged obs instead of the 11 x 7 height scan.  The "lidar" is a heightfield lookup in the reference too (no ray casting):
+    `_compute_lidar_scan` :895-937, `_update_actor_lidar_scan` :939-1002, `_update_critic_lidar_scan` :1004-1015."""
+
+    def _fill_flavour(self, c):
+        super()._fill_flavour(c)
+        self._lidar = L = LidarScanConfig(self.env_cfg.get("lidar", {}), self.device)
+        self._lidar_noise_level = 0.0
+        if not L.enabled:
+            return
+        if L.num_actor_scan > abi.MAX_ACTOR_SCAN or L.num_critic_scan > abi.MAX_CRITIC_SCAN:
+            raise ValueError(f"lidar grids of at most {abi.MAX_ACTOR_SCAN} actor / {abi.MAX_CRITIC_SCAN} critic points are supported")
+        if self.num_obs != 33 + self.num_actions + L.num_actor_scan:
+            raise ValueError(f"obs_cfg['num_obs'] = {self.num_obs} != 33 + {self.num_actions} actions + {L.num_actor_scan} lidar points")
+        c.lidar_on, c.n_actor_scan, c.n_critic_scan = 1, L.num_actor_scan, L.num_critic_scan
+        for i in range(L.num_actor_scan):
+            c.actor_lx[i], c.actor_ly[i] = float(L.actor_local_x[i]), float(L.actor_local_y[i])
+        for i in range(L.num_critic_scan):
+            c.critic_lx[i], c.critic_ly[i] = float(L.critic_local_x[i]), float(L.critic_local_y[i])
+        c.lidar_noise_std, c.lidar_dropout, c.lidar_blackout = L.height_noise_std, L.dropout_prob, L.full_blackout_prob
+        c.lidar_latency, c.lidar_voffset_std, c.lidar_clip, c.lidar_scale = L.latency_prob, L.vertical_offset_std, L.height_clip, L.height_scale
+
+    def _after_bind(self):
+        super()._after_bind()
+        self._actor_scan_buf = self.core.buf["actor_scan"]  # [B, num_actor_scan]; the previous scan until the next tick overwrites it
+
+    @property
+    def _critic_scan_buf(self):
+        k = self.num_obs + 56
+        return self.privileged_obs_buf[:, k:k + self._lidar.num_critic_scan]
+
+    def _curriculum_extras(self, cur, lvl, dr_lvl):
+        super()._curriculum_extras(cur, lvl, dr_lvl)
+        self._lidar_noise_level = float(dr_lvl)  # go2_env_stair_lidar.py:1220
+        cur["lidar_noise_level"] = float(dr_lvl)
+
+    def _flavour_params(self, sp):
+        super()._flavour_params(sp)
+        sp.lidar_noise_level = float(self._lidar_noise_level)
 
 
 class Go2EnvBaseFlavour(_Go2EnvBase):

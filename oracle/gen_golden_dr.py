@@ -37,15 +37,30 @@ class DrawLog:
         self.m = module
         self.calls = []
         self._of, self._oi, self._orn = module.gs_rand_float, getattr(module, "gs_rand_int", None), torch.randn_like
+        self._orl, self._or, self._ornn = torch.rand_like, torch.rand, torch.randn
         module.gs_rand_float = self._wrap(self._of, "f")
         if hasattr(module, "gs_rand_int"):
             module.gs_rand_int = self._wrap(self._oi, "i")
         torch.randn_like = self._wrap_randn
+        # the lidar variant's noise model draws with torch.rand_like / torch.rand / torch.randn (go2_env_stair_lidar.py:973-997);
+        # only calls made from its _update_actor_lidar_scan are logged (gs_rand_float itself calls torch.rand)
+        torch.rand_like = self._wrap_t(self._orl, "ul")
+        torch.rand = self._wrap_t(self._or, "u")
+        torch.randn = self._wrap_t(self._ornn, "nn")
 
     def _wrap(self, fn, kind):
         def w(*a, **k):
             r = fn(*a, **k)
             self.calls.append((sys._getframe(1).f_code.co_name, kind, r.clone()))
+            return r
+
+        return w
+
+    def _wrap_t(self, fn, kind):
+        def w(*a, **k):
+            r = fn(*a, **k)
+            if sys._getframe(1).f_code.co_name == "_update_actor_lidar_scan":
+                self.calls.append(("_update_actor_lidar_scan", kind, r.clone()))
             return r
 
         return w
@@ -57,6 +72,7 @@ class DrawLog:
 
     def restore(self):
         self.m.gs_rand_float, torch.randn_like = self._of, self._orn
+        torch.rand_like, torch.rand, torch.randn = self._orl, self._or, self._ornn
         if hasattr(self.m, "gs_rand_int"):
             self.m.gs_rand_int = self._oi
 
@@ -87,7 +103,7 @@ def pre_state(env, kind):
     # dof_pos / dof_vel (from qpos / qvel), episode sums (running float32 sums of o_rew_terms)
     s = dict(qpos=r.get_qpos(), qvel=r.get_qvel(), qacc_ws=qws, warm=warm, cache_pair=ids, cache_n=nrm,
              commands=env.commands.numpy().copy(), ep_len=env.episode_length_buf.numpy().copy())
-    if kind in ("walk", "stair"):
+    if kind in ("walk", "stair", "stair_lidar"):
         s.update(hist_idx=np.array(env._action_history_write_idx), delay=env._delay_steps.numpy().copy(),
                  air_time=env._feet_air_time.numpy().copy(), foot_contact=env._foot_contact.numpy().copy(),
                  kp_factors=env._kp_factors.numpy().copy(), kd_factors=env._kd_factors.numpy().copy(), motor_strength=env._motor_strength.numpy().copy(),
@@ -97,8 +113,10 @@ def pre_state(env, kind):
                  g_counter=np.array(int(env._global_dr_reset_counter)))
         if env.push_force_range_hard is not None:
             s.update(push_force=env._push_stored_force.numpy().copy(), push_remain=env._push_remaining.numpy().copy(), push_counter=np.array(env._push_counter))
-    if kind == "stair":
+    if kind in ("stair", "stair_lidar"):
         s.update(terrain_row=env._env_terrain_row.numpy().astype(np.int32), last_x=env._last_base_pos_x.numpy().copy())
+    if kind == "stair_lidar":
+        s.update(actor_scan=env._actor_scan_buf.numpy().copy(), lidar_noise_level=np.array(float(env._lidar_noise_level)))
     return s
 
 
@@ -125,6 +143,15 @@ def draws_of_tick(env, kind, calls, done, ep_len_pre, A):
     for _, r in by.pop("step", []):  # action noise (go2_env_walk.py:1001-1003)
         assert r.shape == (B, 12)
         row[:, abi.RP_ACT_NOISE:abi.RP_ACT_NOISE + 12] = r
+    lid = by.pop("_update_actor_lidar_scan", [])
+    if lid:  # order of go2_env_stair_lidar.py:973-997: cell normals, cell uniforms, offset normal, latency uniform, blackout uniform
+        assert [k for k, _ in lid] == ["n", "ul", "nn", "u", "u"], [k for k, _ in lid]
+        n_sc = lid[0][1].shape[1]
+        row[:, abi.RP_LIDAR_N:abi.RP_LIDAR_N + n_sc] = lid[0][1]
+        row[:, abi.RP_LIDAR_U:abi.RP_LIDAR_U + n_sc] = lid[1][1]
+        row[:, abi.RP_LIDAR_V] = lid[2][1][:, 0]
+        row[:, abi.RP_LIDAR_V + 1] = lid[3][1]
+        row[:, abi.RP_LIDAR_V + 2] = lid[4][1]
     for _, r in by.pop("_add_obs_noise", []):
         assert r.shape == (B, env.num_obs)
         # entries with zero noise std never reach the obs; dropping their draws keeps the fixture small
@@ -177,7 +204,7 @@ def draws_of_tick(env, kind, calls, done, ep_len_pre, A):
         if "init_euler_range" in env.env_cfg:
             row[ridx, abi.RP_ROLL] = rr[i][1]; row[ridx, abi.RP_PITCH] = rr[i + 1][1]; i += 2
         assert i == len(rr)
-        if kind == "stair":
+        if kind in ("stair", "stair_lidar"):
             by.pop("_assign_terrain_rows", None)
             row[ridx, abi.RP_ROW] = env._env_terrain_row.numpy()[ridx]
         for k in ("_randomize_friction", "_randomize_mass", "_randomize_leg_mass"):
@@ -192,7 +219,7 @@ def outputs(env, obs, rew, done, extras, kind, terms):
     # the state after the tick (qpos, qvel, commands, ep_len, DR buffers ...) is the NEXT tick's pre-state (`final_*` after the last)
     o = dict(o_obs=obs.numpy().copy(), o_rew=rew.numpy().copy(), o_reset=done.numpy().astype(np.uint8), o_timeout=extras["time_outs"].numpy().copy(),
              o_ncon=r.get_solver_stats()[:, 0].copy(), o_rew_terms=terms)
-    if kind in ("walk", "stair"):
+    if kind in ("walk", "stair", "stair_lidar"):
         pr = extras["observations"]["critic"].numpy()
         assert np.array_equal(pr[:, :env.num_obs], o["o_obs"])
         o.update(o_priv_tail=pr[:, env.num_obs:].copy(), o_foot_contact=env._foot_contact.numpy().copy())
@@ -320,6 +347,15 @@ def stair_cfgs():
     return env_cfg, obs_cfg, reward_cfg, command_cfg
 
 
+def stair_lidar_cfgs():
+    """examples/locomotion/go2_stair_train_lidar.get_cfgs() (actor obs 49 + 15 lidar heights, critic scan 9 x 5) at a curriculum level
+    where the two-phase DR schedule gives a non-zero lidar noise level, with the fixture horizon of stair_c1."""
+    env_cfg, obs_cfg, reward_cfg, command_cfg = load_funcs(os.path.join(REF, "examples/locomotion/go2_stair_train_lidar.py"), ["get_cfgs"]).get_cfgs()
+    env_cfg.update(episode_length_s=3.0, resampling_time_s=1.0)
+    env_cfg["curriculum"]["level_init"] = 0.95  # past the DR gate: every branch of the lidar noise model fires
+    return env_cfg, obs_cfg, reward_cfg, command_cfg
+
+
 def base_allrew_cfgs():
     """go2_train_crouch.get_cfgs() with EVERY reward term of go2_env_base.py switched on (the shipped scripts use 6-10 of the 20;
     logs/go2-crouch/cfgs.pkl names crouch_2 / y_stability / crouch_speed but lacks the termination keys the final env class
@@ -348,7 +384,11 @@ def main():
     import go2_env_stair
     import go2_env_walk
 
+    sys.path.insert(0, os.path.join(REF, "examples/locomotion"))
+    import go2_env_stair_lidar
+
     jobs = {
+        "stair_lidar_c1": lambda: (go2_env_stair_lidar.Go2Env, go2_env_stair_lidar, stair_lidar_cfgs(), "stair_lidar", 16, 300, 0.5, 909, 16),
         "walk_c1": lambda: (go2_env_walk.Go2Env, go2_env_walk, walk_cfgs(), "walk", 32, 1000, 0.5, 1234, 16),
         "walk_hard": lambda: (go2_env_walk.Go2Env, go2_env_walk, walk_hard_cfgs(), "walk", 16, 300, 0.6, 4242, 16),
         "stair_c1": lambda: (go2_env_stair.Go2Env, go2_env_stair, stair_cfgs(), "stair", 16, 400, 0.5, 777, 16),

@@ -93,7 +93,8 @@ def test_walk_module_as_the_train_script_uses_it(backend, dropin):
 
 
 @pytest.mark.parametrize("backend", BACKENDS)
-@pytest.mark.parametrize("module,cfg,n_obs,n_act,n_priv", [("go2_env_stair", "stair", 49, 16, 182), ("go2_env_base", "crouch", 45, 12, None),
+@pytest.mark.parametrize("module,cfg,n_obs,n_act,n_priv", [("go2_env_stair", "stair", 49, 16, 182), ("go2_env_stair4_lidar", "stair_lidar", 64, 16, 165),
+                                                           ("go2_env_stair_lidar", "stair_lidar", 64, 16, 165), ("go2_env_base", "crouch", 45, 12, None),
                                                            ("go2_env_base", "jump", 45, 12, None)])
 def test_stair_and_base_modules(backend, dropin, module, cfg, n_obs, n_act, n_priv):
     gs = dropin
