@@ -172,3 +172,63 @@ def test_invweight_and_meaninertia_recomputed_independently():
     for l in range(1, 14):
         w = np.diag(J[l] @ Minv @ J[l].T).mean()
         assert w == pytest.approx(MODEL["links_invweight"][l][0], rel=5e-3), (l, w, MODEL["links_invweight"][l])
+
+
+def _geom_vertices(g):
+    """Local vertices of a box (full sizes) or of the 32-gon prism the reference meshes a cylinder into (radius, height)."""
+    if g["type"] == 5:
+        sx, sy, sz = (0.5 * v for v in g["data"])
+        return np.array([[a * sx, b * sy, c * sz] for a in (-1, 1) for b in (-1, 1) for c in (-1, 1)])
+    r, h = g["data"][0], g["data"][1]
+    a = np.arange(32) / 32 * 2 * np.pi
+    ring = np.stack([r * np.cos(a), r * np.sin(a)], 1)
+    return np.concatenate([np.c_[ring, np.full(32, -h / 2)], np.c_[ring, np.full(32, h / 2)]])
+
+
+def test_mpr_box_and_cylinder_vs_ground_match_the_deepest_point_answer():
+    """The pairs on which the reference's GJK/EPA fallback can fire with a non-sphere geom (base env: calf / thigh cylinders and
+    calf boxes on the ground in a crouch; counted by orc_get_gjk_stats).  For a convex body against the ground's top face both
+    MPR and EPA must return the minimum-translation answer: normal = +z, depth = how far the body's lowest vertex is under z = 0,
+    witness midway.  The oracle's MPR (first detection of the pair) is checked against exactly that."""
+    B = 16
+    o = OracleRigid(B, kind="f32")
+    geoms = MODEL["geoms"]
+    n = 0
+    worst_pen = worst_n = 0.0
+    rng = np.random.default_rng(5)
+    for t in range(24):
+        # robots lying low in random attitudes with random leg poses: base box, hip / thigh / calf cylinders and calf boxes on the ground
+        qpos = np.zeros((B, 19))
+        qpos[:, 0:2] = rng.uniform(-1, 1, (B, 2))
+        qpos[:, 2] = rng.uniform(0.05, 0.16, B)
+        rpy = rng.uniform(-1.2, 1.2, (B, 3)) * np.array([1.0, 0.6, 1.0])
+        cr, sr, cp, sp, cy, sy = (f(rpy[:, i] / 2) for i in range(3) for f in (np.cos, np.sin))
+        qpos[:, 3:7] = np.stack([cr * cp * cy + sr * sp * sy, sr * cp * cy - cr * sp * sy, cr * sp * cy + sr * cp * sy, cr * cp * sy - sr * sp * cy], 1)
+        qpos[:, 7:19] = rng.uniform(-0.8, 0.8, (B, 12)) + np.tile([0, 0, 0, 0, 1.0, 1.0, 1.0, 1.0, -1.8, -1.8, -1.8, -1.8], (B, 1))
+        o.set_qpos(qpos)
+        o.set_qvel(np.zeros((B, 18)))
+        lp, lq = o.get_links_pos(), o.get_links_quat()  # poses the detection of the next substep runs on
+        o.step(1)
+        for e in range(B):
+            gg, d = o.get_contacts(e)
+            seen = set()
+            for (ga, gb), c in zip(gg, d):
+                a = ga if gb == 0 else (gb if ga == 0 else None)
+                if a is None or geoms[a]["type"] == 1 or a in seen:
+                    continue
+                seen.add(a)  # first contact of the pair = the unperturbed detection
+                G = geoms[a]
+                V = _geom_vertices(G)
+                local = np.array([_quat_rot(G["quat"], v) for v in V]) + np.array(G["pos"])
+                world = np.array([_quat_rot(lq[e, G["link"]], v) for v in local]) + lp[e, G["link"]]  # link 0 = the ground
+                depth = -world[:, 2].min()
+                pos, nrm, pen = c[0:3], c[3:6], c[6]
+                assert depth > 0
+                worst_pen, worst_n = max(worst_pen, abs(pen - depth)), max(worst_n, 1.0 - abs(nrm[2]))
+                if depth > 0.03:
+                    continue  # deep overlaps are not what a running env sees (MPR's portal may settle on another face)
+                assert abs(pen - depth) < 2e-5, (t, e, a, pen, depth)
+                assert 1.0 - abs(nrm[2]) < 1e-5 and abs(pos[2] + depth / 2) < 2e-5, (t, e, a, nrm, pos, depth)
+                n += 1
+    assert n > 50
+    print(f"\n{n} box / cylinder vs ground MPR contacts equal the deepest-point answer (max |d pen| = {worst_pen:.2e}, max 1 - |n.z| = {worst_n:.2e})")
