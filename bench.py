@@ -5,7 +5,9 @@
 A "step" = one `Go2Env.step(actions)` over all B envs of a rank (2 physics substeps + all env logic).
 Headline workload (BASELINE.json configs[4], the one the north-star target is quoted on): Go2 walk, full
 domain-randomisation cfg of go2_train_walk.get_cfgs(), 65,536 envs per GPU, random actions resident on the device.
-  value     device-resident throughput through the public env API (`env.step`), CUDA events, max over ranks
+  value     device-resident throughput through the public env API (`env.step`), CUDA events, max over ranks; measured on a
+            steady-state env population (episode lengths randomised like rsl-rl does, `--settle` untimed ticks after reset()) -
+            `fresh_after_reset` is the same window right after reset(), the cheaper protocol earlier rounds quoted
   e2e       the same tick through the C-ABI host-buffer call go2_step_host (pinned actions H2D, obs / rew / done D2H inside
             the timed region)
   roofline  go2_step_kernel alone (events bracketing its launch inside the timed loop), algorithmic bytes vs measured HBM peak
@@ -214,7 +216,19 @@ def bench_env(args, workload, B, rank, world, dev, headline):
         barrier()
         return a.elapsed_time(b)
 
-    # ---- device-resident throughput through the env API; events around the step kernel of every tick (same stream)
+    # ---- population like a running training job, not like the tick after reset(): episode lengths randomised the way rsl-rl's
+    # OnPolicyRunner.learn(init_at_random_ep_len=True) does (go2_train_walk.py:476) - otherwise all envs time out in the same tick and
+    # no reset ever falls into the window - and `--settle` untimed ticks (default 240 = BASELINE C5's 10 warm-up rollouts of 24) so
+    # that the poses have left the all-standing start (step time rises ~6 % over the first 300 ticks, profiles/tools/tick_time_drift.py)
+    if headline and args.settle > 0:  # the window right after reset() that rounds 1 / early 2 quoted, kept for continuity
+        for i in range(W):
+            env.step(acts[i % n_act])
+        ms_fresh = timed(lambda i: env.step(acts[i % n_act]))
+    else:
+        ms_fresh = None
+    env.episode_length_buf = torch.randint(0, int(env.max_episode_length), (B,), device=dev, generator=g, dtype=torch.int32)
+    for i in range(args.settle):
+        env.step(acts[i % n_act])
     for i in range(W):
         env.step(acts[i % n_act])
     kev = []
@@ -234,7 +248,7 @@ def bench_env(args, workload, B, rank, world, dev, headline):
     clocks = sampler.stop() if (rank == 0 and headline) else None
     kern_ms = sorted(a.elapsed_time(b) for a, b in kev) or [ms_total / K]
     kern_avg = sum(kern_ms) / len(kern_ms)
-    res = {"env": env, "ms_total": ms_total, "kern_avg": kern_avg, "kern_med": kern_ms[len(kern_ms) // 2], "launches": launches, "clocks": clocks,
+    res = {"env": env, "ms_fresh": ms_fresh, "ms_total": ms_total, "kern_avg": kern_avg, "kern_med": kern_ms[len(kern_ms) // 2], "launches": launches, "clocks": clocks,
            "shape": env.core.launch_shape()}
 
     # ---- end to end through the C ABI with pinned host buffers
@@ -306,7 +320,8 @@ def emit(args, workload, B, world, res, headline, cpu):
     out = {
         "metric": METRIC if workload == "walk" else METRIC.replace("walk", workload), "value": value, "unit": UNIT, "n_gpus": world, "steps": K,
         "warmup": max(3, args.warmup), "ms_per_step": res["ms_total"] / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic", "config": dict(workload_config(workload, B), stats_sync_interval=env.stats_sync_interval),
+        "dtype": "f32", "data": "synthetic", "config": dict(workload_config(workload, B), stats_sync_interval=env.stats_sync_interval, settle_ticks=args.settle,
+                                                       population="episode lengths randomised (rsl-rl init_at_random_ep_len), settle_ticks untimed ticks before the warm-up: steady-state poses and a steady stream of time-out resets"),
         "e2e": {"value": world * B * K / (res["ms_e2e"] * 1e-3), "unit": UNIT, "h2d_bytes_per_step": B * env.num_actions * 4,
                 "d2h_bytes_per_step": B * (env.num_obs * 4 + 4 + 1), "ms_per_step": res["ms_e2e"] / K,
                 "what": "go2_step_host: pinned actions H2D, step + post kernels, rew / done / obs D2H, stream sync - every tick"},
@@ -324,6 +339,9 @@ def emit(args, workload, B, world, res, headline, cpu):
                  "errno_envs": int((b["errno"] != 0).sum()),
                  "note": "throughput depends on the action distribution: 0.5*randn actions here; a policy's smaller outputs give fewer contacts / Newton iterations (with_policy_fused)"},
     }
+    if res.get("ms_fresh"):
+        out["fresh_after_reset"] = {"value": world * B * K / (res["ms_fresh"] * 1e-3), "unit": UNIT, "ms_per_step": res["ms_fresh"] / K,
+                                    "what": "the same K ticks timed right after reset() + W warm-up ticks (the protocol of BENCH_r01): every env still near the standing start pose, no resets in the window - cheaper than a running job, reported for continuity only"}
     if "ms_pol" in res:
         out["with_policy"] = {"value": world * B * K / (res["ms_pol"] * 1e-3), "unit": UNIT, "ms_per_step": res["ms_pol"] / K,
                               "policy": f"{env.num_obs}-512-256-128-{env.num_actions} ELU actor, fixed-seed random init (shipped model_188000.pt blob absent), torch fp32, inside the timed loop"}
@@ -377,6 +395,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=48)
     ap.add_argument("--warmup", type=int, default=12)
+    ap.add_argument("--settle", type=int, default=240, help="untimed ticks after reset() before the warm-up (steady-state population); 0 = time right after reset()")
     ap.add_argument("--envs", type=int, default=0, help="envs per GPU (default: 65,536 walk, 8,192 stair, 4,096 crouch / jump)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
