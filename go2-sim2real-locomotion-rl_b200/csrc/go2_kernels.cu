@@ -56,7 +56,7 @@ __device__ __forceinline__ void accumulate_stats(const EnvConfig* gcfg, const St
         atomicAdd(&st[STATS_TRACKING], out.tracking_per_sec);
         for (int k = 0; k < gcfg->n_rew; ++k) atomicAdd(&st[STATS_REW0 + k], out.ep_stat[k]);
     }
-    if (err) atomicAdd(&st[STATS_ERR], 1.0f);  // number of envs that raised an errno bit this tick
+    if (err & ~ERR_GJK_WANTED) atomicAdd(&st[STATS_ERR], 1.0f);  // envs that raised an error bit this tick (bit 16 is a diagnostic, not an error)
 }
 
 // one thread per env

@@ -333,14 +333,14 @@ class _Go2EnvBase:
             return
         self._ticks_since_stats = 0
         if k == 1:
-            self._after_resets(self.core.read_stats())
+            self._consume_stats(self.core.read_stats())
             return
         # asynchronous, double-buffered: enqueue this interval's read, consume the previous interval's (long complete)
         cur, prev = self._stats_slot, self._stats_slot ^ 1
         self.core.read_stats_async(cur)
         self._stats_inflight[cur] = True
         if self._stats_inflight[prev]:
-            self._after_resets(self.core.stats_fetch(prev, block=True))
+            self._consume_stats(self.core.stats_fetch(prev, block=True))
             self._stats_inflight[prev] = False
         self._stats_slot = prev
 
@@ -348,10 +348,19 @@ class _Go2EnvBase:
         """Consume every outstanding statistics read (blocking) - e.g. before reading extras at the end of a rollout."""
         for slot in (self._stats_slot, self._stats_slot ^ 1):
             if self._stats_inflight[slot]:
-                self._after_resets(self.core.stats_fetch(slot, block=True))
+                self._consume_stats(self.core.stats_fetch(slot, block=True))
                 self._stats_inflight[slot] = False
-        self._after_resets(self.core.read_stats())
+        self._consume_stats(self.core.read_stats())
         self._ticks_since_stats = 0
+
+    def _consume_stats(self, stats):
+        """One read of the accumulated statistics: the host side of reset_idx, and - like Genesis' check_errno, which polls the
+        solver's errno every 10 substeps (rigid_solver.py:1189-1213) - the error check: the statistics carry the number of env-ticks
+        that raised an error bit, so the per-env errno buffer is only read (a sync) when there is something to report."""
+        self._after_resets(stats)
+        if float(stats[abi.STATS_ERR]) > 0:
+            self.extras["errno_env_ticks"] = int(round(float(stats[abi.STATS_ERR])))
+            self.poll_errno()  # raises on contact / pair overflow; NaN envs were force-reset (bits 4 / 8 are returned, not raised)
 
     def replay_draws(self, rows):
         """Fixture replay: the NEXT step reads every random draw from `rows` ([B, REPLAY_LEN], layout abi.RP_*) instead of Philox."""

@@ -101,7 +101,7 @@ static int run(go2_handle* h, const float* actions, StepParams sp) {
             st[STATS_TRACKING] += out.tracking_per_sec;
             for (int k = 0; k < h->cfg.n_rew; ++k) st[STATS_REW0 + k] += out.ep_stat[k];
         }
-        if (p->err) st[STATS_ERR] += 1.0f;
+        if (p->err & ~ERR_GJK_WANTED) st[STATS_ERR] += 1.0f;
     }
     delete p;
     delete e;

@@ -43,3 +43,23 @@ def test_interval_reads_deliver_the_same_sums_later(hostemu_lib):
     # k = 4 consumed them in fewer, later calls (every 4th tick, one interval behind, rest at flush)
     mid = c4[1:-2]
     assert len(c4) < len(c1) and all(b - a == 4 for a, b in zip(mid, mid[1:]))
+
+
+def test_error_bits_reach_the_host_through_the_statistics(hostemu_lib):
+    """Genesis polls the solver's errno every 10 substeps and raises (rigid_solver.py:1189-1213); here the statistics row counts the
+    env-ticks that raised an error bit and the errno buffer is polled when that count is non-zero."""
+    import pytest
+
+    cfgs = json.load(open(os.path.join(ROOT, "go2-sim2real-locomotion-rl_b200/go2_b200/cfgs/walk.json")))
+    env = make_env("walk", cfgs, 8, "hostemu", hostemu_lib, seed=3)
+    env.reset()
+    env.step(torch.zeros(8, env.num_actions))
+    assert "errno_env_ticks" not in env.extras
+    stats = np.zeros(env.core.L.stats_len, dtype=np.float32)
+    stats[abi.STATS_ERR] = 2
+    env.core.buf["errno"][3] = 8  # NaN acceleration: the env was force-reset, reported but not raised
+    env._consume_stats(stats)
+    assert env.extras["errno_env_ticks"] == 2
+    env.core.buf["errno"][5] = 2  # contact overflow: raises the reference's message
+    with pytest.raises(RuntimeError, match="max number of contact pairs"):
+        env._consume_stats(stats)
