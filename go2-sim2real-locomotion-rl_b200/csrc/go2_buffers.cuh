@@ -68,6 +68,8 @@ enum BufId {
     B_FK_FRESH,      // u8  [B]  1 = the env's kinematics were refreshed (reset / state setter) after the last global mass / COM change
     B_EXT_FORCE,     // f32 [B][4]  external force of the tick: robot-local link (as float), fx, fy, fz (world frame, at the link origin)
     B_ACTOR_SCAN,    // f32 [B][n_actor_scan]  lidar variant: the actor scan in the obs (kept: a stale scan is replayed on "latency")
+    B_SPAWN_POS,     // f32 [B][3]  heightmap walk variant: spawn point of the env (boundary reset, terrain_manager._env_spawn_pos)
+    B_GROUND_H,      // f32 [B]     heightmap walk variant: ground height under the base at the last tick (_ground_height)
     B_COUNT
 };
 

@@ -106,6 +106,7 @@ struct EnvLocal {
     int ep_len;
     float last_x;     // stair: base x at the previous tick
     int terrain_row;  // stair: difficulty row
+    float ground_h;   // heightmap walk variant: ground height under the base (terrain_manager.get_height_at_robot)
 };
 
 // Terrain height under world (x, y) - go2_env_stair.py:758-770 (truncating index, clamped to the field)
@@ -115,6 +116,23 @@ G2_HD float terrain_height(const Go2Model& m, float x, float y) {
     col = col < 0 ? 0 : (col > m.terrain_r - 1 ? m.terrain_r - 1 : col);
     row = row < 0 ? 0 : (row > m.terrain_c - 1 ? m.terrain_c - 1 : row);
     return m.terrain_hf[(size_t)col * m.terrain_c + row];
+}
+
+// Bilinear ground height at world (x, y) - terrain_manager.py:354-392 `_query_height_batch`: numpy arithmetic in float64 on the
+// float32 height field, clipped to the field, result rounded to float32.  The model keeps the field in metres (field x vertical
+// scale, exact for the shipped vertical_scale = 1.0; the reference scales after interpolating).
+G2_HD float ground_height_bilinear(const Go2Model& m, const EnvConfig& cfg, float x, float y) {
+    if (!m.terrain_on) return 0.0f;
+    const int R = m.terrain_r, C = m.terrain_c;
+    double lx = ((double)x - cfg.tm_ox) / cfg.tm_hs, ly = ((double)y - cfg.tm_oy) / cfg.tm_hs;
+    lx = lx < 0.0 ? 0.0 : (lx > (double)(R - 2) ? (double)(R - 2) : lx);
+    ly = ly < 0.0 ? 0.0 : (ly > (double)(C - 2) ? (double)(C - 2) : ly);
+    const int ix = (int)lx, iy = (int)ly;
+    const double fx = lx - ix, fy = ly - iy;
+    const int ix1 = ix + 1 < R - 1 ? ix + 1 : R - 1, iy1 = iy + 1 < C - 1 ? iy + 1 : C - 1;
+    const float* hf = m.terrain_hf;
+    const double h00 = hf[(size_t)ix * C + iy], h10 = hf[(size_t)ix1 * C + iy], h01 = hf[(size_t)ix * C + iy1], h11 = hf[(size_t)ix1 * C + iy1];
+    return (float)(h00 * (1 - fx) * (1 - fy) + h10 * fx * (1 - fy) + h01 * (1 - fx) * fy + h11 * fx * fy);
 }
 
 template <class P>
@@ -136,6 +154,7 @@ G2_HDN float reward_term(int id, const Go2Model& m, const EnvConfig& cfg, const 
         case R_BASE_HEIGHT: {  // stair: height above the local terrain (go2_env_stair.py:1634-1648)
             float h = e.base_pos.z;
             if (cfg.has_terrain) h = h - terrain_height(m, e.base_pos.x, e.base_pos.y);
+            else if (cfg.tm_on) h = h - e.ground_h;  // go2_env_Omni_kplearn_varied_terrain.py: height above the interpolated ground
             float d = h - cfg.base_height_target;
             return d * d;
         }
@@ -313,6 +332,15 @@ G2_HDN void reset_env(const Go2Model& m, const EnvConfig& cfg, const StepParams&
         }
         // reference quirk (go2_env_stair.py:1541-1546): the drawn z is ADDED to the spawn height
         if (cfg.has_init_z) e.base_pos.z = e.base_pos.z + (rp ? rp[RP_INIT_Z] : urange(cfg.init_z_lo, cfg.init_z_hi, rq.a)) - cfg.base_init_pos[2] + cfg.base_init_pos[2];
+    } else if (cfg.tm_on) {
+        // terrain_manager._sample_spawn_heightmap (:285-306): uniform xy inside the safe area, z = interpolated ground height + the base's
+        // standing height + offset (init_pos_z_range is not used on terrain); the spawn point is kept for the boundary check
+        u4 rs = rng4(rng, SLOT_RESET + 13);
+        float ux = rp ? rp[RP_SPAWN] : u01(rs.a), uy = rp ? rp[RP_SPAWN + 1] : u01(rs.b);
+        e.base_pos.x = cfg.tm_safe_half_x > 0.0f ? (ux * 2.0f - 1.0f) * cfg.tm_safe_half_x : 0.0f;
+        e.base_pos.y = cfg.tm_safe_half_y > 0.0f ? (uy * 2.0f - 1.0f) * cfg.tm_safe_half_y : 0.0f;
+        e.base_pos.z = ground_height_bilinear(m, cfg, e.base_pos.x, e.base_pos.y) + cfg.base_init_pos[2] + cfg.tm_spawn_offset;
+        F32(B_SPAWN_POS)[b * 3] = e.base_pos.x; F32(B_SPAWN_POS)[b * 3 + 1] = e.base_pos.y; F32(B_SPAWN_POS)[b * 3 + 2] = e.base_pos.z;
     } else if (cfg.has_init_z) e.base_pos.z = rp ? rp[RP_INIT_Z] : urange(cfg.init_z_lo, cfg.init_z_hi, rq.a);
     if (cfg.has_init_euler) {
         float roll = rp ? rp[RP_ROLL] : urange(cfg.init_euler_lo, cfg.init_euler_hi, rq.b);
@@ -586,6 +614,10 @@ G2_HDN void env_post(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
             }
         }
         if (G2_LIDAR_ON(cfg)) lidar_update(m, cfg, sp, bf, b, rng, rp, e.base_pos, e.base_quat);
+        if (cfg.tm_on) {  // go2_env_Omni_kplearn_varied_terrain.py: _ground_height[:] = terrain.get_height_at_robot(base_pos[:, :2])
+            e.ground_h = ground_height_bilinear(m, cfg, e.base_pos.x, e.base_pos.y);
+            F32(B_GROUND_H)[b] = e.ground_h;
+        }
         if (e.ep_len % cfg.resample_steps == 0) resample_commands(cfg, sp, rng, SLOT_CMD, cfg.env_offset + b, e.cmd, rp ? rp + RP_CMD : nullptr);
     } else {
         for (int i = 0; i < A; ++i) { e.act[i] = 0.0f; e.applied[i] = F32(B_APPLIED)[b * A + i]; }
@@ -606,6 +638,10 @@ G2_HDN void env_post(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
     if (sp.do_physics) {
         rst = rst || fabsf(e.euler.y) > cfg.term_pitch || fabsf(e.euler.x) > cfg.term_roll;
         rst = rst || fabsf(e.lin_vel.z) > cfg.term_zvel || fabsf(e.lin_vel.y) > cfg.term_yvel;
+        if (cfg.tm_on) {  // terrain_manager.check_boundary: wandered further than max_wander from the spawn point
+            float dx = e.base_pos.x - F32(B_SPAWN_POS)[b * 3], dy = e.base_pos.y - F32(B_SPAWN_POS)[b * 3 + 1];
+            rst = rst || sqrtf(dx * dx + dy * dy) > cfg.tm_max_wander;
+        }
     }
     if (sp.force_reset_all) rst = true;
     // an env whose physics went non-finite is force-reset (stricter than the reference, which raises)

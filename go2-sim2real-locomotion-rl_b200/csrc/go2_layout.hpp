@@ -28,6 +28,7 @@ inline void compute_layout(const EnvConfig& c, int* dtype, int* rows, int* cols)
     set(B_TERRAIN_ROW, 1, B, 1); set(B_LAST_X, 0, B, 1);
     set(B_GLOBALS, 0, 2, GLOBALS_LEN); set(B_REW_TERMS, 0, c.export_rew_terms ? B : 1, c.n_rew > 0 ? c.n_rew : 1);
     set(B_REPLAY, 0, c.replay_rows > 0 ? c.replay_rows : 1, REPLAY_LEN); set(B_FK_FRESH, 2, B, 1); set(B_EXT_FORCE, 0, B, 4);
+    set(B_SPAWN_POS, 0, c.tm_on ? B : 1, 3); set(B_GROUND_H, 0, c.tm_on ? B : 1, 1);
     set(B_ACTOR_SCAN, 0, c.lidar_on && c.n_actor_scan > 0 ? B : 1, c.n_actor_scan > 0 ? c.n_actor_scan : 1);
 }
 

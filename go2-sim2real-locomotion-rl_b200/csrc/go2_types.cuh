@@ -145,6 +145,12 @@ struct EnvConfig {
     int lidar_on, n_actor_scan, n_critic_scan;
     float actor_lx[MAX_ACTOR_SCAN], actor_ly[MAX_ACTOR_SCAN], critic_lx[MAX_CRITIC_SCAN], critic_ly[MAX_CRITIC_SCAN];
     float lidar_noise_std, lidar_dropout, lidar_blackout, lidar_latency, lidar_voffset_std, lidar_clip, lidar_scale;
+    // walk env on a custom heightmap (examples/locomotion/go2_env_Omni_kplearn_varied_terrain.py + terrain_manager.py, heightmap mode):
+    // random spawn points, reset when the base wanders too far from its spawn point, base-height reward relative to the bilinearly
+    // interpolated ground height (computed in double like the reference's numpy code: spacing / origin kept in double)
+    int tm_on;
+    float tm_max_wander, tm_safe_half_x, tm_safe_half_y, tm_spawn_offset;
+    double tm_hs, tm_ox, tm_oy;
 };
 
 // Per-step parameters: everything the reference keeps as host-side python scalars (curriculum-driven
@@ -192,6 +198,7 @@ constexpr int G_FRIC_GROUND = 0, G_FRIC_ROBOT = 1, G_MASS_SHIFT = 2, G_COM_SHIFT
 constexpr int RP_ACT_NOISE = 0, RP_OBS_NOISE = 12, RP_PUSH = 61 /* fx fy duration */, RP_CMD = 64, RP_KPF = 67, RP_KDF = 79, RP_MS = 91,
               RP_GO = 103, RP_DELAY = 106, RP_INIT_Z = 107, RP_ROLL = 108, RP_PITCH = 109, RP_CMD_RESET = 110, RP_ROW = 113, RP_KP = 114,
               RP_KD = 115, RP_LIDAR_N = 116 /* per-cell normals */, RP_LIDAR_U = 116 + MAX_ACTOR_SCAN /* per-cell uniforms */,
-              RP_LIDAR_V = 116 + 2 * MAX_ACTOR_SCAN /* offset normal, latency u, blackout u */, REPLAY_LEN = RP_LIDAR_V + 3;
+              RP_LIDAR_V = 116 + 2 * MAX_ACTOR_SCAN /* offset normal, latency u, blackout u */, RP_SPAWN = RP_LIDAR_V + 3 /* spawn x, y uniforms */,
+              REPLAY_LEN = RP_SPAWN + 2;
 
 }  // namespace go2

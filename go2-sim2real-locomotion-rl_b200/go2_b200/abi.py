@@ -43,7 +43,7 @@ BUF_NAMES = [
     "base_euler", "kp_factors", "kd_factors", "motor_strength", "eff_kp", "eff_kd", "grav_off", "push_force", "cur_push",
     "push_remain", "delay", "foot_contact", "last_foot_contact", "air_time", "ep_sums", "errno", "link_pos", "link_vel",
     "contact_force", "torque", "stats", "ncontact", "nnewton", "terrain_row", "last_x",
-    "globals", "rew_terms", "replay", "fk_fresh", "ext_force", "actor_scan",
+    "globals", "rew_terms", "replay", "fk_fresh", "ext_force", "actor_scan", "spawn_pos", "ground_h",
 ]
 BUF = {n: i for i, n in enumerate(BUF_NAMES)}
 STATS_RESETS, STATS_TIMEOUTS, STATS_TRACKING, STATS_ERR, STATS_REW0 = 0, 1, 2, 3, 4
@@ -52,7 +52,8 @@ G_FRIC_GROUND, G_FRIC_ROBOT, G_MASS_SHIFT, G_COM_SHIFT, G_DR_COUNTER, GLOBALS_LE
 RP_ACT_NOISE, RP_OBS_NOISE, RP_PUSH, RP_CMD, RP_KPF, RP_KDF, RP_MS, RP_GO, RP_DELAY = 0, 12, 61, 64, 67, 79, 91, 103, 106
 RP_INIT_Z, RP_ROLL, RP_PITCH, RP_CMD_RESET, RP_ROW, RP_KP, RP_KD = 107, 108, 109, 110, 113, 114, 115
 RP_LIDAR_N, RP_LIDAR_U, RP_LIDAR_V = 116, 116 + MAX_ACTOR_SCAN, 116 + 2 * MAX_ACTOR_SCAN  # lidar variant: cell normals, cell uniforms, (offset, latency, blackout)
-REPLAY_LEN = RP_LIDAR_V + 3
+RP_SPAWN = RP_LIDAR_V + 3  # heightmap walk variant: spawn x, y uniforms
+REPLAY_LEN = RP_SPAWN + 2
 
 _i, _f, _u = C.c_int32, C.c_float, C.c_uint32
 
@@ -86,6 +87,8 @@ class EnvConfig(C.Structure):
         ("actor_lx", _f * MAX_ACTOR_SCAN), ("actor_ly", _f * MAX_ACTOR_SCAN), ("critic_lx", _f * MAX_CRITIC_SCAN), ("critic_ly", _f * MAX_CRITIC_SCAN),
         ("lidar_noise_std", _f), ("lidar_dropout", _f), ("lidar_blackout", _f), ("lidar_latency", _f), ("lidar_voffset_std", _f),
         ("lidar_clip", _f), ("lidar_scale", _f),
+        ("tm_on", _i), ("tm_max_wander", _f), ("tm_safe_half_x", _f), ("tm_safe_half_y", _f), ("tm_spawn_offset", _f),
+        ("tm_hs", C.c_double), ("tm_ox", C.c_double), ("tm_oy", C.c_double),
     ]
 
 

@@ -880,6 +880,83 @@ class Go2EnvStairLidar(Go2EnvStair):
         sp.lidar_noise_level = float(self._lidar_noise_level)
 
 
+class TerrainManager:
+    """Host-side view of the terrain state of `Go2EnvWalkTerrain`, with the attribute / method names of the reference's
+    examples/locomotion/terrain_manager.py that the env and eval scripts touch.  Only the custom-heightmap mode is built (the
+    sub-terrain grid mode needs Genesis' procedural terrain generator)."""
+
+    def __init__(self, terrain_cfg: dict, num_envs: int, device=None):
+        self.cfg = terrain_cfg or {}
+        self.enabled = bool(self.cfg.get("enabled", False))
+        self.device, self.num_envs = device, num_envs
+        if not self.enabled:
+            return
+        self.use_custom_heightmap = self.cfg.get("height_field", None) is not None
+        if not self.use_custom_heightmap:
+            raise NotImplementedError("terrain: only the custom height_field mode is supported (subterrain grids need Genesis' terrain generator)")
+        self.horizontal_scale = float(self.cfg.get("horizontal_scale", 0.25))
+        self.vertical_scale = float(self.cfg.get("vertical_scale", 0.005))
+        self.spawn_height_offset = float(self.cfg.get("spawn_height_offset", 0.05))
+        self.boundary_margin = float(self.cfg.get("boundary_margin", 1.0))
+        self._height_field_np = np.array(self.cfg["height_field"], dtype=np.float32)  # terrain_manager.py:63-76
+        rows, cols = self._height_field_np.shape
+        self._terrain_size_x, self._terrain_size_y = rows * self.horizontal_scale, cols * self.horizontal_scale
+        self.max_wander = min(self._terrain_size_x, self._terrain_size_y) / 2.0 - self.boundary_margin
+        self._terrain_origin = np.array([-self._terrain_size_x / 2.0, -self._terrain_size_y / 2.0, 0.0])
+        self._height_field = self._height_field_np
+        self.subterrain_types, self.n_rows, self.n_cols, self._tile_centers = None, 1, 1, None
+        self._env_spawn_pos = None  # bound to the device buffer by the env
+
+    def _query_height_batch(self, world_x, world_y):
+        """Bilinear ground height (terrain_manager.py:354-392), float64 numpy arithmetic like the reference."""
+        hf = self._height_field
+        R, Cc = hf.shape
+        lx = np.clip((np.asarray(world_x.detach().cpu()) - self._terrain_origin[0]) / self.horizontal_scale, 0, R - 2).astype(np.float64)
+        ly = np.clip((np.asarray(world_y.detach().cpu()) - self._terrain_origin[1]) / self.horizontal_scale, 0, Cc - 2).astype(np.float64)
+        ix, iy = lx.astype(np.int32), ly.astype(np.int32)
+        fx, fy = lx - ix, ly - iy
+        ix1, iy1 = np.minimum(ix + 1, R - 1), np.minimum(iy + 1, Cc - 1)
+        h = hf[ix, iy] * (1 - fx) * (1 - fy) + hf[ix1, iy] * fx * (1 - fy) + hf[ix, iy1] * (1 - fx) * fy + hf[ix1, iy1] * fx * fy
+        return torch.tensor(h * self.vertical_scale, device=world_x.device, dtype=torch.float32)
+
+    def get_height_at_robot(self, base_pos_xy):
+        return self._query_height_batch(base_pos_xy[:, 0], base_pos_xy[:, 1])
+
+    def check_boundary(self, base_pos_xy):
+        return torch.norm(base_pos_xy - self._env_spawn_pos[:, :2], dim=1) > self.max_wander
+
+    def get_terrain_type_string(self, env_idx: int) -> str:
+        return "custom_heightmap"
+
+
+class Go2EnvWalkTerrain(Go2EnvWalk):
+    """Walk env on a custom heightmap: examples/locomotion/go2_env_Omni_kplearn_varied_terrain.py + terrain_manager.py in heightmap mode
+    (SURVEY 8(f)-4).  The heightfield replaces the ground plane (same terrain narrow phase as the stair env); resets spawn the robot at a
+    random point of the map on top of the interpolated ground, an env is also reset when it wanders further than `max_wander` from
+    its spawn point, and the base-height reward is measured above the ground under the base."""
+
+    def _fill_flavour(self, c):
+        super()._fill_flavour(c)
+        self.terrain = T = TerrainManager(self.env_cfg.get("terrain", {}), self.num_envs, self.device)
+        if not T.enabled:
+            return
+        c.tm_on = 1
+        c.tm_max_wander, c.tm_spawn_offset = float(T.max_wander), float(T.spawn_height_offset)
+        c.tm_safe_half_x = float(T._terrain_size_x / 2.0 - T.boundary_margin - 0.5)
+        c.tm_safe_half_y = float(T._terrain_size_y / 2.0 - T.boundary_margin - 0.5)
+        c.tm_hs, c.tm_ox, c.tm_oy = float(T.horizontal_scale), float(T._terrain_origin[0]), float(T._terrain_origin[1])
+
+    def _after_bind(self):
+        super()._after_bind()
+        T = self.terrain
+        if T.enabled:
+            self.core.set_terrain(T._height_field_np * np.float32(T.vertical_scale), T.horizontal_scale, T._terrain_origin)
+            T._env_spawn_pos = self.core.buf["spawn_pos"]
+            self._ground_height = self.core.buf["ground_h"].view(-1)
+        else:
+            self._ground_height = torch.zeros(self.num_envs, device=self.device)
+
+
 class Go2EnvBaseFlavour(_Go2EnvBase):
     """Genesis stock Go2 env used by the crouch / jump scripts (go2_env_base.py): 12-dim action, 1-step
     latency through last_actions, solver-side PD, reset BEFORE rewards, 45-d obs, no privileged obs."""

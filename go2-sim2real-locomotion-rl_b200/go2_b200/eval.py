@@ -70,6 +70,11 @@ def respawn(env, envs_idx, terrain_row=None):
         centers = torch.tensor(env._terrain_row_centers, device=env.device, dtype=torch.float32)
         spawn = centers[env._env_terrain_row[ii].long()].clone()
         spawn[:, 2] += env.base_init_pos[2]
+    T = getattr(env, "terrain", None)
+    if T is not None and T.enabled:  # custom height map (go2_eval_walk.py:441-464): map centre, on top of the interpolated ground
+        xy = torch.zeros(n, 2, device=env.device)
+        spawn = torch.cat([xy, (T._query_height_batch(xy[:, 0], xy[:, 1]) + float(env.base_init_pos[2]) + T.spawn_height_offset)[:, None]], 1)
+        T._env_spawn_pos[ii] = spawn
     env.dof_pos[ii] = env.default_dof_pos
     env.dof_vel[ii] = 0.0
     env.robot.set_dofs_position(env.default_dof_pos.expand(n, 12), env.motors_dof_idx, zero_velocity=True, envs_idx=ii)

@@ -59,8 +59,9 @@ class DrawLog:
     def _wrap_t(self, fn, kind):
         def w(*a, **k):
             r = fn(*a, **k)
-            if sys._getframe(1).f_code.co_name == "_update_actor_lidar_scan":
-                self.calls.append(("_update_actor_lidar_scan", kind, r.clone()))
+            caller = sys._getframe(1).f_code.co_name
+            if caller in ("_update_actor_lidar_scan", "_sample_spawn_heightmap"):
+                self.calls.append((caller, kind, r.clone()))
             return r
 
         return w
@@ -103,7 +104,7 @@ def pre_state(env, kind):
     # dof_pos / dof_vel (from qpos / qvel), episode sums (running float32 sums of o_rew_terms)
     s = dict(qpos=r.get_qpos(), qvel=r.get_qvel(), qacc_ws=qws, warm=warm, cache_pair=ids, cache_n=nrm,
              commands=env.commands.numpy().copy(), ep_len=env.episode_length_buf.numpy().copy())
-    if kind in ("walk", "stair", "stair_lidar"):
+    if kind in ("walk", "stair", "stair_lidar", "walk_terrain"):
         s.update(hist_idx=np.array(env._action_history_write_idx), delay=env._delay_steps.numpy().copy(),
                  air_time=env._feet_air_time.numpy().copy(), foot_contact=env._foot_contact.numpy().copy(),
                  kp_factors=env._kp_factors.numpy().copy(), kd_factors=env._kd_factors.numpy().copy(), motor_strength=env._motor_strength.numpy().copy(),
@@ -115,6 +116,8 @@ def pre_state(env, kind):
             s.update(push_force=env._push_stored_force.numpy().copy(), push_remain=env._push_remaining.numpy().copy(), push_counter=np.array(env._push_counter))
     if kind in ("stair", "stair_lidar"):
         s.update(terrain_row=env._env_terrain_row.numpy().astype(np.int32), last_x=env._last_base_pos_x.numpy().copy())
+    if kind == "walk_terrain":
+        s.update(spawn_pos=env.terrain._env_spawn_pos.numpy().copy())
     if kind == "stair_lidar":
         s.update(actor_scan=env._actor_scan_buf.numpy().copy(), lidar_noise_level=np.array(float(env._lidar_noise_level)))
     return s
@@ -199,11 +202,16 @@ def draws_of_tick(env, kind, calls, done, ep_len_pre, A):
             row[ridx, abi.RP_DELAY] = r
         rr = by.pop("reset_idx", [])  # init z, roll, pitch in call order (go2_env_walk.py:1190-1203)
         i = 0
-        if "init_pos_z_range" in env.env_cfg:
+        if "init_pos_z_range" in env.env_cfg and not (kind == "walk_terrain" and env.terrain.enabled):  # (not drawn on a terrain)
             row[ridx, abi.RP_INIT_Z] = rr[i][1]; i += 1
         if "init_euler_range" in env.env_cfg:
             row[ridx, abi.RP_ROLL] = rr[i][1]; row[ridx, abi.RP_PITCH] = rr[i + 1][1]; i += 2
         assert i == len(rr)
+        sp_ = by.pop("_sample_spawn_heightmap", [])
+        if sp_:  # terrain_manager.py:293-296: x uniforms, then y uniforms
+            assert [k for k, _ in sp_] == ["u", "u"]
+            row[ridx, abi.RP_SPAWN] = sp_[0][1]
+            row[ridx, abi.RP_SPAWN + 1] = sp_[1][1]
         if kind in ("stair", "stair_lidar"):
             by.pop("_assign_terrain_rows", None)
             row[ridx, abi.RP_ROW] = env._env_terrain_row.numpy()[ridx]
@@ -219,7 +227,7 @@ def outputs(env, obs, rew, done, extras, kind, terms):
     # the state after the tick (qpos, qvel, commands, ep_len, DR buffers ...) is the NEXT tick's pre-state (`final_*` after the last)
     o = dict(o_obs=obs.numpy().copy(), o_rew=rew.numpy().copy(), o_reset=done.numpy().astype(np.uint8), o_timeout=extras["time_outs"].numpy().copy(),
              o_ncon=r.get_solver_stats()[:, 0].copy(), o_rew_terms=terms)
-    if kind in ("walk", "stair", "stair_lidar"):
+    if kind in ("walk", "stair", "stair_lidar", "walk_terrain"):
         pr = extras["observations"]["critic"].numpy()
         assert np.array_equal(pr[:, :env.num_obs], o["o_obs"])
         o.update(o_priv_tail=pr[:, env.num_obs:].copy(), o_foot_contact=env._foot_contact.numpy().copy())
@@ -280,7 +288,7 @@ def instrument_rewards(env):
 
 
 def run(env_cls, module, cfgs, kind, B, T, act_std, seed, act_dim, after_build=None, random_ep_len=True):
-    cfgs_json = json.loads(json.dumps(cfgs))  # pristine copy (the ctor multiplies reward scales by dt in place)
+    cfgs_json = json.loads(json.dumps(cfgs, default=lambda o: "ndarray"))  # pristine copy (the ctor multiplies reward scales by dt in place)
     torch.manual_seed(1)
     with contextlib.redirect_stdout(io.StringIO()):
         env = env_cls(B, *cfgs)
@@ -356,6 +364,25 @@ def stair_lidar_cfgs():
     return env_cfg, obs_cfg, reward_cfg, command_cfg
 
 
+def walk_terrain_cfgs():
+    """examples/locomotion/go2_train_Omni_kplearn_varied_terrain.get_cfgs() (heightmap mode: left half flat, right half smoothed random
+    bumps drawn with numpy's global RNG, seeded here), short episodes, and a small map so that the boundary reset occurs."""
+    import ast
+
+    path = os.path.join(REF, "examples/locomotion/go2_train_Omni_kplearn_varied_terrain.py")
+    tree = ast.parse(open(path).read())
+    keep = [n for n in tree.body if isinstance(n, (ast.FunctionDef, ast.Assign))]  # module constants (TERRAIN_MODE, HEIGHTMAP_*) + functions
+    ns = {"np": np}
+    exec(compile(ast.Module(body=keep, type_ignores=[]), path, "exec"), ns)
+    ns["HEIGHTMAP_SIZE_X"], ns["HEIGHTMAP_SIZE_Y"] = 6.0, 5.0  # 120 x 100 cells: max_wander = 1.5 m
+    np.random.seed(11)
+    with contextlib.redirect_stdout(io.StringIO()):
+        env_cfg, obs_cfg, reward_cfg, command_cfg = ns["get_cfgs"]()
+    env_cfg.update(episode_length_s=4.0, resampling_time_s=1.0)
+    env_cfg["curriculum"]["level_init"] = 1.0  # full command ranges: the robots cover ground
+    return env_cfg, obs_cfg, reward_cfg, command_cfg
+
+
 def base_allrew_cfgs():
     """go2_train_crouch.get_cfgs() with EVERY reward term of go2_env_base.py switched on (the shipped scripts use 6-10 of the 20;
     logs/go2-crouch/cfgs.pkl names crouch_2 / y_stability / crouch_speed but lacks the termination keys the final env class
@@ -386,8 +413,11 @@ def main():
 
     sys.path.insert(0, os.path.join(REF, "examples/locomotion"))
     import go2_env_stair_lidar
+    import go2_env_Omni_kplearn_varied_terrain as go2_env_wt
+    import terrain_manager  # noqa: F401  (the env imports it inside its ctor)
 
     jobs = {
+        "walk_terrain_c1": lambda: (go2_env_wt.Go2Env, go2_env_wt, walk_terrain_cfgs(), "walk_terrain", 16, 300, 0.5, 515, 16),
         "stair_lidar_c1": lambda: (go2_env_stair_lidar.Go2Env, go2_env_stair_lidar, stair_lidar_cfgs(), "stair_lidar", 16, 300, 0.5, 909, 16),
         "walk_c1": lambda: (go2_env_walk.Go2Env, go2_env_walk, walk_cfgs(), "walk", 32, 1000, 0.5, 1234, 16),
         "walk_hard": lambda: (go2_env_walk.Go2Env, go2_env_walk, walk_hard_cfgs(), "walk", 16, 300, 0.6, 4242, 16),
@@ -397,7 +427,13 @@ def main():
     only = sys.argv[1:] or list(jobs)
     for name in only:
         cls, mod, cfgs, kind, B, T, std, seed, ad = jobs[name]()
+        hf = None
+        if isinstance(cfgs[0].get("terrain", {}).get("height_field", None), np.ndarray):
+            hf = cfgs[0]["terrain"]["height_field"]  # kept as an array for the reference env, stored in the npz for the tests
         out, cj, names = run(cls, mod, cfgs, kind, B, T, std, seed, ad)
+        if hf is not None:
+            out["cfg_height_field"] = hf
+            cj[0]["terrain"]["height_field"] = "npz:cfg_height_field"
         np.savez_compressed(os.path.join(OUT, name + ".npz"), **out)
         with open(os.path.join(OUT, name + "_cfg.json"), "w") as f:
             json.dump(cj, f)
