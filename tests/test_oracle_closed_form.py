@@ -5,6 +5,7 @@ rigid solver, so the restatement is pinned against things that can be derived on
     (narrowphase.py:724-736, not restated) converges to for the only pairs on which it fires in the walk / crouch / jump envs;
   * the soft-contact law: resting normal force of every contact = 4 K imp(pen) pen / diag from MuJoCo's published solref /
     solimp formulas (geom.py:405-427, solver.py:498-595);
+  * Coulomb's slip threshold of the friction pyramid and the closed-form minimiser of a single joint-limit row;
   * free flight: the centre of mass accelerates with exactly g and the angular momentum about it is conserved;
   * `invweight` / `meaninertia` of the model table (shared by product and oracle) recomputed from the oracle's mass matrix and
     a velocity-kinematics Jacobian, following rigid_solver.py:529-682.
@@ -232,3 +233,64 @@ def test_mpr_box_and_cylinder_vs_ground_match_the_deepest_point_answer():
                 n += 1
     assert n > 50
     print(f"\n{n} box / cylinder vs ground MPR contacts equal the deepest-point answer (max |d pen| = {worst_pen:.2e}, max 1 - |n.z| = {worst_n:.2e})")
+
+
+def test_friction_pyramid_slip_threshold():
+    """Standing robot (PD hold) on mu = 0.3 pushed horizontally at the base along a pyramid axis (world x): below mu m g it stays put
+    (the soft constraint only creeps), above it slides with a = (F - mu m g) / m.  Exercises contact-row assembly, the pyramid's
+    friction limit and the Newton solve's active-set logic against Coulomb's law."""
+    m, mu, g = MODEL["total_mass"], 0.3, 9.81
+    out = {}
+    for frac in (0.5, 1.6):
+        o = OracleRigid(1, kind="f64")
+        o.set_friction(0, mu)
+        o.set_friction(1, mu)
+        o.set_dofs_position(Q0[None], MDI)
+        o.set_dofs_kp(np.full(12, 60.0), MDI)
+        o.set_dofs_kv(np.full(12, 5.0), MDI)
+        for _ in range(1500):  # settle
+            o.control_dofs_position(Q0[None], MDI)
+            o.step(1)
+        F = frac * mu * m * g
+        vx = []
+        for k in range(60):  # 0.6 s of pushing (the force is cleared by every step call, like Scene.step does)
+            o.control_dofs_position(Q0[None], MDI)
+            o.apply_link_external_force(np.array([[F, 0.0, 0.0]]), 1)
+            o.step(1)
+            vx.append(o.get_qvel()[0, 0])
+        out[frac] = (F, np.array(vx))
+    F, vx = out[0.5]
+    assert abs(vx[-1]) < 0.01 and np.abs(vx).max() < 0.15, vx[-5:]  # sticks: the legs deflect under the PD hold (transient sway), then rest
+    F, vx = out[1.6]
+    a = (vx[-1] - vx[19]) / (40 * 0.01)  # mean acceleration over the last 0.4 s
+    assert a == pytest.approx((F - mu * m * g) / m, rel=0.15), (a, (F - mu * m * g) / m)
+
+
+def test_single_joint_limit_row_has_the_closed_form_solution():
+    """Robot in free flight with ONE joint pushed 0.05 rad past its upper limit and nothing else active: the constrained
+    acceleration minimises 1/2 (a - a0)' M (a - a0) + 1/2 D (J a - aref)^2, i.e. a = a0 + M^-1 J' f with
+    f = -D (J a0 - aref) / (1 + D J M^-1 J') - checked against the oracle's limit row (solver.py:1088-1143: jac = -1 at the upper
+    limit, diag = invweight_dof (1 - imp) / imp) and its Newton solve."""
+    link = next(l for l in MODEL["links"] if l["name"] == "FL_calf")
+    j, over = link["dof_start"], 0.05
+    o = OracleRigid(1, kind="f64", base_pos=(0.0, 0.0, 1.0))
+    o.set_dofs_position(Q0[None], MDI)
+    q = o.get_qpos()
+    q[0, link["q_start"]] = link["limit"][1] + over
+    o.set_qpos(q)
+    o.set_qvel(np.zeros((1, 18)))
+    o.control_dofs_force(np.zeros((1, 12)), MDI)
+    o.step(1)
+    assert len(o.get_contacts(0)[0]) == 0
+    a0, a = o.get_acc()
+    M = o.get_mass_matrix(0)
+    imp, aref = _sol(-over, 0.0, -over)
+    D = 1.0 / (MODEL["dofs_invweight"][j] * (1 - imp) / imp)
+    J = np.zeros(18)
+    J[j] = -1.0
+    Minv_Jt = np.linalg.solve(M, J)
+    f = -D * (J @ a0[0] - aref) / (1.0 + D * (J @ Minv_Jt))
+    assert f > 0
+    want = a0[0] + Minv_Jt * f
+    np.testing.assert_allclose(a[0], want, rtol=1e-6, atol=1e-6 * np.abs(want).max())
+    assert a[0, j] < a0[0, j] - 1.0  # the limit pushes the joint back (negative direction at the upper limit)
