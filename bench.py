@@ -193,7 +193,7 @@ def bench_env(args, workload, B, rank, world, dev, headline):
 
     env_cls = {"walk": Go2EnvWalk, "stair": Go2EnvStair, "stair_lidar": Go2EnvStairLidar}.get(workload, Go2EnvBaseFlavour)
     env = env_cls(B, *load_cfgs(workload), device=dev, seed=1, env_offset=rank * B, total_envs=world * B,
-                  stats_sync_interval=args.stats_interval, lib_path=os.environ.get("GO2_B200_LIB") or None)
+                  stats_sync_interval=args.stats_interval, lib_path=os.environ.get("GO2_B200_LIB") or None, fast_math=(args.math == "fast"))
     env.reset()
     g = torch.Generator(device=dev).manual_seed(1234 + rank)
     n_act = 8
@@ -297,6 +297,17 @@ def bench_env(args, workload, B, rank, world, dev, headline):
         res["ms_roll"], res["n_roll"] = timed(roll, n_roll), n_roll
         res["actor_macs"] = sum(a * b for a, b in zip([env.num_obs, 512, 256, 128], [512, 256, 128, env.num_actions]))
     env.flush_stats()
+    if headline and env.fast_math and not os.environ.get("GO2_B200_LIB"):
+        # the same window on the IEEE-division build (the one the bit-faithful parity claim is stated for), for reference
+        env2 = env_cls(B, *load_cfgs(workload), device=dev, seed=1, env_offset=rank * B, total_envs=world * B, stats_sync_interval=args.stats_interval,
+                       fast_math=False)
+        env2.reset()
+        env2.episode_length_buf = torch.randint(0, int(env2.max_episode_length), (B,), device=dev, generator=g, dtype=torch.int32)
+        for i in range(args.settle + W):
+            env2.step(acts[i % n_act])
+        res["ms_precise"] = timed(lambda i: env2.step(acts[i % n_act]))
+        env2.flush_stats()
+        env2.close()
     return res
 
 
@@ -321,6 +332,7 @@ def emit(args, workload, B, world, res, headline, cpu):
         "metric": METRIC if workload == "walk" else METRIC.replace("walk", workload), "value": value, "unit": UNIT, "n_gpus": world, "steps": K,
         "warmup": max(3, args.warmup), "ms_per_step": res["ms_total"] / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic", "config": dict(workload_config(workload, B), stats_sync_interval=env.stats_sync_interval, settle_ticks=args.settle,
+                                                       math=("fast (approximate division / sqrt like the reference's fast_math; libgo2_b200_fast.so)" if env.fast_math else "precise (IEEE division / sqrt; libgo2_b200.so)"),
                                                        population="episode lengths randomised (rsl-rl init_at_random_ep_len), settle_ticks untimed ticks before the warm-up: steady-state poses and a steady stream of time-out resets"),
         "e2e": {"value": world * B * K / (res["ms_e2e"] * 1e-3), "unit": UNIT, "h2d_bytes_per_step": B * env.num_actions * 4,
                 "d2h_bytes_per_step": B * (env.num_obs * 4 + 4 + 1), "ms_per_step": res["ms_e2e"] / K,
@@ -342,6 +354,9 @@ def emit(args, workload, B, world, res, headline, cpu):
     if res.get("ms_fresh"):
         out["fresh_after_reset"] = {"value": world * B * K / (res["ms_fresh"] * 1e-3), "unit": UNIT, "ms_per_step": res["ms_fresh"] / K,
                                     "what": "the same K ticks timed right after reset() + W warm-up ticks (the protocol of BENCH_r01): every env still near the standing start pose, no resets in the window - cheaper than a running job, reported for continuity only"}
+    if res.get("ms_precise"):
+        out["precise_math"] = {"value": world * B * K / (res["ms_precise"] * 1e-3), "unit": UNIT, "ms_per_step": res["ms_precise"] / K,
+                               "what": "the same steady-state window on libgo2_b200.so (IEEE division / sqrt): the build whose results are bit-faithful to the CPU oracle's operation order"}
     if "ms_pol" in res:
         out["with_policy"] = {"value": world * B * K / (res["ms_pol"] * 1e-3), "unit": UNIT, "ms_per_step": res["ms_pol"] / K,
                               "policy": f"{env.num_obs}-512-256-128-{env.num_actions} ELU actor, fixed-seed random init (shipped model_188000.pt blob absent), torch fp32, inside the timed loop"}
@@ -370,7 +385,7 @@ def run_gpu(args):
         jobs += [("walk", 4096, False), ("stair", 8192, False), ("stair_lidar", 8192, False), ("crouch", 4096, False), ("jump", 4096, False)]
     for workload, B, headline in jobs:
         res = bench_env(args, workload, B, rank, world, dev, headline)
-        keys = ["ms_total", "ms_e2e", "kern_avg", "kern_med"] + [k for k in ("ms_pol", "ms_fused", "ms_roll", "ms_k_fused", "ms_k_torch") if k in res]
+        keys = ["ms_total", "ms_e2e", "kern_avg", "kern_med"] + [k for k in ("ms_pol", "ms_fused", "ms_roll", "ms_k_fused", "ms_k_torch", "ms_fresh", "ms_precise") if res.get(k) is not None]
         t = torch.tensor([res[k] for k in keys], device=dev, dtype=torch.float64)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -395,6 +410,10 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=48)
     ap.add_argument("--warmup", type=int, default=12)
+    ap.add_argument("--math", default="fast", choices=["fast", "precise"],
+                    help="fast = the library build with approximate division / sqrt, the arithmetic class of the reference (its solver is JIT-compiled "
+                         "with fast_math on, genesis/__init__.py:289) and what the drop-in genesis.init() selects; precise = IEEE division / sqrt, the "
+                         "build the bit-faithful parity against the CPU oracle is stated for")
     ap.add_argument("--settle", type=int, default=240, help="untimed ticks after reset() before the warm-up (steady-state population); 0 = time right after reset()")
     ap.add_argument("--envs", type=int, default=0, help="envs per GPU (default: 65,536 walk, 8,192 stair, 4,096 crouch / jump)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])

@@ -16,8 +16,11 @@ logger = logging.getLogger("genesis")
 constraint_solver = types.SimpleNamespace(Newton="Newton", CG="CG")
 
 
-def init(backend=None, precision="32", performance_mode=False, seed=None, logging_level=None, **kw):
+def init(backend=None, precision="32", performance_mode=False, seed=None, logging_level=None, debug=False, **kw):
     global device
+    from go2_b200 import envs as _envs
+
+    _envs.DEFAULT_FAST_MATH[0] = not debug  # genesis/__init__.py:289: the reference's kernels are compiled with fast_math unless debug
     if backend == cpu:
         raise RuntimeError("go2_b200 has no CPU backend (CUDA only)")
     if str(precision) != "32":

@@ -18,6 +18,10 @@ MAX_ACTOR_SCAN, MAX_CRITIC_SCAN = 32, 96
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CUDA_LIB_PATH = os.path.join(_HERE, "libgo2_b200.so")
+# the same sources compiled with approximate division / square root (nvcc -prec-div=false -prec-sqrt=false -ftz=true): the arithmetic class
+# of the reference itself, whose solver is always JIT-compiled with fast_math on (genesis/__init__.py:289 `fast_math=not debug`).
+# libgo2_b200.so keeps IEEE division / sqrt and is what the bit-faithful parity against the CPU oracle is stated for.
+CUDA_LIB_FAST_PATH = os.path.join(_HERE, "libgo2_b200_fast.so")
 
 ENV_WALK, ENV_STAIR, ENV_BASE = 0, 1, 2
 CTRL_MANUAL_PLS, CTRL_MANUAL_FIXED, CTRL_GENESIS_PD = 0, 1, 2

@@ -115,6 +115,11 @@ def _default_device():
 _DEFAULT_CORE = [Go2Core]  # the test-suite swaps in its host emulation of the kernel source here (tests/hostemu_core.py)
 
 
+# default arithmetic of new envs: False = IEEE division / sqrt (libgo2_b200.so), True = approximate (libgo2_b200_fast.so, ~9 % faster).
+# The drop-in `genesis.init()` sets it like the reference does for its own solver: fast_math = not debug (genesis/__init__.py:289).
+DEFAULT_FAST_MATH = [False]
+
+
 class _Go2EnvBase:
     """State shared by the walk / stair / base flavours: buffers, views, rsl-rl facing attributes."""
 
@@ -122,13 +127,15 @@ class _Go2EnvBase:
 
     def __init__(self, num_envs, env_cfg, obs_cfg, reward_cfg, command_cfg, show_viewer=False, *, device=None, seed=1,
                  env_offset=0, total_envs=None, lib_path=None, stats_sync_interval=1, sync_ranks=True, core_cls=None,
-                 replay=False, export_reward_terms=False, solver_dense=False):
+                 replay=False, export_reward_terms=False, solver_dense=False, fast_math=None):
         """Keyword-only extras (none is needed by the train / eval scripts):
         stats_sync_interval  ticks between reads of the device-side episode statistics.  1 = read (and wait) every tick, the
                              reference's timing for extras["episode"] and the curriculum; k > 1 = an asynchronous double-buffered
                              read every k ticks (no tick waits for the host; the curriculum sees the numbers k ticks late).
         sync_ranks           with torch.distributed initialised: sum the per-tick statistics over the ranks (env shards) on the
                              device, so that every rank runs the same curriculum / global-DR state machine.
+        fast_math            True = the library build with approximate division / sqrt (the reference's own fast_math arithmetic class,
+                             ~9 % faster), False = IEEE (bit-faithful parity against the CPU oracle); None = DEFAULT_FAST_MATH.
         replay               allocate the draw-replay buffer (fixture replay, see replay_draws()).
         export_reward_terms  keep every scaled reward term of the tick in `reward_terms` [B, n_rew].
         solver_dense         diagnostic: every env takes the dense 18x18 Newton path."""
@@ -150,7 +157,8 @@ class _Go2EnvBase:
         self._np_rng = np.random.default_rng(self._seed)
         self._env_offset = int(env_offset)
         self._total_envs = int(total_envs) if total_envs is not None else self.num_envs
-        self._lib_path = lib_path
+        self.fast_math = bool(DEFAULT_FAST_MATH[0] if fast_math is None else fast_math)
+        self._lib_path = lib_path or (abi.CUDA_LIB_FAST_PATH if self.fast_math and core_cls is None and _DEFAULT_CORE[0] is Go2Core else None)
         self._core_cls = core_cls or _DEFAULT_CORE[0]
         self.stats_sync_interval = int(stats_sync_interval)
         self._sync_ranks = bool(sync_ranks)

@@ -25,6 +25,8 @@ def test_header_symbols_exported():
     assert declared2 == set(abi._POLICY_EXPORTS), declared2 ^ set(abi._POLICY_EXPORTS)
     for name in abi._POLICY_EXPORTS:
         assert hasattr(lib.lib, name), name
+    fast = abi.Go2Lib(abi.CUDA_LIB_FAST_PATH)  # the fast-math build of the same sources exports the same ABI
+    assert fast.stats_len == lib.stats_len and all(hasattr(fast.lib, n) for n in abi._EXPORTS + abi._POLICY_EXPORTS)
 
 
 def test_missing_library_fails_loudly(tmp_path):

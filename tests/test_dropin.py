@@ -31,8 +31,10 @@ def dropin(backend, hostemu_lib, monkeypatch):
         sys.modules.pop(m, None)
     gs = importlib.import_module("genesis")
     assert os.path.dirname(gs.__file__).startswith(DROPIN)
+    import go2_b200.envs as envs
+
+    monkeypatch.setattr(envs, "DEFAULT_FAST_MATH", [False])  # gs.init() switches the default to the fast-math build: undone after the test
     if backend == "hostemu":
-        import go2_b200.envs as envs
         from hostemu_core import HostEmuCore
 
         monkeypatch.setattr(envs, "_DEFAULT_CORE", [HostEmuCore])

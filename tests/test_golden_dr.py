@@ -20,6 +20,11 @@ from util import Derived, close, force_state_dr, load_golden, make_env, np_, pre
 
 ATOL, RTOL = 1e-4, 1e-3
 BACKENDS = ["hostemu", pytest.param("cuda", marks=pytest.mark.gpu)]
+# the library build with approximate division / sqrt (the reference's own fast_math arithmetic class, what `bench.py` and the drop-in
+# `genesis.init()` select): same code, so the same fixtures - but an operation that is 1-2 ulp off can flip a borderline decision (a
+# foot-contact flag at the 3 N threshold, a contact mode), after which that env-tick is off by far more than the band.  Measured on
+# a B200: 1 such env-tick in walk_c1's 32,000, 2 in walk_hard's 4,800 (profiles/r02_fast_math_parity.txt).  Budget: 1 in 2,000.
+FAST_EXTRA = lambda n: max(2, n // 2000)  # noqa: E731
 # fixture, env kind, env-ticks allowed outside the float band (contact-mode flips at the solver tolerance)
 # walk_terrain_c1 (walk env on a custom height map, smoothed +-8 cm bumps): 3.7 %, contacts on prism edges again
 # stair_lidar_c1 (go2_stair_train_lidar cfg: 20 cm risers, 25 cm treads): 7.5 % for the same reason; its lidar outputs (actor scan in the
@@ -92,6 +97,15 @@ def _run(name, kind, backend, hostemu_lib, stride=1):
                 bad_float.append((name, t, int(e)))
         der.advance(g, t)
     return bad_exact, bad_float, worst, T * B // stride
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,kind,max_outside", CASES)
+def test_teacher_forced_fast_math_build(name, kind, max_outside, hostemu_lib):
+    bad_exact, bad_float, worst, n = _run(name, kind, "cuda_fast", hostemu_lib)
+    print(f"\n[{name}/cuda_fast] {n} env-ticks, {len(bad_exact)} exact mismatches {bad_exact[:4]}, {len(bad_float)} outside the band, worst {worst}")
+    assert len(bad_exact) <= FAST_EXTRA(n), bad_exact[:10]
+    assert len(bad_float) <= max_outside + FAST_EXTRA(n), (len(bad_float), worst)
 
 
 @pytest.mark.parametrize("backend", BACKENDS)

@@ -28,7 +28,7 @@ def make_env(kind, cfgs, B, backend, hostemu_lib=None, **kw):
         from hostemu_core import HostEmuCore
 
         return cls(B, *cfgs, device="cpu", lib_path=hostemu_lib, core_cls=HostEmuCore, **kw)
-    return cls(B, *cfgs, device="cuda:0", **kw)
+    return cls(B, *cfgs, device="cuda:0", fast_math=(backend == "cuda_fast"), **kw)
 
 
 def _t(env, a, dtype=torch.float32):
