@@ -9,6 +9,7 @@ schedule, delay-ring write index) and turns them into the per-step parameter blo
 """
 from __future__ import annotations
 
+import ctypes as C
 import math
 
 import numpy as np
@@ -30,7 +31,8 @@ def _lerp(a, b, t):
 
 
 def _lerp_range(a, b, t):
-    return [_lerp(a[0], b[0], t), _lerp(a[1], b[1], t)]
+    t = 0.0 if t < 0.0 else (1.0 if t > 1.0 else float(t))  # == _clamp01, inlined: this runs ~15 times per tick on the host
+    return [a[0] + (b[0] - a[0]) * t, a[1] + (b[1] - a[1]) * t]
 
 
 class CurriculumManager:
@@ -570,6 +572,7 @@ class Go2EnvWalk(_Go2EnvBase):
         nv[9:21] = nc.get("dof_pos", 0.0) * s["dof_pos"] * nl
         nv[21:33] = nc.get("dof_vel", 0.0) * s["dof_vel"] * nl
         self.obs_noise_vec = nv
+        self._obs_noise_c = (C.c_float * abi.NOBS_MAX)(*[float(v) for v in nv[:abi.NOBS_MAX]])  # copied into StepParams in one go
 
     def _apply_curriculum_level(self, force=False):
         if not self.curriculum.enabled and not force:
@@ -630,8 +633,7 @@ class Go2EnvWalk(_Go2EnvBase):
         sp.action_noise_std = float(self._action_noise_std_cur)
         if self.obs_noise_vec is not None:
             sp.obs_noise_on = 1
-            for i in range(min(self.num_obs, abi.NOBS_MAX)):  # (a lidar scan appended to the obs carries its own noise model)
-                sp.obs_noise[i] = float(self.obs_noise_vec[i])
+            sp.obs_noise = self._obs_noise_c  # the proprioceptive entries (a lidar scan appended to the obs carries its own noise model)
         for i, k in enumerate(("lin_vel_x", "lin_vel_y", "ang_vel")):
             sp.cmd_lo[i], sp.cmd_hi[i] = float(self._cmd_cur_ranges[k][0]), float(self._cmd_cur_ranges[k][1])
         t = self._t_sample = self._sample_t()
