@@ -45,7 +45,11 @@ struct go2_handle {
 #define GO2_TPB_SMALL 256
 #endif
 #ifndef GO2_TPB
-#define GO2_TPB 512  // max envs (threads) per block; the launch picks blockDim <= GO2_TPB
+#define GO2_TPB 256  // max envs (threads) per block; the launch picks blockDim <= GO2_TPB
+#endif
+#ifndef GO2_MIN_BLOCKS
+#define GO2_MIN_BLOCKS 2  // resident blocks per SM the register budget is sized for: 2 x 224 threads x 128 registers at 65,536 envs
+                          // (measured +1 % over one 448-thread block per SM, -DGO2_TPB=512 -DGO2_MIN_BLOCKS=1; profiles/r02_experiments.md)
 #endif
 
 __device__ __forceinline__ void accumulate_stats(const EnvConfig* gcfg, const StepParams& sp, const Buffers& bf, const EnvStepOut& out, int err) {
@@ -87,8 +91,8 @@ __device__ __forceinline__ void step_body(const Go2Model* __restrict__ gm, const
         }
     }
 }
-// large batches: up to GO2_TPB threads per block, 128 registers (one 448-thread block per SM at 65,536 envs)
-__global__ void __launch_bounds__(GO2_TPB) go2_step_kernel(const Go2Model* __restrict__ gm, const EnvConfig* __restrict__ gcfg,
+// large batches: up to GO2_TPB threads per block, 128 registers (two 224-thread blocks per SM at 65,536 envs)
+__global__ void __launch_bounds__(GO2_TPB, GO2_MIN_BLOCKS) go2_step_kernel(const Go2Model* __restrict__ gm, const EnvConfig* __restrict__ gcfg,
                                                            StepParams sp, Buffers bf, const float* __restrict__ actions) {
     step_body(gm, gcfg, sp, bf, actions);
 }
@@ -172,7 +176,7 @@ int go2_create(const int32_t* model_iv, int n_iv, const double* model_fv, int n_
     h->post_pending = 0;
     memcpy(&h->cfg, cfg, sizeof(EnvConfig));
     {
-        // One block per SM per wave, as large as allowed: the warps of a block run phase-locked (barriers in
+        // k blocks per SM over all waves, as large as allowed: the warps of a block run phase-locked (barriers in
         // t_env_step / solve_constraints) and share instruction fetches, so big blocks win; the block size is
         // the smallest multiple of 32 that covers the envs with k * n_SM blocks.
         int n_sm = 148;
