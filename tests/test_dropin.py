@@ -27,7 +27,7 @@ def _cfgs(name):
 def dropin(backend, hostemu_lib, monkeypatch):
     """sys.path as INTEGRATION.md prescribes; on the CPU backend the env's native core is the host emulation of the kernel."""
     monkeypatch.syspath_prepend(DROPIN)
-    for m in ("genesis", "genesis.utils", "genesis.utils.geom", "go2_env_walk", "go2_env_stair", "go2_env_base", "go2_env"):
+    for m in ("genesis", "genesis.utils", "genesis.utils.geom", "go2_env_walk", "go2_env_stair", "go2_env_base", "go2_env", "go2_env_stair6", "go2_env_stair4", "go2_env_stair3", "go2_env_Omni_walk_16output"):
         sys.modules.pop(m, None)
     gs = importlib.import_module("genesis")
     assert os.path.dirname(gs.__file__).startswith(DROPIN)
@@ -42,7 +42,7 @@ def dropin(backend, hostemu_lib, monkeypatch):
     else:
         gs.init(backend=gs.gpu, precision="32", performance_mode=True)
     yield gs
-    for m in ("genesis", "genesis.utils", "genesis.utils.geom", "go2_env_walk", "go2_env_stair", "go2_env_base", "go2_env"):
+    for m in ("genesis", "genesis.utils", "genesis.utils.geom", "go2_env_walk", "go2_env_stair", "go2_env_base", "go2_env", "go2_env_stair6", "go2_env_stair4", "go2_env_stair3", "go2_env_Omni_walk_16output"):
         sys.modules.pop(m, None)
 
 
@@ -95,7 +95,7 @@ def test_walk_module_as_the_train_script_uses_it(backend, dropin):
 
 
 @pytest.mark.parametrize("backend", BACKENDS)
-@pytest.mark.parametrize("module,cfg,n_obs,n_act,n_priv", [("go2_env_stair", "stair", 49, 16, 182), ("go2_env_stair4_lidar", "stair_lidar", 64, 16, 165),
+@pytest.mark.parametrize("module,cfg,n_obs,n_act,n_priv", [("go2_env_stair", "stair", 49, 16, 182), ("go2_env_stair6", "stair", 49, 16, 182), ("go2_env_Omni_walk_16output", "walk", 49, 16, 104), ("go2_env_stair4_lidar", "stair_lidar", 64, 16, 165),
                                                            ("go2_env_stair_lidar", "stair_lidar", 64, 16, 165), ("go2_env_base", "crouch", 45, 12, None), ("go2_env", "go2", 45, 12, None),
                                                            ("go2_env_base", "jump", 45, 12, None)])
 def test_stair_and_base_modules(backend, dropin, module, cfg, n_obs, n_act, n_priv):
