@@ -193,7 +193,7 @@ def bench_env(args, workload, B, rank, world, dev, headline):
 
     env_cls = {"walk": Go2EnvWalk, "stair": Go2EnvStair, "stair_lidar": Go2EnvStairLidar}.get(workload, Go2EnvBaseFlavour)
     env = env_cls(B, *load_cfgs(workload), device=dev, seed=1, env_offset=rank * B, total_envs=world * B,
-                  stats_sync_interval=args.stats_interval, lib_path=os.environ.get("GO2_B200_LIB") or None, fast_math=(args.math == "fast"))
+                  stats_sync_interval=args.stats_interval, lib_path=os.environ.get("GO2_B200_LIB") or None, fast_math=(args.math == "fast"), sync_ranks=args.rank_sync)
     env.reset()
     g = torch.Generator(device=dev).manual_seed(1234 + rank)
     n_act = 8
@@ -331,7 +331,7 @@ def emit(args, workload, B, world, res, headline, cpu):
     out = {
         "metric": METRIC if workload == "walk" else METRIC.replace("walk", workload), "value": value, "unit": UNIT, "n_gpus": world, "steps": K,
         "warmup": max(3, args.warmup), "ms_per_step": res["ms_total"] / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic", "config": dict(workload_config(workload, B), stats_sync_interval=env.stats_sync_interval, settle_ticks=args.settle,
+        "dtype": "f32", "data": "synthetic", "config": dict(workload_config(workload, B), stats_sync_interval=env.stats_sync_interval, settle_ticks=args.settle, rank_sync=bool(args.rank_sync),
                                                        math=("fast (approximate division / sqrt like the reference's fast_math; libgo2_b200_fast.so)" if env.fast_math else "precise (IEEE division / sqrt; libgo2_b200.so)"),
                                                        population="episode lengths randomised (rsl-rl init_at_random_ep_len), settle_ticks untimed ticks before the warm-up: steady-state poses and a steady stream of time-out resets"),
         "e2e": {"value": world * B * K / (res["ms_e2e"] * 1e-3), "unit": UNIT, "h2d_bytes_per_step": B * env.num_actions * 4,
@@ -414,6 +414,9 @@ def main():
                     help="fast = the library build with approximate division / sqrt, the arithmetic class of the reference (its solver is JIT-compiled "
                          "with fast_math on, genesis/__init__.py:289) and what the drop-in genesis.init() selects; precise = IEEE division / sqrt, the "
                          "build the bit-faithful parity against the CPU oracle is stated for")
+    ap.add_argument("--rank-sync", action="store_true",
+                    help="N > 1: all-reduce the statistics row every tick so that all ranks run ONE curriculum / global-DR state machine (default: "
+                         "independent env shards, no collective on the step path - what N copies of the reference script would be)")
     ap.add_argument("--settle", type=int, default=240, help="untimed ticks after reset() before the warm-up (steady-state population); 0 = time right after reset()")
     ap.add_argument("--envs", type=int, default=0, help="envs per GPU (default: 65,536 walk, 8,192 stair, 4,096 crouch / jump)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
