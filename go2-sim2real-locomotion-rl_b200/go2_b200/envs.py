@@ -1158,7 +1158,11 @@ class _RobotFacade:
 
 class _GroundFacade:
     def __init__(self, env):
+        import types
+
         self._env = env
+        # go2_eval_stairs.py:592-601 looks the ground plane up among scene.entities by its URDF file name
+        self.morph = types.SimpleNamespace(file="urdf/plane/plane.urdf") if not getattr(env, "_use_terrain", False) else types.SimpleNamespace()
 
     def set_friction(self, mu):
         self._env._set_global(abi.G_FRIC_GROUND, mu)
@@ -1172,6 +1176,10 @@ class _SceneFacade:
 
         self.sim = types.SimpleNamespace(rigid_solver=self)
         self._env = env
+
+    @property
+    def entities(self):
+        return [self._env.ground, self._env.robot]
 
     def apply_links_external_force(self, force, links_idx, envs_idx=None):
         """World-frame force at the link origin for the NEXT tick's two substeps, then cleared (abd/misc.py:655-715,
