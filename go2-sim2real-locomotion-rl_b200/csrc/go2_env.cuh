@@ -206,11 +206,24 @@ G2_HDN float reward_term(int id, const Go2Model& m, const EnvConfig& cfg, const 
                 v3 v = link_vel_world(p, l);
                 float fz = p.lpos[l].z;
                 if (cfg.has_terrain) fz = fz - terrain_height(m, p.lpos[l].x, p.lpos[l].y);  // go2_env_stair.py:1745-1750
+                else if (cfg.tm_on && cfg.tm_variant) fz = fz - e.ground_h;  // go2_env_terrain.py:1355: above the ground under the BASE
                 float he = cfg.feet_height_target - fz;
                 s += (e.fc[i] ? 0.0f : 1.0f) * (he * he) * sqrtf(v.x * v.x + v.y * v.y);
             }
             float mv = sqrtf(e.cmd[0] * e.cmd[0] + e.cmd[1] * e.cmd[1]) > 0.1f ? 1.0f : 0.0f;
             return s * mv;
+        }
+        case R_STUMBLE: {  // go2_env_terrain.py:1380-1394: contact force on the non-foot links above a threshold
+            float s = 0.0f;
+            for (int l = 0; l < NLINK; ++l) {
+                bool foot = false;
+                for (int i = 0; i < 4; ++i) foot = foot || (cfg.has_foot_tracking && cfg.foot_link[i] == l);
+                if (foot) continue;
+                v3 f = p.cforce[l];
+                float d = sqrtf(f.x * f.x + f.y * f.y + f.z * f.z) - cfg.stumble_threshold;
+                s += d > 0.0f ? d : 0.0f;
+            }
+            return cfg.has_foot_tracking ? s : 0.0f;
         }
         case R_JOINT_TRACKING: {
             float s = 0.0f;
@@ -720,6 +733,7 @@ G2_HDN void env_post(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
             pr[k++] = go[0]; pr[k++] = go[1]; pr[k++] = go[2];
             pr[k++] = F32(B_CUR_PUSH)[b * 3]; pr[k++] = F32(B_CUR_PUSH)[b * 3 + 1]; pr[k++] = F32(B_CUR_PUSH)[b * 3 + 2];
             pr[k++] = cfg.max_delay > 0 ? (float)I32(B_DELAY)[b] / (float)cfg.max_delay : 0.0f;
+            if (cfg.tm_variant && k < cfg.num_priv) pr[k++] = cfg.tm_on ? e.ground_h : 0.0f;  // go2_env_terrain.py:1139-1141
             if (cfg.kind == ENV_STAIR)
                 stair_priv_tail(m, cfg, pr, k, e.terrain_row, G2_LIDAR_ON(cfg) ? lid_pos : e.base_pos, G2_LIDAR_ON(cfg) ? lid_q : e.base_quat, rst);
         }

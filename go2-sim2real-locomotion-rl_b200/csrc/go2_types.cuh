@@ -90,6 +90,8 @@ enum RewardId {
     R_CROUCH_TARGET, R_NO_FALL, R_Y_STABILITY, R_CROUCH_PROGRESS, R_CROUCH_SPEED,
     // stair
     R_ORIENTATION_ROLL_ONLY, R_FORWARD_PROGRESS,
+    // go2_env_terrain.py
+    R_STUMBLE,
     R_COUNT
 };
 
@@ -149,6 +151,8 @@ struct EnvConfig {
     // random spawn points, reset when the base wanders too far from its spawn point, base-height reward relative to the bilinearly
     // interpolated ground height (computed in double like the reference's numpy code: spacing / origin kept in double)
     int tm_on;
+    int tm_variant;       // 1 = go2_env_terrain.py: ground height in the privileged obs, foot clearance above the ground under the base
+    float stumble_threshold;
     float tm_max_wander, tm_safe_half_x, tm_safe_half_y, tm_spawn_offset;
     double tm_hs, tm_ox, tm_oy;
 };

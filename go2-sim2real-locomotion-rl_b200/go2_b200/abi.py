@@ -36,6 +36,7 @@ REWARD_IDS = {
             "jump_impulse", "jump_apex", "xy_stability", "orientation", "no_shake", "crouch", "crouch_2", "ground_penalty",
             "crouch_target", "no_fall", "y_stability", "crouch_progress", "crouch_speed",
             "orientation_roll_only", "forward_progress",
+            "stumble",
         ]
     )
 }
@@ -91,7 +92,7 @@ class EnvConfig(C.Structure):
         ("actor_lx", _f * MAX_ACTOR_SCAN), ("actor_ly", _f * MAX_ACTOR_SCAN), ("critic_lx", _f * MAX_CRITIC_SCAN), ("critic_ly", _f * MAX_CRITIC_SCAN),
         ("lidar_noise_std", _f), ("lidar_dropout", _f), ("lidar_blackout", _f), ("lidar_latency", _f), ("lidar_voffset_std", _f),
         ("lidar_clip", _f), ("lidar_scale", _f),
-        ("tm_on", _i), ("tm_max_wander", _f), ("tm_safe_half_x", _f), ("tm_safe_half_y", _f), ("tm_spawn_offset", _f),
+        ("tm_on", _i), ("tm_variant", _i), ("stumble_threshold", _f), ("tm_max_wander", _f), ("tm_safe_half_x", _f), ("tm_safe_half_y", _f), ("tm_spawn_offset", _f),
         ("tm_hs", C.c_double), ("tm_ox", C.c_double), ("tm_oy", C.c_double),
     ]
 

@@ -971,6 +971,22 @@ class Go2EnvWalkTerrain(Go2EnvWalk):
             self._ground_height = torch.zeros(self.num_envs, device=self.device)
 
 
+class Go2EnvTerrain(Go2EnvWalkTerrain):
+    """examples/locomotion/go2_env_terrain.py: the height-map walk env plus the ground height under the base as one more privileged-obs
+    entry (:1139-1141), foot clearance measured above that ground height (:1355-1363), the `stumble` reward (contact force on
+    non-foot links above `stumble_threshold`, :1380-1394) and `terrain_row_mean` in the episode log."""
+
+    def _fill_flavour(self, c):
+        super()._fill_flavour(c)
+        c.tm_variant = 1
+        c.stumble_threshold = float(self.reward_cfg.get("stumble_threshold", 5.0))
+
+    def _after_resets(self, stats):
+        super()._after_resets(stats)
+        if self.terrain.enabled and int(round(float(stats[abi.STATS_RESETS]))) > 0 and "episode" in self.extras:
+            self.extras["episode"]["terrain_row_mean"] = 0.0  # heightmap mode: every env is on tile row 0
+
+
 class Go2EnvBaseFlavour(_Go2EnvBase):
     """Genesis stock Go2 env used by the crouch / jump scripts (go2_env_base.py): 12-dim action, 1-step
     latency through last_actions, solver-side PD, reset BEFORE rewards, 45-d obs, no privileged obs."""

@@ -104,7 +104,7 @@ def pre_state(env, kind):
     # dof_pos / dof_vel (from qpos / qvel), episode sums (running float32 sums of o_rew_terms)
     s = dict(qpos=r.get_qpos(), qvel=r.get_qvel(), qacc_ws=qws, warm=warm, cache_pair=ids, cache_n=nrm,
              commands=env.commands.numpy().copy(), ep_len=env.episode_length_buf.numpy().copy())
-    if kind in ("walk", "stair", "stair_lidar", "walk_terrain"):
+    if kind in ("walk", "stair", "stair_lidar", "walk_terrain", "terrain_env"):
         s.update(hist_idx=np.array(env._action_history_write_idx), delay=env._delay_steps.numpy().copy(),
                  air_time=env._feet_air_time.numpy().copy(), foot_contact=env._foot_contact.numpy().copy(),
                  kp_factors=env._kp_factors.numpy().copy(), kd_factors=env._kd_factors.numpy().copy(), motor_strength=env._motor_strength.numpy().copy(),
@@ -116,7 +116,7 @@ def pre_state(env, kind):
             s.update(push_force=env._push_stored_force.numpy().copy(), push_remain=env._push_remaining.numpy().copy(), push_counter=np.array(env._push_counter))
     if kind in ("stair", "stair_lidar"):
         s.update(terrain_row=env._env_terrain_row.numpy().astype(np.int32), last_x=env._last_base_pos_x.numpy().copy())
-    if kind == "walk_terrain":
+    if kind in ("walk_terrain", "terrain_env"):
         s.update(spawn_pos=env.terrain._env_spawn_pos.numpy().copy())
     if kind == "stair_lidar":
         s.update(actor_scan=env._actor_scan_buf.numpy().copy(), lidar_noise_level=np.array(float(env._lidar_noise_level)))
@@ -202,7 +202,7 @@ def draws_of_tick(env, kind, calls, done, ep_len_pre, A):
             row[ridx, abi.RP_DELAY] = r
         rr = by.pop("reset_idx", [])  # init z, roll, pitch in call order (go2_env_walk.py:1190-1203)
         i = 0
-        if "init_pos_z_range" in env.env_cfg and not (kind == "walk_terrain" and env.terrain.enabled):  # (not drawn on a terrain)
+        if "init_pos_z_range" in env.env_cfg and not (kind in ("walk_terrain", "terrain_env") and env.terrain.enabled):  # (not drawn on a terrain)
             row[ridx, abi.RP_INIT_Z] = rr[i][1]; i += 1
         if "init_euler_range" in env.env_cfg:
             row[ridx, abi.RP_ROLL] = rr[i][1]; row[ridx, abi.RP_PITCH] = rr[i + 1][1]; i += 2
@@ -227,7 +227,7 @@ def outputs(env, obs, rew, done, extras, kind, terms):
     # the state after the tick (qpos, qvel, commands, ep_len, DR buffers ...) is the NEXT tick's pre-state (`final_*` after the last)
     o = dict(o_obs=obs.numpy().copy(), o_rew=rew.numpy().copy(), o_reset=done.numpy().astype(np.uint8), o_timeout=extras["time_outs"].numpy().copy(),
              o_ncon=r.get_solver_stats()[:, 0].copy(), o_rew_terms=terms)
-    if kind in ("walk", "stair", "stair_lidar", "walk_terrain"):
+    if kind in ("walk", "stair", "stair_lidar", "walk_terrain", "terrain_env"):
         pr = extras["observations"]["critic"].numpy()
         assert np.array_equal(pr[:, :env.num_obs], o["o_obs"])
         o.update(o_priv_tail=pr[:, env.num_obs:].copy(), o_foot_contact=env._foot_contact.numpy().copy())
@@ -383,6 +383,16 @@ def walk_terrain_cfgs():
     return env_cfg, obs_cfg, reward_cfg, command_cfg
 
 
+def terrain_env_cfgs():
+    """go2_env_terrain.py has no train script in the tree: the height-map cfg above with what the class adds switched on - one more
+    privileged-obs entry (ground height), the stumble reward (low threshold so that it fires) and the foot rewards it relies on."""
+    env_cfg, obs_cfg, reward_cfg, command_cfg = walk_terrain_cfgs()
+    obs_cfg["num_privileged_obs"] = obs_cfg["num_privileged_obs"] + 1
+    reward_cfg["reward_scales"]["stumble"] = -0.05
+    reward_cfg["stumble_threshold"] = 1.0
+    return env_cfg, obs_cfg, reward_cfg, command_cfg
+
+
 def base_allrew_cfgs():
     """go2_train_crouch.get_cfgs() with EVERY reward term of go2_env_base.py switched on (the shipped scripts use 6-10 of the 20;
     logs/go2-crouch/cfgs.pkl names crouch_2 / y_stability / crouch_speed but lacks the termination keys the final env class
@@ -416,7 +426,10 @@ def main():
     import go2_env_Omni_kplearn_varied_terrain as go2_env_wt
     import terrain_manager  # noqa: F401  (the env imports it inside its ctor)
 
+    import go2_env_terrain
+
     jobs = {
+        "terrain_env_c1": lambda: (go2_env_terrain.Go2Env, go2_env_terrain, terrain_env_cfgs(), "terrain_env", 16, 300, 0.6, 616, 16),
         "walk_terrain_c1": lambda: (go2_env_wt.Go2Env, go2_env_wt, walk_terrain_cfgs(), "walk_terrain", 16, 300, 0.5, 515, 16),
         "stair_lidar_c1": lambda: (go2_env_stair_lidar.Go2Env, go2_env_stair_lidar, stair_lidar_cfgs(), "stair_lidar", 16, 300, 0.5, 909, 16),
         "walk_c1": lambda: (go2_env_walk.Go2Env, go2_env_walk, walk_cfgs(), "walk", 32, 1000, 0.5, 1234, 16),

@@ -31,7 +31,7 @@ FAST_EXTRA = lambda n: max(2, n // 2000)  # noqa: E731
 # obs, critic scan in the privileged obs, the kept scan) differ in 1 of 4,800 env-ticks
 # stair: 4.9 % of the env-ticks (hostemu) sit on rounded step-edge contacts whose MPR output is discontinuous at rounding level
 # (test_oracle_contact_output_is_discontinuous_at_rounding_level); every bit-exact output still matches on all of them
-CASES = [("walk_c1", "walk", 0), ("walk_hard", "walk", 0), ("base_allrew", "base", 0), ("stair_c1", "stair", 400), ("stair_lidar_c1", "stair_lidar", 420), ("walk_terrain_c1", "walk_terrain", 240)]
+CASES = [("walk_c1", "walk", 0), ("walk_hard", "walk", 0), ("base_allrew", "base", 0), ("stair_c1", "stair", 400), ("stair_lidar_c1", "stair_lidar", 420), ("walk_terrain_c1", "walk_terrain", 240), ("terrain_env_c1", "terrain_env", 240)]
 EXACT_AFTER = ["kp_factors", "kd_factors", "motor_strength", "grav_off", "delay", "commands", "ep_len"]
 
 
@@ -55,7 +55,7 @@ def _run(name, kind, backend, hostemu_lib, stride=1):
             for k in EXACT_AFTER:
                 if k in g:
                     ex[k] = (np_(b[k]).reshape(pre(g, k, t + 1).shape), pre(g, k, t + 1))
-            if kind in ("walk", "stair", "stair_lidar", "walk_terrain"):
+            if kind in ("walk", "stair", "stair_lidar", "walk_terrain", "terrain_env"):
                 ex["foot_contact"] = (np_(env._foot_contact), g["o_foot_contact"][t])
                 if "push_force" in g:
                     ex["push_force"] = (np_(b["push_force"]), pre(g, "push_force", t + 1))
@@ -65,7 +65,7 @@ def _run(name, kind, backend, hostemu_lib, stride=1):
                 ex["g_mass"] = (np.float32(gv["mass_shift"][0]), np.float32(pre(g, "g_mass", t + 1)))
                 ex["g_com"] = (np.asarray(gv["com_shift"], np.float32), pre(g, "g_com", t + 1))
                 ex["g_counter"] = (np.float32(gv["reset_counter"]), np.float32(pre(g, "g_counter", t + 1)))
-            if kind == "walk_terrain":
+            if kind in ("walk_terrain", "terrain_env"):
                 ex["spawn_pos_xy"] = (np_(b["spawn_pos"])[:, :2], pre(g, "spawn_pos", t + 1)[:, :2])  # (u * 2 - 1) * half: exact in f32
             if kind == "stair_lidar":  # the scan kept for the next tick's "latency" replay (noise branches decided by replayed uniforms)
                 fl_scan = (np_(b["actor_scan"]), pre(g, "actor_scan", t + 1))
@@ -79,7 +79,7 @@ def _run(name, kind, backend, hostemu_lib, stride=1):
             same = np_(done).astype(np.uint8) == g["o_reset"][t]
             fl = {"obs": (np_(obs), g["o_obs"][t]), "rew": (np_(rew), g["o_rew"][t]), "rew_terms": (np_(env.reward_terms), g["o_rew_terms"][t]),
                   "qpos": (np_(b["qpos"]), pre(g, "qpos", t + 1)), "qvel": (np_(b["qvel"]), pre(g, "qvel", t + 1))}
-            if kind in ("walk", "stair", "stair_lidar", "walk_terrain"):
+            if kind in ("walk", "stair", "stair_lidar", "walk_terrain", "terrain_env"):
                 fl["priv"] = (np_(extras["observations"]["critic"])[:, env.num_obs:], g["o_priv_tail"][t])
                 fl["air_time"] = (np_(b["air_time"]), pre(g, "air_time", t + 1))
             if kind == "stair_lidar":
@@ -99,6 +99,16 @@ def _run(name, kind, backend, hostemu_lib, stride=1):
     return bad_exact, bad_float, worst, T * B // stride
 
 
+def _drop_force_derived(bad_exact, bad_float, max_outside):
+    """On the terrain fixtures (the ones with a float budget: contacts on prism edges, where MPR's output is discontinuous at rounding
+    level) an env-tick that is already counted outside the float band has different contact forces, so its foot-contact flag - the
+    3 N threshold on those forces - may differ too.  Such a flag mismatch belongs to the same counted env-tick; anything else stays exact."""
+    if max_outside == 0:
+        return bad_exact
+    out = {(t, e) for _, t, e in bad_float}
+    return [m for m in bad_exact if not (m[2] == "foot_contact" and all((m[1], e) in out for e in m[3]))]
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("name,kind,max_outside", CASES)
 def test_teacher_forced_fast_math_build(name, kind, max_outside, hostemu_lib):
@@ -114,6 +124,7 @@ def test_teacher_forced_with_replayed_draws(name, kind, max_outside, backend, ho
     stride = 4 if (backend == "hostemu" and name == "walk_c1") else 1  # keep the CPU suite short; the GPU run checks every tick
     bad_exact, bad_float, worst, n = _run(name, kind, backend, hostemu_lib, stride)
     print(f"\n[{name}/{backend}] {n} env-ticks, worst float error = {worst[0]:.3f} x band at {worst[1]}, outside: {bad_float[:20]}")
+    bad_exact = _drop_force_derived(bad_exact, bad_float, max_outside)
     assert not bad_exact, f"bit-exact outputs differ (fixture, tick, buffer, envs): {bad_exact[:10]}"
     assert len(bad_float) <= max_outside, f"{len(bad_float)} env-ticks outside |d| <= {ATOL} + {RTOL}|x|: {bad_float[:20]}; worst {worst}"
 

@@ -61,12 +61,13 @@ def test_dropin_modules_of_the_terrain_variant(hostemu_lib):
     sys.path.insert(0, os.path.join(ROOT, "go2-sim2real-locomotion-rl_b200/dropin"))
     try:
         import go2_env_Omni_kplearn_varied_terrain as mod
+        import go2_env_terrain as mod2
         import terrain_manager as tm
     finally:
         sys.path.pop(0)
-    from go2_b200.envs import Go2EnvWalkTerrain, TerrainManager
+    from go2_b200.envs import Go2EnvTerrain, Go2EnvWalkTerrain, TerrainManager
 
-    assert mod.Go2Env is Go2EnvWalkTerrain and tm.TerrainManager is TerrainManager
+    assert mod.Go2Env is Go2EnvWalkTerrain and mod2.Go2Env is Go2EnvTerrain and tm.TerrainManager is TerrainManager
     with pytest.raises(NotImplementedError):
         TerrainManager({"enabled": True, "subterrain_types": [["flat_terrain"]]}, 4)
     assert not TerrainManager({}, 4).enabled
