@@ -618,38 +618,52 @@ G2_HDN void detect_collisions(const Go2Model& m, Phys& p, float fric_ground, flo
         else if (k < 64) ov1 |= bit;
         else ov2 |= bit;
     }
-    int ip = 0;
-    for (int r = 0; r < m.n_run; ++r) {
-        const int end = m.run_end[r], k = m.run_lp[r];
-        const uint32_t w = k < 32 ? ov0 : (k < 64 ? ov1 : ov2);
-        if (!((w >> (k & 31)) & 1u)) { ip = end; continue; }
-      for (; ip < end; ++ip) {
-        int a = m.pair_a[ip], b = m.pair_b[ip];
-        const float mu = (a == 0 || b == 0) ? mu_gr : mu_rr;
-        v3 dc = p.g_c[a] - p.g_c[b], hs = p.g_h[a] + p.g_h[b];
-        if (!(fabsf(dc.x) < hs.x && fabsf(dc.y) < hs.y && fabsf(dc.z) < hs.z)) continue;
-        if (m.terrain_on && (a == 0 || b == 0)) {  // geom 0 is the terrain: no normal cache, own narrow phase
-            terrain_contacts(m, p, a == 0 ? b : a, mu);
-            continue;
+    // The sweep only COLLECTS the pairs whose boxes overlap (up to NCAND at a time); the narrow phase then runs on "the k-th
+    // candidate of every lane" together.  Inside the sweep the lanes of a warp met their candidates at different pair indices and
+    // ran MPR 8 lanes wide (ncu: support / mpr / mtmul at 7.5-9.3 active lanes); same candidates in the same order per env, so
+    // every contact is unchanged.
+    constexpr int NCAND = 16;
+    int ip = 0, r = 0;
+    while (r < m.n_run) {
+        uint16_t cand[NCAND];
+        int nc = 0;
+        while (r < m.n_run && nc < NCAND) {
+            const int end = m.run_end[r], k = m.run_lp[r];
+            const uint32_t w = k < 32 ? ov0 : (k < 64 ? ov1 : ov2);
+            if (!((w >> (k & 31)) & 1u)) { ip = end; ++r; continue; }
+            for (; ip < end && nc < NCAND; ++ip) {
+                const int a = m.pair_a[ip], b = m.pair_b[ip];
+                v3 dc = p.g_c[a] - p.g_c[b], hs = p.g_h[a] + p.g_h[b];
+                if (fabsf(dc.x) < hs.x && fabsf(dc.y) < hs.y && fabsf(dc.z) < hs.z) cand[nc++] = (uint16_t)ip;
+            }
+            if (ip >= end) ++r;
         }
-        // narrow phase wants the lower geom type first (sphere < cylinder < box)
-        int ga = a, gb = b;
-        if (m.g_type[ga] > m.g_type[gb]) { ga = b; gb = a; }
-        v3 nws = mk3(0, 0, 0);
-        bool have = false;
-        for (int k = 0; k < p.n_cache; ++k)
-            if (p.cache_pair[k] == ip) { nws = p.cache_n[k]; have = true; }
-        v3 n;
-        if (pair_contacts(m, p, ga, gb, nws, have, mu, n)) {
-            if (n_new < MAX_CPAIRS) {
-                new_pair[n_new] = ip;
-                new_n[n_new] = n;
-                n_new++;
-            } else {
-                p.err |= ERR_CPAIR_OVERFLOW;
+        for (int ic = 0; ic < nc; ++ic) {
+            const int jp = cand[ic];
+            int a = m.pair_a[jp], b = m.pair_b[jp];
+            const float mu = (a == 0 || b == 0) ? mu_gr : mu_rr;
+            if (m.terrain_on && (a == 0 || b == 0)) {  // geom 0 is the terrain: no normal cache, own narrow phase
+                terrain_contacts(m, p, a == 0 ? b : a, mu);
+                continue;
+            }
+            // narrow phase wants the lower geom type first (sphere < cylinder < box)
+            int ga = a, gb = b;
+            if (m.g_type[ga] > m.g_type[gb]) { ga = b; gb = a; }
+            v3 nws = mk3(0, 0, 0);
+            bool have = false;
+            for (int k = 0; k < p.n_cache; ++k)
+                if (p.cache_pair[k] == jp) { nws = p.cache_n[k]; have = true; }
+            v3 n;
+            if (pair_contacts(m, p, ga, gb, nws, have, mu, n)) {
+                if (n_new < MAX_CPAIRS) {
+                    new_pair[n_new] = jp;
+                    new_n[n_new] = n;
+                    n_new++;
+                } else {
+                    p.err |= ERR_CPAIR_OVERFLOW;
+                }
             }
         }
-      }
     }
     p.n_cache = n_new;
     for (int k = 0; k < n_new; ++k) {

@@ -825,7 +825,7 @@ G2_HD void store_phys(const Buffers& bf, int b, const Phys& p) {
 // Block-wide phase alignment: the kernel is far larger than the SM's instruction cache (ncu: icc hit rate 59 %,
 // no-instruction stalls ~ long-scoreboard stalls), so the warps of a block are kept in the same phase and share
 // their instruction fetches.  `valid` = this thread owns an env (threads past B only take part in the barriers).
-#ifdef __CUDA_ARCH__
+#if defined(__CUDA_ARCH__) && !defined(G2_WARP_ASYNC)
 #define G2_PHASE_SYNC() __syncthreads()
 #else
 #define G2_PHASE_SYNC()
