@@ -32,9 +32,10 @@ for p in (ROOT, PKG):
 METRIC = "env-steps/sec (whole box) Go2 walk"
 UNIT = "env-steps/s"
 BYTES_PER_ENV_STEP = {"walk": 1952, "stair": 2272, "crouch": 948, "jump": 948,  # algorithmic bytes per env-step
-                      "stair_lidar": 2384}  # stair + 15 obs words - 17 privileged-obs words + the kept actor scan read and written (30)
+                      "stair_lidar": 2384,  # stair + 15 obs words - 17 privileged-obs words + the kept actor scan read and written (30)
+                      "stair_info": 2044}   # stair + 4 obs words - 69 privileged-obs words + the kept stair info read and written (8)
 NCU_JSON = os.path.join(ROOT, "profiles", "step_kernel_ncu.json")  # written from the ncu capture of the CURRENT build (profiles/tools/ncu_to_json.py)
-DEFAULT_ENVS = {"walk": 65536, "stair": 8192, "stair_lidar": 8192, "crouch": 4096, "jump": 4096}
+DEFAULT_ENVS = {"walk": 65536, "stair": 8192, "stair_lidar": 8192, "stair_info": 8192, "crouch": 4096, "jump": 4096}
 
 
 def load_cfgs(name):
@@ -43,7 +44,7 @@ def load_cfgs(name):
 
 
 def workload_config(workload, B):
-    dr = ", full DR + curriculum" if workload in ("walk", "stair", "stair_lidar") else ""
+    dr = ", full DR + curriculum" if workload in ("walk", "stair", "stair_lidar", "stair_info") else ""
     return {"workload": f"Go2 {workload} (go2_train_{workload} cfg{dr}), {B} envs/GPU, random actions on device", "envs_per_gpu": B,
             "l2": "per-tick state (2 KB/env) + thread-local working set of the resident threads exceed the 126 MB L2 at 65,536 envs: inputs larger than L2, no flush"}
 
@@ -189,9 +190,9 @@ def make_policy(env, dev, seed=188000):
 def bench_env(args, workload, B, rank, world, dev, headline):
     import torch
     import torch.distributed as dist
-    from go2_b200.envs import Go2EnvBaseFlavour, Go2EnvStair, Go2EnvStairLidar, Go2EnvWalk
+    from go2_b200.envs import Go2EnvBaseFlavour, Go2EnvStair, Go2EnvStairInfo, Go2EnvStairLidar, Go2EnvWalk
 
-    env_cls = {"walk": Go2EnvWalk, "stair": Go2EnvStair, "stair_lidar": Go2EnvStairLidar}.get(workload, Go2EnvBaseFlavour)
+    env_cls = {"walk": Go2EnvWalk, "stair": Go2EnvStair, "stair_lidar": Go2EnvStairLidar, "stair_info": Go2EnvStairInfo}.get(workload, Go2EnvBaseFlavour)
     env = env_cls(B, *load_cfgs(workload), device=dev, seed=1, env_offset=rank * B, total_envs=world * B,
                   stats_sync_interval=args.stats_interval, lib_path=os.environ.get("GO2_B200_LIB") or None, fast_math=(args.math == "fast"), sync_ranks=args.rank_sync)
     env.reset()
@@ -382,7 +383,7 @@ def run_gpu(args):
         dist.init_process_group("nccl", device_id=dev)
     jobs = [(args.workload, args.envs or DEFAULT_ENVS[args.workload], True)]
     if args.all_configs:
-        jobs += [("walk", 4096, False), ("stair", 8192, False), ("stair_lidar", 8192, False), ("crouch", 4096, False), ("jump", 4096, False)]
+        jobs += [("walk", 4096, False), ("stair", 8192, False), ("stair_lidar", 8192, False), ("stair_info", 8192, False), ("crouch", 4096, False), ("jump", 4096, False)]
     for workload, B, headline in jobs:
         res = bench_env(args, workload, B, rank, world, dev, headline)
         keys = ["ms_total", "ms_e2e", "kern_avg", "kern_med"] + [k for k in ("ms_pol", "ms_fused", "ms_roll", "ms_k_fused", "ms_k_torch", "ms_fresh", "ms_precise") if res.get(k) is not None]
@@ -424,7 +425,7 @@ def main():
     ap.add_argument("--policy", action="store_true", help="policy / rollout legs for the non-headline configs too")
     ap.add_argument("--all-configs", action="store_true", help="one more JSON line per other BASELINE config (walk 4,096, stair 8,192, crouch / jump 4,096)")
     ap.add_argument("--stats-interval", type=int, default=24, help="ticks between asynchronous reads of the device-side episode statistics (1 = blocking read every tick)")
-    ap.add_argument("--workload", default="walk", choices=["walk", "stair", "stair_lidar", "crouch", "jump"],
+    ap.add_argument("--workload", default="walk", choices=["walk", "stair", "stair_lidar", "stair_info", "crouch", "jump"],
                     help="walk = headline metric; stair = BASELINE configs[2]; crouch / jump = configs[3] (base env)")
     args = ap.parse_args()
     if args.impl == "reference":

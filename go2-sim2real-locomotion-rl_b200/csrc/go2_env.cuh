@@ -225,6 +225,14 @@ G2_HDN float reward_term(int id, const Go2Model& m, const EnvConfig& cfg, const 
             }
             return cfg.has_foot_tracking ? s : 0.0f;
         }
+        case R_BODY_CONTACT: {  // go2_env_stair_lidar_2.py:1865-1880: how many of the listed links carry a contact force above the threshold
+            float s = 0.0f;
+            for (int i = 0; i < cfg.n_body_contact; ++i) {
+                v3 f = p.cforce[cfg.body_contact_link[i]];
+                s += sqrtf(f.x * f.x + f.y * f.y + f.z * f.z) > cfg.body_contact_threshold ? 1.0f : 0.0f;
+            }
+            return s;
+        }
         case R_JOINT_TRACKING: {
             float s = 0.0f;
             for (int i = 0; i < NHINGE; ++i) { float d = e.target[i] - e.dof_pos[i]; s += d * d; }
@@ -566,6 +574,64 @@ G2_HDN void lidar_update(const Go2Model& m, const EnvConfig& cfg, const StepPara
     }
 }
 
+// ---- 4-value stair info (go2_env_stair_lidar_2.py, cfg.lidar_on == 2) -------------------------------------------------------------
+// Edge detector (:848-906 _compute_edge_detection): terrain heights at si_n_samples points on the forward axis of a base at `pos`
+// with yaw of `q`; the first consecutive pair whose heights differ by more than the threshold gives the distance (midpoint of the
+// pair) and the direction (sign of the change); (max range, 0) if there is none or no terrain.
+G2_HD void stair_edge(const Go2Model& m, const EnvConfig& cfg, v3 pos, q4 q, float& dist, float& dir) {
+    dist = cfg.si_max_range;
+    dir = 0.0f;
+    if (!cfg.has_terrain) return;
+    float cy, sy;
+    yaw_cs(q, cy, sy);
+    float hprev = 0.0f;
+    bool found = false;
+    for (int i = 0; i < cfg.si_n_samples; ++i) {
+        const float lx = cfg.si_edge_x[i];
+        const float h = terrain_height(m, pos.x + cy * lx, pos.y + sy * lx);
+        if (i > 0 && !found) {
+            const float dh = h - hprev;
+            if (fabsf(dh) > cfg.si_threshold) {
+                found = true;
+                dist = cfg.si_edge_mid[i - 1];
+                dir = dh > 0.0f ? 1.0f : (dh < 0.0f ? -1.0f : 0.0f);
+            }
+        }
+        hprev = h;
+    }
+}
+// Noisy actor copy of the tick (:908-975 _update_stair_info), in the reference's order: Gaussian noise on the edge distance (then
+// clamp to [0, max range]), on the riser height, on the tread depth; direction flip; latency (edge distance and direction of the
+// previous tick's info); blackout (edge -> max range, direction -> 0); scale.  B_ACTOR_SCAN holds the previous info on entry.
+G2_HDN void stair_info_update(const Go2Model& m, const EnvConfig& cfg, const StepParams& sp, const Buffers& bf, int b, const Rng& rng,
+                              const float* rp, v3 pos, q4 q, int row) {
+    float* buf = F32(B_ACTOR_SCAN) + (size_t)b * 4;
+    const float lvl = sp.lidar_noise_level;
+    const bool on = lvl > 0.0f;
+    float edge, dir;
+    stair_edge(m, cfg, pos, q, edge, dir);
+    float h = cfg.si_row_height[row], d = cfg.si_row_depth[row];
+    u4 rn = rng4(rng, SLOT_LIDAR), ru = rng4(rng, SLOT_LIDAR + 8);
+    float z[4];
+    boxmuller(rn.a, rn.b, z[0], z[1]);
+    boxmuller(rn.c, rn.d, z[2], z[3]);
+    if (rp) { z[0] = rp[RP_LIDAR_N]; z[1] = rp[RP_LIDAR_N + 1]; z[2] = rp[RP_LIDAR_N + 2]; }
+    const float uf = rp ? rp[RP_LIDAR_U] : u01(ru.a), ul = rp ? rp[RP_LIDAR_U + 1] : u01(ru.b), ub = rp ? rp[RP_LIDAR_U + 2] : u01(ru.c);
+    if (on && cfg.si_edge_noise_std > 0.0f) edge = clampf(edge + (z[0] * cfg.si_edge_noise_std) * lvl, 0.0f, cfg.si_max_range);
+    if (on && cfg.si_height_noise_std > 0.0f) h = h + (z[1] * cfg.si_height_noise_std) * lvl;
+    if (on && cfg.si_depth_noise_std > 0.0f) d = d + (z[2] * cfg.si_depth_noise_std) * lvl;
+    if (on && cfg.si_flip_prob > 0.0f && uf < cfg.si_flip_prob * lvl) dir = -dir;
+    if (on && cfg.si_latency_prob > 0.0f && ul < cfg.si_latency_prob * lvl) {
+        edge = buf[0] / cfg.si_scale[0];
+        dir = buf[3] / cfg.si_scale[3];
+    }
+    if (on && cfg.si_blackout_prob > 0.0f && ub < cfg.si_blackout_prob * lvl) { edge = cfg.si_max_range; dir = 0.0f; }
+    buf[0] = edge * cfg.si_scale[0];
+    buf[1] = h * cfg.si_scale[1];
+    buf[2] = d * cfg.si_scale[2];
+    buf[3] = dir * cfg.si_scale[3];
+}
+
 // tail of the stair env's privileged obs (go2_env_stair.py:1466-1484): terrain difficulty of the env's row, then the body-frame
 // height scan around the base - or, in the lidar variant, the clean critic lidar scan of the tick's pre-reset pose (zeros for an
 // env reset in this tick, go2_env_stair_lidar.py:1004-1015,1689-1692); `k` = first index of the tail (num_obs + 55)
@@ -576,6 +642,17 @@ G2_HD void stair_priv_tail(const Go2Model& m, const EnvConfig& cfg, float* pr, i
     }
     float cy, sy;
     yaw_cs(q, cy, sy);
+    if (G2_LIDAR_ON(cfg) && cfg.lidar_on == 2) {  // clean stair info of the tick's pre-reset pose (go2_env_stair_lidar_2.py:930-934,1621-1624)
+        if (k + 4 <= cfg.num_priv) {
+            float edge = 0.0f, dir = 0.0f;
+            if (!was_reset) stair_edge(m, cfg, base_pos, q, edge, dir);
+            pr[k++] = was_reset ? 0.0f : edge * cfg.si_scale[0];
+            pr[k++] = was_reset ? 0.0f : cfg.si_row_height[terrain_row] * cfg.si_scale[1];
+            pr[k++] = was_reset ? 0.0f : cfg.si_row_depth[terrain_row] * cfg.si_scale[2];
+            pr[k++] = was_reset ? 0.0f : dir * cfg.si_scale[3];
+        }
+        return;
+    }
     if (G2_LIDAR_ON(cfg)) {
         if (cfg.n_critic_scan > 0 && k + cfg.n_critic_scan <= cfg.num_priv)
             for (int i = 0; i < cfg.n_critic_scan; ++i)
@@ -626,7 +703,10 @@ G2_HDN void env_post(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
                 e.fc[i] = fabsf(p.cforce[cfg.foot_link[i]].z) > cfg.foot_contact_threshold ? 1 : 0;
             }
         }
-        if (G2_LIDAR_ON(cfg)) lidar_update(m, cfg, sp, bf, b, rng, rp, e.base_pos, e.base_quat);
+        if (G2_LIDAR_ON(cfg)) {
+            if (cfg.lidar_on == 2) stair_info_update(m, cfg, sp, bf, b, rng, rp, e.base_pos, e.base_quat, e.terrain_row);
+            else lidar_update(m, cfg, sp, bf, b, rng, rp, e.base_pos, e.base_quat);
+        }
         if (cfg.tm_on) {  // go2_env_Omni_kplearn_varied_terrain.py: _ground_height[:] = terrain.get_height_at_robot(base_pos[:, :2])
             e.ground_h = ground_height_bilinear(m, cfg, e.base_pos.x, e.base_pos.y);
             F32(B_GROUND_H)[b] = e.ground_h;
@@ -843,6 +923,11 @@ __device__ unsigned long long g2_phase_clk[8];
 #define G2_CLK(i)
 #define G2_CLK_INIT()
 #endif
+#if defined(__CUDA_ARCH__) && defined(G2_FINE_SYNC2_ON)
+#define G2_FINE_SYNC2() __syncthreads()
+#else
+#define G2_FINE_SYNC2()
+#endif
 G2_HD void t_env_step(const Go2Model& m, const EnvConfig& cfg, const StepParams& sp, const Buffers& bf, const float* actions, int b,
                       bool valid, Phys& p, EnvLocal& e, EnvStepOut& out) {
     G2_CLK_INIT();
@@ -858,8 +943,9 @@ G2_HD void t_env_step(const Go2Model& m, const EnvConfig& cfg, const StepParams&
         const float* gl0 = U8(B_FK_FRESH)[b] ? gl : F32(B_GLOBALS) + (sp.parity ^ 1) * GLOBALS_LEN;
         kinematics(m, gl0, p);
         velocities(m, p);
-        env_pre(m, cfg, sp, bf, actions, b, p, e, out);
     }
+    G2_FINE_SYNC2();
+    if (valid) env_pre(m, cfg, sp, bf, actions, b, p, e, out);
     if (sp.do_physics) {
         for (int s = 0; s < 2; ++s) {
             G2_PHASE_SYNC();
@@ -875,8 +961,9 @@ G2_HD void t_env_step(const Go2Model& m, const EnvConfig& cfg, const StepParams&
             solve_constraints(m, p, valid);  // block-synchronous iteration loop: every thread calls it
             G2_PHASE_SYNC();
             G2_CLK(4);
+            if (valid) integrate(m, p);
+            G2_FINE_SYNC2();
             if (valid) {
-                integrate(m, p);
                 kinematics(m, gl, p);
                 velocities(m, p);
             }

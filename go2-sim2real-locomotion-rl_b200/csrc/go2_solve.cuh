@@ -822,6 +822,12 @@ constexpr int MAX_RANK1 = 6;  // more flips than this in one Newton iteration ->
 #define G2_BLOCK_ANY(x) (x)
 #endif
 
+#if defined(__CUDA_ARCH__) && defined(G2_FINE_SYNC_ON)
+#define G2_FINE_SYNC() __syncthreads()
+#else
+#define G2_FINE_SYNC()
+#endif
+
 // Newton solve for the constrained acceleration; writes p.acc, warm start, per-link contact forces.
 // Called by EVERY thread of the block (`valid` = the thread owns an env) because the iteration loop contains
 // block barriers.  Trip 0 of the loop is the initial evaluation (active set, Hessian factorisation, gradient);
@@ -847,50 +853,52 @@ G2_HDN void solve_constraints_t(const Go2Model& m, Phys& p, bool valid) {
     const float tol = m.meaninertia * (float)NV * SOLVER_TOL;
     for (int it = 0; it <= SOLVER_ITERS; ++it) {
         if (!G2_BLOCK_ANY(active)) break;
-        if (active) {
-            bool first = it == 0;
-            if (!first) {
-                n_newton++;
-                float alpha = linesearch<AR>(m, p, search, Ma, mv);
-                if (fabsf(alpha) < EPSF) {
-                    active = false;
-                } else {
-                    G2_UNROLL
-                    for (int d = 0; d < NV; ++d) {
-                        qacc[d] += search[d] * alpha;
-                        Ma[d] += mv[d] * alpha;
-                    }
-                    for (int c = 0; c < n; ++c) p.Jaref[c] += p.jv[c] * alpha;
-                }
-            }
-            if (active) {
-                unsigned long long flist;
-                int nfl;
-                update_constraint<AR>(p, qacc, Ma, qfc, flist, nfl);
-                // active-set changes: k-th flip of every lane together, oldest first (row order, like the reference)
-                bool refactor = first || nfl > MAX_RANK1;
-                for (int k = nfl - 1; k >= 0 && !refactor; --k) {
-                    int c = (int)((flist >> (8 * k)) & 0xffull);
-                    float sg = p.act[c] ? 1.0f : -1.0f;
-                    if (!(AR ? hessian_rank1_a(p, c, sg) : hessian_rank1(p, Hs, c, sg))) refactor = true;
-                }
-                if (refactor) {
-                    if (AR) hessian_factor_a(p);
-                    else hessian_factor(p, Hs);
-                }
-                if (AR) update_gradient_a(p, Ma, qfc, grad, Mgrad);
-                else update_gradient(p, Hs, Ma, qfc, grad, Mgrad);
-                if (!first) {
-                    float gn = 0.0f;
-                    G2_UNROLL
-                    for (int d = 0; d < NV; ++d) gn += grad[d] * grad[d];
-                    gn = sqrtf(gn);
-                    bool improved = gn > tol && (p.prev_cost - p.cost) > tol;
-                    if (!improved || it == SOLVER_ITERS) active = false;
-                }
+        const bool first = it == 0;
+        if (active && !first) {
+            n_newton++;
+            float alpha = linesearch<AR>(m, p, search, Ma, mv);
+            if (fabsf(alpha) < EPSF) {
+                active = false;
+            } else {
                 G2_UNROLL
-                for (int d = 0; d < NV; ++d) search[d] = -Mgrad[d];
+                for (int d = 0; d < NV; ++d) {
+                    qacc[d] += search[d] * alpha;
+                    Ma[d] += mv[d] * alpha;
+                }
+                for (int c = 0; c < n; ++c) p.Jaref[c] += p.jv[c] * alpha;
             }
+        }
+        G2_FINE_SYNC();
+        if (active) {
+            unsigned long long flist;
+            int nfl;
+            update_constraint<AR>(p, qacc, Ma, qfc, flist, nfl);
+            // active-set changes: k-th flip of every lane together, oldest first (row order, like the reference)
+            bool refactor = first || nfl > MAX_RANK1;
+            for (int k = nfl - 1; k >= 0 && !refactor; --k) {
+                int c = (int)((flist >> (8 * k)) & 0xffull);
+                float sg = p.act[c] ? 1.0f : -1.0f;
+                if (!(AR ? hessian_rank1_a(p, c, sg) : hessian_rank1(p, Hs, c, sg))) refactor = true;
+            }
+            if (refactor) {
+                if (AR) hessian_factor_a(p);
+                else hessian_factor(p, Hs);
+            }
+        }
+        G2_FINE_SYNC();
+        if (active) {
+            if (AR) update_gradient_a(p, Ma, qfc, grad, Mgrad);
+            else update_gradient(p, Hs, Ma, qfc, grad, Mgrad);
+            if (!first) {
+                float gn = 0.0f;
+                G2_UNROLL
+                for (int d = 0; d < NV; ++d) gn += grad[d] * grad[d];
+                gn = sqrtf(gn);
+                bool improved = gn > tol && (p.prev_cost - p.cost) > tol;
+                if (!improved || it == SOLVER_ITERS) active = false;
+            }
+            G2_UNROLL
+            for (int d = 0; d < NV; ++d) search[d] = -Mgrad[d];
         }
     }
     if (!valid) return;

@@ -33,6 +33,7 @@ constexpr int HIST_MAX = 4;      // action-delay ring slots (max_delay_steps + 1
 constexpr int NOBS_MAX = 49;     // proprioceptive obs entries (the lidar variant appends up to MAX_ACTOR_SCAN heights after them)
 constexpr int MAX_ACTOR_SCAN = 32, MAX_CRITIC_SCAN = 96;  // simulated-lidar height grids (go2_env_stair_lidar.py LidarScanConfig)
 constexpr int SCAN_MAX = 77;
+constexpr int MAX_EDGE_SAMPLES = 32;  // forward samples of the stair-info edge detector (go2_env_stair_lidar_2.py: 14)
 constexpr int MAX_TERRAIN_ROWS = 16;  // difficulty rows of the stair terrain (go2_env_stair.py:61)
 constexpr int TERRAIN_MIP_SHIFT = 2;      // 4 x 4 cells per block of the max-height level
 constexpr int TERRAIN_PAIR_CONTACTS = 5;  // n_contacts_per_pair (collider.py)
@@ -92,6 +93,8 @@ enum RewardId {
     R_ORIENTATION_ROLL_ONLY, R_FORWARD_PROGRESS,
     // go2_env_terrain.py
     R_STUMBLE,
+    // go2_env_stair_lidar_2.py
+    R_BODY_CONTACT,
     R_COUNT
 };
 
@@ -147,6 +150,18 @@ struct EnvConfig {
     int lidar_on, n_actor_scan, n_critic_scan;
     float actor_lx[MAX_ACTOR_SCAN], actor_ly[MAX_ACTOR_SCAN], critic_lx[MAX_CRITIC_SCAN], critic_ly[MAX_CRITIC_SCAN];
     float lidar_noise_std, lidar_dropout, lidar_blackout, lidar_latency, lidar_voffset_std, lidar_clip, lidar_scale;
+    // lidar_on == 2: the 4-value stair info of examples/locomotion/go2_env_stair_lidar_2.py instead of the height grids
+    // (n_actor_scan = n_critic_scan = 4): [distance to the next height change along the forward axis, riser height of the env's
+    // terrain row, tread depth of the row, direction +1 up / -1 down / 0 none] x si_scale, noisy copy in the obs, clean copy at the
+    // tail of the privileged obs.  si_edge_x = forward sample points, si_edge_mid = midpoints between consecutive samples.
+    int si_n_samples;
+    float si_edge_x[MAX_EDGE_SAMPLES], si_edge_mid[MAX_EDGE_SAMPLES];
+    float si_max_range, si_threshold, si_scale[4];
+    float si_edge_noise_std, si_height_noise_std, si_depth_noise_std, si_flip_prob, si_blackout_prob, si_latency_prob;
+    float si_row_height[MAX_TERRAIN_ROWS], si_row_depth[MAX_TERRAIN_ROWS];
+    // body_contact reward of the same file (:1865-1880): number of the listed links whose net contact force exceeds the threshold
+    int n_body_contact, body_contact_link[4];
+    float body_contact_threshold;
     // walk env on a custom heightmap (examples/locomotion/go2_env_Omni_kplearn_varied_terrain.py + terrain_manager.py, heightmap mode):
     // random spawn points, reset when the base wanders too far from its spawn point, base-height reward relative to the bilinearly
     // interpolated ground height (computed in double like the reference's numpy code: spacing / origin kept in double)

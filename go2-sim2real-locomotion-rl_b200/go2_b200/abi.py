@@ -15,6 +15,7 @@ NLINK, NV, NQ, NHINGE = 13, 18, 19, 12
 MAX_REW, NOBS_MAX, MAX_CPAIRS = 32, 49, 24
 MAX_TERRAIN_ROWS = 16
 MAX_ACTOR_SCAN, MAX_CRITIC_SCAN = 32, 96
+MAX_EDGE_SAMPLES = 32
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CUDA_LIB_PATH = os.path.join(_HERE, "libgo2_b200.so")
@@ -37,6 +38,7 @@ REWARD_IDS = {
             "crouch_target", "no_fall", "y_stability", "crouch_progress", "crouch_speed",
             "orientation_roll_only", "forward_progress",
             "stumble",
+            "body_contact",
         ]
     )
 }
@@ -92,6 +94,11 @@ class EnvConfig(C.Structure):
         ("actor_lx", _f * MAX_ACTOR_SCAN), ("actor_ly", _f * MAX_ACTOR_SCAN), ("critic_lx", _f * MAX_CRITIC_SCAN), ("critic_ly", _f * MAX_CRITIC_SCAN),
         ("lidar_noise_std", _f), ("lidar_dropout", _f), ("lidar_blackout", _f), ("lidar_latency", _f), ("lidar_voffset_std", _f),
         ("lidar_clip", _f), ("lidar_scale", _f),
+        ("si_n_samples", _i), ("si_edge_x", _f * MAX_EDGE_SAMPLES), ("si_edge_mid", _f * MAX_EDGE_SAMPLES),
+        ("si_max_range", _f), ("si_threshold", _f), ("si_scale", _f * 4),
+        ("si_edge_noise_std", _f), ("si_height_noise_std", _f), ("si_depth_noise_std", _f), ("si_flip_prob", _f), ("si_blackout_prob", _f),
+        ("si_latency_prob", _f), ("si_row_height", _f * MAX_TERRAIN_ROWS), ("si_row_depth", _f * MAX_TERRAIN_ROWS),
+        ("n_body_contact", _i), ("body_contact_link", _i * 4), ("body_contact_threshold", _f),
         ("tm_on", _i), ("tm_variant", _i), ("stumble_threshold", _f), ("tm_max_wander", _f), ("tm_safe_half_x", _f), ("tm_safe_half_y", _f), ("tm_spawn_offset", _f),
         ("tm_hs", C.c_double), ("tm_ox", C.c_double), ("tm_oy", C.c_double),
     ]

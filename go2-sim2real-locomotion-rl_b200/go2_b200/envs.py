@@ -726,6 +726,12 @@ class Go2EnvStair(Go2EnvWalk):
 
     KIND = abi.ENV_STAIR
 
+    @staticmethod
+    def _build_terrain(terrain_cfg):
+        from .terrain import build_stair_terrain
+
+        return build_stair_terrain(terrain_cfg)
+
     def _fill_flavour(self, c):
         e = self.env_cfg
         self._terrain_cfg = e.get("terrain", None)
@@ -738,9 +744,7 @@ class Go2EnvStair(Go2EnvWalk):
             self._dr_terrain_gate = float(dr.get("terrain_gate", 0.85))
         c.lin_vel_z_deadzone = float(self.reward_cfg.get("lin_vel_z_deadzone", 0.0))
         if self._use_terrain:
-            from .terrain import build_stair_terrain
-
-            self._hf, self._terrain_info = build_stair_terrain(self._terrain_cfg)
+            self._hf, self._terrain_info = self._build_terrain(self._terrain_cfg)
             ti = self._terrain_info
             self._num_terrain_rows = ti["num_difficulty_rows"]
             if self._num_terrain_rows > abi.MAX_TERRAIN_ROWS:
@@ -892,6 +896,112 @@ class Go2EnvStairLidar(Go2EnvStair):
     def _flavour_params(self, sp):
         super()._flavour_params(sp)
         sp.lidar_noise_level = float(self._lidar_noise_level)
+
+
+class StairInfoConfig:
+    """Parameters of the 4-value stair info (go2_env_stair_lidar_2.py:331-391, same cfg keys and attribute names): `edge_detection`
+    (`max_range`, `threshold`, `num_samples`), the four observation scales and the `noise` model."""
+
+    NUM_STAIR_INFO = 4
+
+    def __init__(self, cfg: dict, device=None):
+        self.device = device
+        self.enabled = bool(cfg.get("enabled", True))
+        if not self.enabled:
+            return
+        ed = cfg.get("edge_detection", {})
+        self.edge_max_range = float(ed.get("max_range", 0.27))
+        self.edge_threshold = float(ed.get("threshold", 0.02))
+        self.edge_num_samples = int(ed.get("num_samples", 14))
+        self.edge_dist_scale = float(cfg.get("edge_dist_scale", 1.0 / 0.27))
+        self.height_scale = float(cfg.get("height_scale", 1.0 / 0.20))
+        self.depth_scale = float(cfg.get("depth_scale", 1.0 / 0.30))
+        self.direction_scale = float(cfg.get("direction_scale", 1.0))
+        n = cfg.get("noise", {})
+        self.edge_noise_std = float(n.get("edge_noise_std", 0.04))
+        self.height_noise_std = float(n.get("height_noise_std", 0.01))
+        self.depth_noise_std = float(n.get("depth_noise_std", 0.01))
+        self.direction_flip_prob = float(n.get("direction_flip_prob", 0.03))
+        self.full_blackout_prob = float(n.get("full_blackout_prob", 0.05))
+        self.latency_prob = float(n.get("latency_prob", 0.10))
+        self.edge_sample_x = torch.linspace(0.0, self.edge_max_range, self.edge_num_samples)  # f32 rounding of the reference
+
+
+class Go2EnvStairInfo(Go2EnvStair):
+    """Stair env with the 4-value stair info of examples/locomotion/go2_env_stair_lidar_2.py instead of height grids:
+    [distance to the next height change on the forward axis, riser height and tread depth of the env's terrain row, direction] with
+    a sim-to-real noise model appended to the ACTOR obs (49 + 4 = 53), the clean copy at the tail of the privileged obs (113); rows
+    with individual tread depths (`build_stair_terrain` :83-203, numpy-global shuffle) and the `body_contact` reward (:1865-1880)."""
+
+    @staticmethod
+    def _build_terrain(terrain_cfg):
+        from .terrain import build_stair_terrain_variable_depth
+
+        return build_stair_terrain_variable_depth(terrain_cfg)
+
+    def _fill_flavour(self, c):
+        super()._fill_flavour(c)
+        self._stair_cfg = S = StairInfoConfig(self.env_cfg.get("stair_info", {}), self.device)
+        self._stair_noise_level = 0.0
+        e = self.env_cfg
+        self._has_body_contact_penalty = float(self.reward_cfg.get("reward_scales", {}).get("body_contact", 0.0)) != 0.0
+        self._body_contact_link_indices = []
+        if self._has_body_contact_penalty:  # _init_body_contact_tracking :1098-1137: unknown names are skipped
+            names = [l["name"] for l in self._model["links"]]
+            self._body_contact_link_indices = [names.index(n) for n in e.get("body_contact_names", ["FR_thigh", "FL_thigh"]) if n in names]
+            self._body_contact_threshold = float(e.get("body_contact_threshold", 1.0))
+            if len(self._body_contact_link_indices) > 4:
+                raise ValueError("at most 4 body_contact_names are supported")
+            if not self._body_contact_link_indices:
+                self._has_body_contact_penalty = False
+            c.n_body_contact = len(self._body_contact_link_indices)
+            for i, l in enumerate(self._body_contact_link_indices):
+                c.body_contact_link[i] = l
+            c.body_contact_threshold = self._body_contact_threshold if self._has_body_contact_penalty else 0.0
+        if not S.enabled:
+            return
+        if S.edge_num_samples > abi.MAX_EDGE_SAMPLES:
+            raise ValueError(f"at most {abi.MAX_EDGE_SAMPLES} edge-detection samples are supported")
+        if self.num_obs != 33 + self.num_actions + S.NUM_STAIR_INFO:
+            raise ValueError(f"obs_cfg['num_obs'] = {self.num_obs} != 33 + {self.num_actions} actions + 4 stair-info values")
+        c.lidar_on, c.n_actor_scan, c.n_critic_scan = 2, S.NUM_STAIR_INFO, S.NUM_STAIR_INFO
+        c.si_n_samples = S.edge_num_samples
+        sx = S.edge_sample_x
+        mid = (sx[:-1] + sx[1:]) / 2
+        for i in range(S.edge_num_samples):
+            c.si_edge_x[i] = float(sx[i])
+        for i in range(S.edge_num_samples - 1):
+            c.si_edge_mid[i] = float(mid[i])
+        c.si_max_range, c.si_threshold = S.edge_max_range, S.edge_threshold
+        for i, v in enumerate((S.edge_dist_scale, S.height_scale, S.depth_scale, S.direction_scale)):
+            c.si_scale[i] = v
+        c.si_edge_noise_std, c.si_height_noise_std, c.si_depth_noise_std = S.edge_noise_std, S.height_noise_std, S.depth_noise_std
+        c.si_flip_prob, c.si_blackout_prob, c.si_latency_prob = S.direction_flip_prob, S.full_blackout_prob, S.latency_prob
+        if self._use_terrain:
+            self._terrain_step_depths = self._terrain_info["step_depths_m"]
+            hs, ds = self._terrain_step_heights, self._terrain_step_depths
+        else:
+            hs, ds = [0.0], [0.25]
+        for r in range(len(hs)):
+            c.si_row_height[r], c.si_row_depth[r] = float(np.float32(hs[r])), float(np.float32(ds[r]))
+
+    def _after_bind(self):
+        super()._after_bind()
+        self._stair_info_buf = self.core.buf["actor_scan"]  # [B, 4]; the previous tick's info until the next tick overwrites it
+
+    @property
+    def _stair_info_clean(self):
+        k = self.num_obs + 56
+        return self.privileged_obs_buf[:, k:k + 4]
+
+    def _curriculum_extras(self, cur, lvl, dr_lvl):
+        super()._curriculum_extras(cur, lvl, dr_lvl)
+        self._stair_noise_level = float(dr_lvl)  # go2_env_stair_lidar_2.py:1188
+        cur["stair_noise_level"] = float(dr_lvl)
+
+    def _flavour_params(self, sp):
+        super()._flavour_params(sp)
+        sp.lidar_noise_level = float(self._stair_noise_level)
 
 
 class TerrainManager:

@@ -16,9 +16,9 @@ import os
 import torch
 
 from . import checkpoint
-from .envs import Go2EnvBaseFlavour, Go2EnvStair, Go2EnvStairLidar, Go2EnvWalk
+from .envs import Go2EnvBaseFlavour, Go2EnvStair, Go2EnvStairInfo, Go2EnvStairLidar, Go2EnvWalk
 
-_ENVS = {"walk": Go2EnvWalk, "stair": Go2EnvStair, "stair_lidar": Go2EnvStairLidar, "crouch": Go2EnvBaseFlavour, "jump": Go2EnvBaseFlavour}
+_ENVS = {"walk": Go2EnvWalk, "stair": Go2EnvStair, "stair_lidar": Go2EnvStairLidar, "stair_info": Go2EnvStairInfo, "crouch": Go2EnvBaseFlavour, "jump": Go2EnvBaseFlavour}
 
 # training-time randomisation the eval scripts strip from the cfg before building the env (go2_eval_walk.py:519-545)
 _EVAL_STRIP = (

@@ -15,6 +15,7 @@ SCRIPTS = {
     "walk": os.path.join(FINAL, "go2_train_walk.py"), "stair": os.path.join(FINAL, "go2_train_stair.py"),
     "crouch": os.path.join(FINAL, "go2_train_crouch.py"), "jump": os.path.join(FINAL, "go2_train_jump.py"),
     "stair_lidar": os.path.join(REF, "examples/locomotion/go2_stair_train_lidar.py"),
+    "stair_info": os.path.join(REF, "examples/locomotion/go2_stair_train_lidar_2.py"),
     "go2": os.path.join(REF, "examples/locomotion/go2_train.py"),  # Genesis' stock example (go2_env.py == final/go2_env_base.py)
 }
 

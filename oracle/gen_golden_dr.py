@@ -60,7 +60,7 @@ class DrawLog:
         def w(*a, **k):
             r = fn(*a, **k)
             caller = sys._getframe(1).f_code.co_name
-            if caller in ("_update_actor_lidar_scan", "_sample_spawn_heightmap"):
+            if caller in ("_update_actor_lidar_scan", "_update_stair_info", "_sample_spawn_heightmap"):
                 self.calls.append((caller, kind, r.clone()))
             return r
 
@@ -104,7 +104,7 @@ def pre_state(env, kind):
     # dof_pos / dof_vel (from qpos / qvel), episode sums (running float32 sums of o_rew_terms)
     s = dict(qpos=r.get_qpos(), qvel=r.get_qvel(), qacc_ws=qws, warm=warm, cache_pair=ids, cache_n=nrm,
              commands=env.commands.numpy().copy(), ep_len=env.episode_length_buf.numpy().copy())
-    if kind in ("walk", "stair", "stair_lidar", "walk_terrain", "terrain_env"):
+    if kind in ("walk", "stair", "stair_lidar", "stair_info", "walk_terrain", "terrain_env"):
         s.update(hist_idx=np.array(env._action_history_write_idx), delay=env._delay_steps.numpy().copy(),
                  air_time=env._feet_air_time.numpy().copy(), foot_contact=env._foot_contact.numpy().copy(),
                  kp_factors=env._kp_factors.numpy().copy(), kd_factors=env._kd_factors.numpy().copy(), motor_strength=env._motor_strength.numpy().copy(),
@@ -114,12 +114,14 @@ def pre_state(env, kind):
                  g_counter=np.array(int(env._global_dr_reset_counter)))
         if env.push_force_range_hard is not None:
             s.update(push_force=env._push_stored_force.numpy().copy(), push_remain=env._push_remaining.numpy().copy(), push_counter=np.array(env._push_counter))
-    if kind in ("stair", "stair_lidar"):
+    if kind in ("stair", "stair_lidar", "stair_info"):
         s.update(terrain_row=env._env_terrain_row.numpy().astype(np.int32), last_x=env._last_base_pos_x.numpy().copy())
     if kind in ("walk_terrain", "terrain_env"):
         s.update(spawn_pos=env.terrain._env_spawn_pos.numpy().copy())
     if kind == "stair_lidar":
         s.update(actor_scan=env._actor_scan_buf.numpy().copy(), lidar_noise_level=np.array(float(env._lidar_noise_level)))
+    if kind == "stair_info":
+        s.update(actor_scan=env._stair_info_buf.numpy().copy(), lidar_noise_level=np.array(float(env._stair_noise_level)))
     return s
 
 
@@ -155,6 +157,12 @@ def draws_of_tick(env, kind, calls, done, ep_len_pre, A):
         row[:, abi.RP_LIDAR_V] = lid[2][1][:, 0]
         row[:, abi.RP_LIDAR_V + 1] = lid[3][1]
         row[:, abi.RP_LIDAR_V + 2] = lid[4][1]
+    sti = by.pop("_update_stair_info", [])
+    if sti:  # order of go2_env_stair_lidar_2.py:939-967: edge / height / depth normals, flip / latency / blackout uniforms
+        assert [k for k, _ in sti] == ["n", "n", "n", "u", "u", "u"], [k for k, _ in sti]
+        for j in range(3):
+            row[:, abi.RP_LIDAR_N + j] = sti[j][1]
+            row[:, abi.RP_LIDAR_U + j] = sti[3 + j][1]
     for _, r in by.pop("_add_obs_noise", []):
         assert r.shape == (B, env.num_obs)
         # entries with zero noise std never reach the obs; dropping their draws keeps the fixture small
@@ -212,7 +220,7 @@ def draws_of_tick(env, kind, calls, done, ep_len_pre, A):
             assert [k for k, _ in sp_] == ["u", "u"]
             row[ridx, abi.RP_SPAWN] = sp_[0][1]
             row[ridx, abi.RP_SPAWN + 1] = sp_[1][1]
-        if kind in ("stair", "stair_lidar"):
+        if kind in ("stair", "stair_lidar", "stair_info"):
             by.pop("_assign_terrain_rows", None)
             row[ridx, abi.RP_ROW] = env._env_terrain_row.numpy()[ridx]
         for k in ("_randomize_friction", "_randomize_mass", "_randomize_leg_mass"):
@@ -227,7 +235,7 @@ def outputs(env, obs, rew, done, extras, kind, terms):
     # the state after the tick (qpos, qvel, commands, ep_len, DR buffers ...) is the NEXT tick's pre-state (`final_*` after the last)
     o = dict(o_obs=obs.numpy().copy(), o_rew=rew.numpy().copy(), o_reset=done.numpy().astype(np.uint8), o_timeout=extras["time_outs"].numpy().copy(),
              o_ncon=r.get_solver_stats()[:, 0].copy(), o_rew_terms=terms)
-    if kind in ("walk", "stair", "stair_lidar", "walk_terrain", "terrain_env"):
+    if kind in ("walk", "stair", "stair_lidar", "stair_info", "walk_terrain", "terrain_env"):
         pr = extras["observations"]["critic"].numpy()
         assert np.array_equal(pr[:, :env.num_obs], o["o_obs"])
         o.update(o_priv_tail=pr[:, env.num_obs:].copy(), o_foot_contact=env._foot_contact.numpy().copy())
@@ -292,6 +300,8 @@ def run(env_cls, module, cfgs, kind, B, T, act_std, seed, act_dim, after_build=N
     torch.manual_seed(1)
     with contextlib.redirect_stdout(io.StringIO()):
         env = env_cls(B, *cfgs)
+    if hasattr(env, "_terrain_step_depths"):  # stair-info variant: the rows' tread depths come out of np.random.shuffle; kept with the cfg
+        cfgs_json[0]["terrain"]["step_depths_m"] = [float(d) for d in env._terrain_step_depths]
     log = DrawLog(module)
     try:
         env.reset()
@@ -364,6 +374,18 @@ def stair_lidar_cfgs():
     return env_cfg, obs_cfg, reward_cfg, command_cfg
 
 
+def stair_info_cfgs():
+    """examples/locomotion/go2_stair_train_lidar_2.get_cfgs() (actor obs 49 + 4 stair-info values, rows with individual tread depths,
+    body_contact reward with a low threshold so that it fires) past the DR gate, with the fixture horizon of stair_c1."""
+    env_cfg, obs_cfg, reward_cfg, command_cfg = load_funcs(os.path.join(REF, "examples/locomotion/go2_stair_train_lidar_2.py"), ["get_cfgs"]).get_cfgs()
+    env_cfg.update(episode_length_s=3.0, resampling_time_s=1.0)
+    env_cfg["curriculum"]["level_init"] = 0.95
+    env_cfg["terrain"]["flat_before_m"] = 0.5   # spawn 0.25 m before the first riser: the edge detector (range 0.27 m) sees it from the start
+    env_cfg["body_contact_names"] = ["FR_thigh", "FL_thigh", "RR_calf"]  # a foot link as well, so that the count is non-zero in the fixture
+    np.random.seed(21)  # the env ctor shuffles the rows' tread depths with numpy's global generator
+    return env_cfg, obs_cfg, reward_cfg, command_cfg
+
+
 def walk_terrain_cfgs():
     """examples/locomotion/go2_train_Omni_kplearn_varied_terrain.get_cfgs() (heightmap mode: left half flat, right half smoothed random
     bumps drawn with numpy's global RNG, seeded here), short episodes, and a small map so that the boundary reset occurs."""
@@ -427,8 +449,10 @@ def main():
     import terrain_manager  # noqa: F401  (the env imports it inside its ctor)
 
     import go2_env_terrain
+    import go2_env_stair_lidar_2
 
     jobs = {
+        "stair_info_c1": lambda: (go2_env_stair_lidar_2.Go2Env, go2_env_stair_lidar_2, stair_info_cfgs(), "stair_info", 16, 300, 0.5, 2121, 16),
         "terrain_env_c1": lambda: (go2_env_terrain.Go2Env, go2_env_terrain, terrain_env_cfgs(), "terrain_env", 16, 300, 0.6, 616, 16),
         "walk_terrain_c1": lambda: (go2_env_wt.Go2Env, go2_env_wt, walk_terrain_cfgs(), "walk_terrain", 16, 300, 0.5, 515, 16),
         "stair_lidar_c1": lambda: (go2_env_stair_lidar.Go2Env, go2_env_stair_lidar, stair_lidar_cfgs(), "stair_lidar", 16, 300, 0.5, 909, 16),

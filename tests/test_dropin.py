@@ -96,7 +96,8 @@ def test_walk_module_as_the_train_script_uses_it(backend, dropin):
 
 @pytest.mark.parametrize("backend", BACKENDS)
 @pytest.mark.parametrize("module,cfg,n_obs,n_act,n_priv", [("go2_env_stair", "stair", 49, 16, 182), ("go2_env_stair6", "stair", 49, 16, 182), ("go2_env_Omni_walk_16output", "walk", 49, 16, 104), ("go2_env_stair4_lidar", "stair_lidar", 64, 16, 165),
-                                                           ("go2_env_stair_lidar", "stair_lidar", 64, 16, 165), ("go2_env_base", "crouch", 45, 12, None), ("go2_env", "go2", 45, 12, None),
+                                                           ("go2_env_stair_lidar", "stair_lidar", 64, 16, 165), ("go2_env_stair_lidar_2", "stair_info", 53, 16, 113), ("go2_env_stair5_info", "stair_info", 53, 16, 113),
+                                                           ("go2_env_base", "crouch", 45, 12, None), ("go2_env", "go2", 45, 12, None),
                                                            ("go2_env_base", "jump", 45, 12, None)])
 def test_stair_and_base_modules(backend, dropin, module, cfg, n_obs, n_act, n_priv):
     gs = dropin

@@ -29,9 +29,12 @@ FAST_EXTRA = lambda n: max(2, n // 2000)  # noqa: E731
 # walk_terrain_c1 (walk env on a custom height map, smoothed +-8 cm bumps): 3.7 %, contacts on prism edges again
 # stair_lidar_c1 (go2_stair_train_lidar cfg: 20 cm risers, 25 cm treads): 7.5 % for the same reason; its lidar outputs (actor scan in the
 # obs, critic scan in the privileged obs, the kept scan) differ in 1 of 4,800 env-ticks
+# stair_info_c1 (go2_stair_train_lidar_2 cfg, spawn 0.25 m before the first 20 cm riser so that the edge detector fires from tick 0: the
+# robots spend the fixture ON the riser edges): 9.4 %, all of them qvel / qpos (the stair-info outputs - noisy copy in the obs, clean
+# copy in the privileged obs, the kept copy - are inside the band on all 4,800 env-ticks)
 # stair: 4.9 % of the env-ticks (hostemu) sit on rounded step-edge contacts whose MPR output is discontinuous at rounding level
 # (test_oracle_contact_output_is_discontinuous_at_rounding_level); every bit-exact output still matches on all of them
-CASES = [("walk_c1", "walk", 0), ("walk_hard", "walk", 0), ("base_allrew", "base", 0), ("stair_c1", "stair", 400), ("stair_lidar_c1", "stair_lidar", 420), ("walk_terrain_c1", "walk_terrain", 240), ("terrain_env_c1", "terrain_env", 240)]
+CASES = [("walk_c1", "walk", 0), ("walk_hard", "walk", 0), ("base_allrew", "base", 0), ("stair_c1", "stair", 400), ("stair_lidar_c1", "stair_lidar", 420), ("stair_info_c1", "stair_info", 480), ("walk_terrain_c1", "walk_terrain", 240), ("terrain_env_c1", "terrain_env", 240)]
 EXACT_AFTER = ["kp_factors", "kd_factors", "motor_strength", "grav_off", "delay", "commands", "ep_len"]
 
 
@@ -55,7 +58,7 @@ def _run(name, kind, backend, hostemu_lib, stride=1):
             for k in EXACT_AFTER:
                 if k in g:
                     ex[k] = (np_(b[k]).reshape(pre(g, k, t + 1).shape), pre(g, k, t + 1))
-            if kind in ("walk", "stair", "stair_lidar", "walk_terrain", "terrain_env"):
+            if kind in ("walk", "stair", "stair_lidar", "stair_info", "walk_terrain", "terrain_env"):
                 ex["foot_contact"] = (np_(env._foot_contact), g["o_foot_contact"][t])
                 if "push_force" in g:
                     ex["push_force"] = (np_(b["push_force"]), pre(g, "push_force", t + 1))
@@ -67,9 +70,9 @@ def _run(name, kind, backend, hostemu_lib, stride=1):
                 ex["g_counter"] = (np.float32(gv["reset_counter"]), np.float32(pre(g, "g_counter", t + 1)))
             if kind in ("walk_terrain", "terrain_env"):
                 ex["spawn_pos_xy"] = (np_(b["spawn_pos"])[:, :2], pre(g, "spawn_pos", t + 1)[:, :2])  # (u * 2 - 1) * half: exact in f32
-            if kind == "stair_lidar":  # the scan kept for the next tick's "latency" replay (noise branches decided by replayed uniforms)
+            if kind in ("stair_lidar", "stair_info"):  # the scan kept for the next tick's "latency" replay (noise branches decided by replayed uniforms)
                 fl_scan = (np_(b["actor_scan"]), pre(g, "actor_scan", t + 1))
-            if kind in ("stair", "stair_lidar"):
+            if kind in ("stair", "stair_lidar", "stair_info"):
                 ex["terrain_row"] = (np_(b["terrain_row"]).reshape(-1), pre(g, "terrain_row", t + 1))
             for k, (a, r) in ex.items():
                 if not np.array_equal(np.asarray(a), np.asarray(r)):
@@ -79,10 +82,10 @@ def _run(name, kind, backend, hostemu_lib, stride=1):
             same = np_(done).astype(np.uint8) == g["o_reset"][t]
             fl = {"obs": (np_(obs), g["o_obs"][t]), "rew": (np_(rew), g["o_rew"][t]), "rew_terms": (np_(env.reward_terms), g["o_rew_terms"][t]),
                   "qpos": (np_(b["qpos"]), pre(g, "qpos", t + 1)), "qvel": (np_(b["qvel"]), pre(g, "qvel", t + 1))}
-            if kind in ("walk", "stair", "stair_lidar", "walk_terrain", "terrain_env"):
+            if kind in ("walk", "stair", "stair_lidar", "stair_info", "walk_terrain", "terrain_env"):
                 fl["priv"] = (np_(extras["observations"]["critic"])[:, env.num_obs:], g["o_priv_tail"][t])
                 fl["air_time"] = (np_(b["air_time"]), pre(g, "air_time", t + 1))
-            if kind == "stair_lidar":
+            if kind in ("stair_lidar", "stair_info"):
                 fl["actor_scan"] = fl_scan
             out = np.zeros(B, bool)
             for k, (a, r) in fl.items():

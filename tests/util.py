@@ -20,9 +20,9 @@ def load_golden(name):
 
 
 def make_env(kind, cfgs, B, backend, hostemu_lib=None, **kw):
-    from go2_b200.envs import Go2EnvBaseFlavour, Go2EnvStair, Go2EnvStairLidar, Go2EnvTerrain, Go2EnvWalk, Go2EnvWalkTerrain
+    from go2_b200.envs import Go2EnvBaseFlavour, Go2EnvStair, Go2EnvStairInfo, Go2EnvStairLidar, Go2EnvTerrain, Go2EnvWalk, Go2EnvWalkTerrain
 
-    cls = {"walk": Go2EnvWalk, "stair": Go2EnvStair, "stair_lidar": Go2EnvStairLidar, "walk_terrain": Go2EnvWalkTerrain, "terrain_env": Go2EnvTerrain}.get(kind, Go2EnvBaseFlavour)
+    cls = {"walk": Go2EnvWalk, "stair": Go2EnvStair, "stair_lidar": Go2EnvStairLidar, "stair_info": Go2EnvStairInfo, "walk_terrain": Go2EnvWalkTerrain, "terrain_env": Go2EnvTerrain}.get(kind, Go2EnvBaseFlavour)
     cfgs = json.loads(json.dumps(cfgs))
     if backend == "hostemu":
         from hostemu_core import HostEmuCore
@@ -63,11 +63,11 @@ def force_state(env, g, t, kind):
     b["ep_len"].copy_(_t(env, g["ep_len"][t][:, None], torch.int32))
     if g["ep_sums"].shape[1] > 0:
         b["ep_sums"].copy_(_t(env, g["ep_sums"][t].T))
-    if kind in ("stair", "stair_lidar"):
+    if kind in ("stair", "stair_lidar", "stair_info"):
         b["terrain_row"].copy_(_t(env, g["terrain_row"][t][:, None], torch.int32))
         b["last_x"].copy_(_t(env, g["last_x"][t][:, None]))
         env._lock_terrain_rows = True
-    if kind in ("walk", "stair", "stair_lidar", "walk_terrain", "terrain_env"):
+    if kind in ("walk", "stair", "stair_lidar", "stair_info", "walk_terrain", "terrain_env"):
         b["hist"].copy_(_t(env, g["hist"][t].reshape(B, -1)))
         env._action_history_write_idx = int(g["hist_idx"][t])
         b["applied"].copy_(_t(env, g["applied"][t]))
@@ -149,7 +149,7 @@ def force_state_dr(env, g, t, kind, der):
     b["ep_len"].copy_(_t(env, g["ep_len"][t][:, None], torch.int32))
     if der.ep_sums.shape[1] > 0:
         b["ep_sums"].copy_(_t(env, der.ep_sums))
-    if kind in ("walk", "stair", "stair_lidar", "walk_terrain", "terrain_env"):
+    if kind in ("walk", "stair", "stair_lidar", "stair_info", "walk_terrain", "terrain_env"):
         b["hist"].copy_(_t(env, der.hist.reshape(B, -1)))
         env._action_history_write_idx = int(g["hist_idx"][t])
         b["delay"].copy_(_t(env, g["delay"][t][:, None], torch.int32))
@@ -185,7 +185,7 @@ def force_state_dr(env, g, t, kind, der):
         b["fk_fresh"].copy_(_t(env, (g["o_reset"][t - 1] if t > 0 else np.ones(B))[:, None], torch.uint8))
         env._cand_override = {"friction": float(pre(g, "g_friction", t + 1)), "mass": float(pre(g, "g_mass", t + 1)),
                               "com": [float(x) for x in pre(g, "g_com", t + 1)], "leg": [float(x) for x in pre(g, "g_leg", t + 1)]}
-    if kind in ("stair", "stair_lidar"):
+    if kind in ("stair", "stair_lidar", "stair_info"):
         b["terrain_row"].copy_(_t(env, g["terrain_row"][t][:, None], torch.int32))
         b["last_x"].copy_(_t(env, g["last_x"][t][:, None]))
     if kind in ("walk_terrain", "terrain_env"):
@@ -193,4 +193,7 @@ def force_state_dr(env, g, t, kind, der):
     if kind == "stair_lidar":
         b["actor_scan"].copy_(_t(env, g["actor_scan"][t]))
         env._lidar_noise_level = float(g["lidar_noise_level"][t])
+    if kind == "stair_info":
+        b["actor_scan"].copy_(_t(env, g["actor_scan"][t]))
+        env._stair_noise_level = float(g["lidar_noise_level"][t])
     env.replay_draws(g["replay"][t])
