@@ -122,7 +122,7 @@ G2_HD float terrain_height(const Go2Model& m, float x, float y) {
 // float32 height field, clipped to the field, result rounded to float32.  The model keeps the field in metres (field x vertical
 // scale, exact for the shipped vertical_scale = 1.0; the reference scales after interpolating).
 G2_HD float ground_height_bilinear(const Go2Model& m, const EnvConfig& cfg, float x, float y) {
-    if (!m.terrain_on) return 0.0f;
+    if (!m.terrain_on || cfg.tm_blind) return 0.0f;
     const int R = m.terrain_r, C = m.terrain_c;
     double lx = ((double)x - cfg.tm_ox) / cfg.tm_hs, ly = ((double)y - cfg.tm_oy) / cfg.tm_hs;
     lx = lx < 0.0 ? 0.0 : (lx > (double)(R - 2) ? (double)(R - 2) : lx);
@@ -358,8 +358,15 @@ G2_HDN void reset_env(const Go2Model& m, const EnvConfig& cfg, const StepParams&
         // standing height + offset (init_pos_z_range is not used on terrain); the spawn point is kept for the boundary check
         u4 rs = rng4(rng, SLOT_RESET + 13);
         float ux = rp ? rp[RP_SPAWN] : u01(rs.a), uy = rp ? rp[RP_SPAWN + 1] : u01(rs.b);
-        e.base_pos.x = cfg.tm_safe_half_x > 0.0f ? (ux * 2.0f - 1.0f) * cfg.tm_safe_half_x : 0.0f;
-        e.base_pos.y = cfg.tm_safe_half_y > 0.0f ? (uy * 2.0f - 1.0f) * cfg.tm_safe_half_y : 0.0f;
+        float cx = 0.0f, cy = 0.0f;
+        if (cfg.tm_grid_rows > 0) {  // _sample_spawn_grid (:308-335): uniform tile, its centre (float32 of a float64 sum) + the jitter
+            const int tr = rp ? (int)rp[RP_TILE] : (int)(rs.c % (uint32_t)cfg.tm_grid_rows);
+            const int tc = rp ? (int)rp[RP_TILE + 1] : (int)(rs.d % (uint32_t)cfg.tm_grid_cols);
+            cx = (float)(cfg.tm_ox + ((double)tr + 0.5) * cfg.tm_tile_x);
+            cy = (float)(cfg.tm_oy + ((double)tc + 0.5) * cfg.tm_tile_y);
+        }
+        e.base_pos.x = cfg.tm_safe_half_x > 0.0f ? add_nf(cx, mul_nf(ux * 2.0f - 1.0f, cfg.tm_safe_half_x)) : cx;  // torch: separate multiply and add
+        e.base_pos.y = cfg.tm_safe_half_y > 0.0f ? add_nf(cy, mul_nf(uy * 2.0f - 1.0f, cfg.tm_safe_half_y)) : cy;
         e.base_pos.z = ground_height_bilinear(m, cfg, e.base_pos.x, e.base_pos.y) + cfg.base_init_pos[2] + cfg.tm_spawn_offset;
         F32(B_SPAWN_POS)[b * 3] = e.base_pos.x; F32(B_SPAWN_POS)[b * 3 + 1] = e.base_pos.y; F32(B_SPAWN_POS)[b * 3 + 2] = e.base_pos.z;
     } else if (cfg.has_init_z) e.base_pos.z = rp ? rp[RP_INIT_Z] : urange(cfg.init_z_lo, cfg.init_z_hi, rq.a);

@@ -169,7 +169,12 @@ struct EnvConfig {
     int tm_variant;       // 1 = go2_env_terrain.py: ground height in the privileged obs, foot clearance above the ground under the base
     float stumble_threshold;
     float tm_max_wander, tm_safe_half_x, tm_safe_half_y, tm_spawn_offset;
+    // sub-terrain GRID mode of terrain_manager.py (tm_grid_rows > 0): a reset picks a random tile and spawns at its centre + a uniform
+    // jitter of +-tm_safe_half_x / y; tm_blind = 1: height queries return 0 (the reference's manager cannot read the height field of
+    // a Genesis-generated terrain, terrain_manager.py:236-262), collision still runs on the field
+    int tm_grid_rows, tm_grid_cols, tm_blind;
     double tm_hs, tm_ox, tm_oy;
+    double tm_tile_x, tm_tile_y;  // tile size in metres (grid mode)
 };
 
 // Per-step parameters: everything the reference keeps as host-side python scalars (curriculum-driven
@@ -217,7 +222,7 @@ constexpr int G_FRIC_GROUND = 0, G_FRIC_ROBOT = 1, G_MASS_SHIFT = 2, G_COM_SHIFT
 constexpr int RP_ACT_NOISE = 0, RP_OBS_NOISE = 12, RP_PUSH = 61 /* fx fy duration */, RP_CMD = 64, RP_KPF = 67, RP_KDF = 79, RP_MS = 91,
               RP_GO = 103, RP_DELAY = 106, RP_INIT_Z = 107, RP_ROLL = 108, RP_PITCH = 109, RP_CMD_RESET = 110, RP_ROW = 113, RP_KP = 114,
               RP_KD = 115, RP_LIDAR_N = 116 /* per-cell normals */, RP_LIDAR_U = 116 + MAX_ACTOR_SCAN /* per-cell uniforms */,
-              RP_LIDAR_V = 116 + 2 * MAX_ACTOR_SCAN /* offset normal, latency u, blackout u */, RP_SPAWN = RP_LIDAR_V + 3 /* spawn x, y uniforms */,
-              REPLAY_LEN = RP_SPAWN + 2;
+              RP_LIDAR_V = 116 + 2 * MAX_ACTOR_SCAN /* offset normal, latency u, blackout u */, RP_SPAWN = RP_LIDAR_V + 3 /* spawn x, y uniforms */, RP_TILE = RP_SPAWN + 2 /* grid mode: tile row, column */,
+              REPLAY_LEN = RP_TILE + 2;
 
 }  // namespace go2

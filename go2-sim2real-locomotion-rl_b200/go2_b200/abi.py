@@ -60,7 +60,8 @@ RP_ACT_NOISE, RP_OBS_NOISE, RP_PUSH, RP_CMD, RP_KPF, RP_KDF, RP_MS, RP_GO, RP_DE
 RP_INIT_Z, RP_ROLL, RP_PITCH, RP_CMD_RESET, RP_ROW, RP_KP, RP_KD = 107, 108, 109, 110, 113, 114, 115
 RP_LIDAR_N, RP_LIDAR_U, RP_LIDAR_V = 116, 116 + MAX_ACTOR_SCAN, 116 + 2 * MAX_ACTOR_SCAN  # lidar variant: cell normals, cell uniforms, (offset, latency, blackout)
 RP_SPAWN = RP_LIDAR_V + 3  # heightmap walk variant: spawn x, y uniforms
-REPLAY_LEN = RP_SPAWN + 2
+RP_TILE = RP_SPAWN + 2  # grid mode of the terrain manager: tile row, column
+REPLAY_LEN = RP_TILE + 2
 
 _i, _f, _u = C.c_int32, C.c_float, C.c_uint32
 
@@ -100,7 +101,8 @@ class EnvConfig(C.Structure):
         ("si_latency_prob", _f), ("si_row_height", _f * MAX_TERRAIN_ROWS), ("si_row_depth", _f * MAX_TERRAIN_ROWS),
         ("n_body_contact", _i), ("body_contact_link", _i * 4), ("body_contact_threshold", _f),
         ("tm_on", _i), ("tm_variant", _i), ("stumble_threshold", _f), ("tm_max_wander", _f), ("tm_safe_half_x", _f), ("tm_safe_half_y", _f), ("tm_spawn_offset", _f),
-        ("tm_hs", C.c_double), ("tm_ox", C.c_double), ("tm_oy", C.c_double),
+        ("tm_grid_rows", _i), ("tm_grid_cols", _i), ("tm_blind", _i),
+        ("tm_hs", C.c_double), ("tm_ox", C.c_double), ("tm_oy", C.c_double), ("tm_tile_x", C.c_double), ("tm_tile_y", C.c_double),
     ]
 
 

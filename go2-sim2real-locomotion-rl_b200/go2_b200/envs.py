@@ -1006,8 +1006,10 @@ class Go2EnvStairInfo(Go2EnvStair):
 
 class TerrainManager:
     """Host-side view of the terrain state of `Go2EnvWalkTerrain`, with the attribute / method names of the reference's
-    examples/locomotion/terrain_manager.py that the env and eval scripts touch.  Only the custom-heightmap mode is built (the
-    sub-terrain grid mode needs Genesis' procedural terrain generator)."""
+    examples/locomotion/terrain_manager.py that the env and eval scripts touch.  Both modes: a custom `height_field` (heightmap mode,
+    :63-98) and the sub-terrain GRID (`subterrain_types`, :104-133,179-214) - there the field is generated here by the restatement of
+    Genesis' terrain parser (`go2_b200.terrain.build_subterrain_grid`), and, like the reference's manager, which cannot read the
+    field of a Genesis-generated terrain (`post_build` :216-262 finds no attribute), every height query returns 0."""
 
     def __init__(self, terrain_cfg: dict, num_envs: int, device=None):
         self.cfg = terrain_cfg or {}
@@ -1016,12 +1018,32 @@ class TerrainManager:
         if not self.enabled:
             return
         self.use_custom_heightmap = self.cfg.get("height_field", None) is not None
-        if not self.use_custom_heightmap:
-            raise NotImplementedError("terrain: only the custom height_field mode is supported (subterrain grids need Genesis' terrain generator)")
         self.horizontal_scale = float(self.cfg.get("horizontal_scale", 0.25))
         self.vertical_scale = float(self.cfg.get("vertical_scale", 0.005))
         self.spawn_height_offset = float(self.cfg.get("spawn_height_offset", 0.05))
         self.boundary_margin = float(self.cfg.get("boundary_margin", 1.0))
+        self._env_spawn_pos = None  # bound to the device buffer by the env
+        if not self.use_custom_heightmap:
+            from .terrain import build_subterrain_grid
+
+            self.subterrain_types = [list(r) for r in self.cfg["subterrain_types"]]
+            self.n_rows, self.n_cols = len(self.subterrain_types), len(self.subterrain_types[0])
+            self.subterrain_size = tuple(self.cfg.get("subterrain_size", (8.0, 8.0)))
+            self.randomize = bool(self.cfg.get("randomize", True))
+            self.max_wander = min(self.subterrain_size) / 2.0 - self.boundary_margin
+            self._flat_row_indices = [r for r, row in enumerate(self.subterrain_types) if all(t == "flat_terrain" for t in row)]
+            self._terrain_size_x, self._terrain_size_y = self.n_rows * self.subterrain_size[0], self.n_cols * self.subterrain_size[1]
+            self._terrain_origin = np.array([-self._terrain_size_x / 2.0, -self._terrain_size_y / 2.0, 0.0])
+            self._tile_centers = torch.zeros((self.n_rows, self.n_cols, 3), dtype=torch.float32)
+            for r in range(self.n_rows):
+                for c in range(self.n_cols):
+                    self._tile_centers[r, c, 0] = self._terrain_origin[0] + (r + 0.5) * self.subterrain_size[0]
+                    self._tile_centers[r, c, 1] = self._terrain_origin[1] + (c + 0.5) * self.subterrain_size[1]
+            # collision field (gs.morphs.Terrain(n_subterrains=..., subterrain_types=...) -> genesis/utils/terrain.py parse_terrain)
+            self._height_field_np = build_subterrain_grid(self.subterrain_types, self.subterrain_size, self.horizontal_scale, self.vertical_scale,
+                                                          self.randomize, self.cfg.get("subterrain_parameters", None))
+            self._height_field = None  # what the manager itself sees
+            return
         self._height_field_np = np.array(self.cfg["height_field"], dtype=np.float32)  # terrain_manager.py:63-76
         rows, cols = self._height_field_np.shape
         self._terrain_size_x, self._terrain_size_y = rows * self.horizontal_scale, cols * self.horizontal_scale
@@ -1029,11 +1051,31 @@ class TerrainManager:
         self._terrain_origin = np.array([-self._terrain_size_x / 2.0, -self._terrain_size_y / 2.0, 0.0])
         self._height_field = self._height_field_np
         self.subterrain_types, self.n_rows, self.n_cols, self._tile_centers = None, 1, 1, None
-        self._env_spawn_pos = None  # bound to the device buffer by the env
+
+    def _tile_of(self, k, size, n):
+        o = float(self._terrain_origin[k])
+        return ((self._env_spawn_pos[:, k] - o) / size).floor().long().clamp(0, n - 1)
+
+    @property
+    def _env_tile_row(self):  # tile the env spawned on (heightmap mode: 0), recovered from the spawn point
+        if self.use_custom_heightmap:
+            return torch.zeros(self.num_envs, dtype=torch.long, device=self._env_spawn_pos.device)
+        return self._tile_of(0, self.subterrain_size[0], self.n_rows)
+
+    @property
+    def _env_tile_col(self):
+        if self.use_custom_heightmap:
+            return torch.zeros(self.num_envs, dtype=torch.long, device=self._env_spawn_pos.device)
+        return self._tile_of(1, self.subterrain_size[1], self.n_cols)
+
+    def get_env_tile_rows(self):
+        return self._env_tile_row
 
     def _query_height_batch(self, world_x, world_y):
         """Bilinear ground height (terrain_manager.py:354-392), float64 numpy arithmetic like the reference."""
         hf = self._height_field
+        if hf is None:
+            return torch.zeros(len(world_x), device=world_x.device, dtype=torch.float32)
         R, Cc = hf.shape
         lx = np.clip((np.asarray(world_x.detach().cpu()) - self._terrain_origin[0]) / self.horizontal_scale, 0, R - 2).astype(np.float64)
         ly = np.clip((np.asarray(world_y.detach().cpu()) - self._terrain_origin[1]) / self.horizontal_scale, 0, Cc - 2).astype(np.float64)
@@ -1050,7 +1092,9 @@ class TerrainManager:
         return torch.norm(base_pos_xy - self._env_spawn_pos[:, :2], dim=1) > self.max_wander
 
     def get_terrain_type_string(self, env_idx: int) -> str:
-        return "custom_heightmap"
+        if self.use_custom_heightmap:
+            return "custom_heightmap"
+        return self.subterrain_types[int(self._env_tile_row[env_idx])][int(self._env_tile_col[env_idx])]
 
 
 class Go2EnvWalkTerrain(Go2EnvWalk):
@@ -1066,8 +1110,14 @@ class Go2EnvWalkTerrain(Go2EnvWalk):
             return
         c.tm_on = 1
         c.tm_max_wander, c.tm_spawn_offset = float(T.max_wander), float(T.spawn_height_offset)
-        c.tm_safe_half_x = float(T._terrain_size_x / 2.0 - T.boundary_margin - 0.5)
-        c.tm_safe_half_y = float(T._terrain_size_y / 2.0 - T.boundary_margin - 0.5)
+        if T.use_custom_heightmap:
+            c.tm_safe_half_x = float(T._terrain_size_x / 2.0 - T.boundary_margin - 0.5)
+            c.tm_safe_half_y = float(T._terrain_size_y / 2.0 - T.boundary_margin - 0.5)
+        else:  # grid mode: random tile, centre + jitter (terrain_manager.py:308-335); height queries see nothing
+            c.tm_grid_rows, c.tm_grid_cols, c.tm_blind = T.n_rows, T.n_cols, 1
+            c.tm_tile_x, c.tm_tile_y = float(T.subterrain_size[0]), float(T.subterrain_size[1])
+            c.tm_safe_half_x = float(T.subterrain_size[0] / 2.0 - T.boundary_margin - 0.5)
+            c.tm_safe_half_y = float(T.subterrain_size[1] / 2.0 - T.boundary_margin - 0.5)
         c.tm_hs, c.tm_ox, c.tm_oy = float(T.horizontal_scale), float(T._terrain_origin[0]), float(T._terrain_origin[1])
 
     def _after_bind(self):
@@ -1094,7 +1144,9 @@ class Go2EnvTerrain(Go2EnvWalkTerrain):
     def _after_resets(self, stats):
         super()._after_resets(stats)
         if self.terrain.enabled and int(round(float(stats[abi.STATS_RESETS]))) > 0 and "episode" in self.extras:
-            self.extras["episode"]["terrain_row_mean"] = 0.0  # heightmap mode: every env is on tile row 0
+            T = self.terrain  # go2_env_terrain.py:1242-1244: mean tile row of the envs reset in this tick (heightmap mode: row 0)
+            m = self.reset_buf.bool()
+            self.extras["episode"]["terrain_row_mean"] = 0.0 if (T.use_custom_heightmap or not bool(m.any())) else float(T._env_tile_row[m].float().mean())
 
 
 class Go2EnvBaseFlavour(_Go2EnvBase):

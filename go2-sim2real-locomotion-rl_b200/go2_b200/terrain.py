@@ -110,3 +110,148 @@ def build_stair_terrain_variable_depth(terrain_cfg: dict):
         "num_flights": num_flights, "num_steps": num_steps,
     }
     return hf, info
+
+
+# ---------------------------------------------------------------------------------------------------------------------------------
+# Sub-terrain grid of examples/locomotion/terrain_manager.py's grid mode = Genesis' `gs.morphs.Terrain(n_subterrains=...,
+# subterrain_types=...)`: genesis/utils/terrain.py:17-160 (parse_terrain: tile loop, shared borders keep the maximum) over the Isaac
+# Gym tile generators of genesis/ext/isaacgym/terrain_utils.py.  Heights are float32 in units of `vertical_scale`, like Genesis'.
+# Random tiles draw from numpy's GLOBAL generator in the reference's order; `randomize=False` seeds 0 around every tile and restores
+# the state.  tests/test_terrain_grid.py pins the tiles against digests of the reference functions' own output.
+# ---------------------------------------------------------------------------------------------------------------------------------
+GS_EPS = np.finfo(np.float32).eps  # gs.EPS at precision "32"
+TILE_DEFAULTS = {  # genesis/options/morphs.py:1313-1356
+    "flat_terrain": {},
+    "random_uniform_terrain": {"min_height": -0.1, "max_height": 0.1, "step": 0.1, "downsampled_scale": 0.5},
+    "sloped_terrain": {"slope": -0.5},
+    "pyramid_sloped_terrain": {"slope": -0.1},
+    "discrete_obstacles_terrain": {"max_height": 0.05, "min_size": 1.0, "max_size": 5.0, "num_rects": 20},
+    "wave_terrain": {"num_waves": 2.0, "amplitude": 0.1},
+    "stairs_terrain": {"step_width": 0.75, "step_height": -0.1},
+    "pyramid_stairs_terrain": {"step_width": 0.75, "step_height": -0.1},
+}
+
+
+def not_a_knot_spline(x, y, xv):
+    """Cubic spline through (x, y[:, k]) with not-a-knot ends, evaluated at xv (genesis/utils/geom.py:2151-2230 cubic_spline_1d): the
+    second-derivative system is an almost tridiagonal matrix (one extra entry in the first and the last row) eliminated top-down in
+    FLOAT32 like the reference's band storage, data and abscissae stay float64."""
+    y = y[:, None] if y.ndim == 1 else y
+    n = len(x)
+    h = np.diff(x)
+    f32 = np.float32
+    lo2, lo, di, up, up2 = (np.zeros(n, f32) for _ in range(5))  # A[i, i-2], A[i, i-1], A[i, i], A[i, i+1], A[i, i+2]
+    r = np.zeros(y.shape, f32)
+    di[0], up[0], up2[0] = h[1], -(h[0] + h[1]), h[0]
+    lo2[-1], lo[-1], di[-1] = h[-1], -(h[-2] + h[-1]), h[-2]
+    for i in range(1, n - 1):
+        lo[i], di[i], up[i] = h[i - 1], 2 * (h[i - 1] + h[i]), h[i]
+        r[i] = 3 * ((y[i + 1] - y[i]) / h[i] - (y[i] - y[i - 1]) / h[i - 1])
+    for k in range(n - 1):
+        piv = di[k]
+        f = lo[k + 1] / piv
+        di[k + 1] -= f * up[k]
+        if k + 2 < n:
+            up[k + 1] -= f * up2[k]
+        r[k + 1] -= f * r[k]
+        if k == n - 3:  # the last row's extra entry sits in column n - 3
+            f = lo2[-1] / piv
+            lo[-1] -= f * up[k]
+            di[-1] -= f * up2[k]
+            r[-1] -= f * r[k]
+    c = np.zeros_like(r)
+    c[-1] = r[-1] / di[-1]
+    c[-2] = (r[-2] - up[-2] * c[-1]) / di[-2]
+    for i in range(n - 3, -1, -1):
+        c[i] = r[i] - up[i] * c[i + 1]
+        if up2[i] != 0:
+            c[i] -= up2[i] * c[i + 2]
+        c[i] /= di[i]
+    b = (y[1:] - y[:-1]) / h[:, None] - h[:, None] * (2 * c[:-1] + c[1:]) / 3
+    d = (c[1:] - c[:-1]) / (3 * h[:, None])
+    xv = np.atleast_1d(xv)
+    k = np.clip(np.searchsorted(x[1:], xv), 0, n - 2)
+    t = (xv - x[k])[:, None]
+    return y[k] + b[k] * t + c[k] * t**2 + d[k] * t**3
+
+
+def _tile(kind, W, L, hs, vs, p):
+    """One W x L tile (float32, units of vs) of the named Isaac Gym generator (genesis/ext/isaacgym/terrain_utils.py)."""
+    z = np.zeros((W, L), dtype=np.float32)
+    if kind == "flat_terrain":
+        return z
+    if kind == "random_uniform_terrain":  # :43-90: coarse random grid -> separable spline up-sampling -> rint
+        ds = p["downsampled_scale"] if p.get("downsampled_scale") is not None else hs
+        sw, sl = W * hs, L * hs
+        lo, hi, st = int(p["min_height"] / vs), int(p["max_height"] / vs), int(p["step"] / vs)
+        coarse = np.random.choice(np.arange(lo, hi + st, st), (int(sw / ds), int(sl / ds)))
+        xc, yc = np.linspace(0, sw, coarse.shape[0]), np.linspace(0, sl, coarse.shape[1])
+        along_y = not_a_knot_spline(yc, coarse.T, np.linspace(0, sl, L)).T
+        z += np.rint(not_a_knot_spline(xc, along_y, np.linspace(0, sw, W)))
+        return z
+    if kind == "sloped_terrain":  # :93-110
+        top = int(p["slope"] * (hs / vs) * W)
+        z[:, np.arange(L)] += top * np.arange(W).reshape(W, 1) / W
+        return z
+    if kind == "pyramid_sloped_terrain":  # :113-145
+        cx, cy = int(W / 2), int(L / 2)
+        fx = ((cx - np.abs(cx - np.arange(W))) / cx).reshape(W, 1)
+        fy = ((cy - np.abs(cy - np.arange(L))) / cy).reshape(1, L)
+        z += int(p["slope"] * (hs / vs) * (W / 2)) * fx * fy
+        half = int(p.get("platform_size", 1.0) / hs / 2)
+        edge = z[W // 2 - half, L // 2 - half]
+        return np.clip(z, min(edge, 0), max(edge, 0))
+    if kind == "discrete_obstacles_terrain":  # :148-185
+        top, smin, smax = int(p["max_height"] / vs), int(p["min_size"] / hs), int(p["max_size"] / hs)
+        plat = int(p.get("platform_size", 1.0) / hs)
+        ws = np.arange(min(smin, W - 1), min(smax, W - 1) + 1, 4)
+        ls = np.arange(min(smin, L - 1), min(smax, L - 1) + 1, 4)
+        hts = [-top, -top // 2, top // 2, top]
+        for _ in range(int(p["num_rects"])):
+            w, l, hgt = np.random.choice(ws), np.random.choice(ls), np.random.choice(hts)
+            x0 = np.random.choice(range(0, W - w, 4))
+            y0 = np.random.choice(range(0, L - l, 4))
+            z[x0:x0 + w, y0:y0 + l] = hgt
+        z[(W - plat) // 2:(W + plat) // 2, (L - plat) // 2:(L + plat) // 2] = 0
+        return z
+    if kind == "wave_terrain":  # :188-208
+        amp = 0.5 * p["amplitude"] / vs
+        if p["num_waves"] > 0:
+            div = L / (p["num_waves"] * np.pi * 2)
+            z += amp * np.cos(np.arange(L).reshape(1, L) / div) + amp * np.sin(np.arange(W).reshape(W, 1) / div)
+        return z
+    if kind == "stairs_terrain":  # :211-231
+        sw, sh = int(p["step_width"] / hs), int(p["step_height"] / vs)
+        for i in range(W // sw):
+            z[i * sw:(i + 1) * sw, :] += (i + 1) * sh
+        return z
+    if kind == "pyramid_stairs_terrain":  # :234-263
+        sw, sh, plat = int(p["step_width"] / hs), int(p["step_height"] / vs), int(p.get("platform_size", 1.0) / hs)
+        x0, x1, y0, y1, hgt = 0, W, 0, L, 0
+        while (x1 - x0) > plat and (y1 - y0) > plat:
+            x0, x1, y0, y1, hgt = x0 + sw, x1 - sw, y0 + sw, y1 - sw, hgt + sh
+            z[x0:x1, y0:y1] = hgt
+        return z
+    raise NotImplementedError(f"subterrain type '{kind}' is not built (supported: {sorted(TILE_DEFAULTS)})")
+
+
+def build_subterrain_grid(subterrain_types, subterrain_size=(12.0, 12.0), horizontal_scale=0.25, vertical_scale=0.005, randomize=False,
+                          subterrain_parameters=None):
+    """Height field (float32, units of vertical_scale) of a grid of tiles; tile (i, j) covers rows i * (R - 1) .. (i + 1) * (R - 1)
+    with R = int(size_x / horizontal_scale + eps) + 1 cells, neighbours share their border row / column (maximum of the two)."""
+    types = [list(r) for r in subterrain_types]
+    R = int(subterrain_size[0] / horizontal_scale + GS_EPS) + 1
+    Cc = int(subterrain_size[1] / horizontal_scale + GS_EPS) + 1
+    hf = np.full((len(types) * (R - 1) + 1, len(types[0]) * (Cc - 1) + 1), -np.inf, dtype=np.float32)
+    for i, row in enumerate(types):
+        for j, kind in enumerate(row):
+            params = dict(TILE_DEFAULTS.get(kind, {}), **((subterrain_parameters or {}).get(kind, {})))
+            if not randomize:
+                state = np.random.get_state()
+                np.random.seed(0)
+            tile = _tile(kind, R, Cc, horizontal_scale, vertical_scale, params)
+            if not randomize:
+                np.random.set_state(state)
+            view = hf[i * (R - 1):(i + 1) * (R - 1) + 1, j * (Cc - 1):(j + 1) * (Cc - 1) + 1]
+            view[:] = np.maximum(view, tile)
+    return hf

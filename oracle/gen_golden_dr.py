@@ -37,7 +37,7 @@ class DrawLog:
         self.m = module
         self.calls = []
         self._of, self._oi, self._orn = module.gs_rand_float, getattr(module, "gs_rand_int", None), torch.randn_like
-        self._orl, self._or, self._ornn = torch.rand_like, torch.rand, torch.randn
+        self._orl, self._or, self._ornn, self._ori = torch.rand_like, torch.rand, torch.randn, torch.randint
         module.gs_rand_float = self._wrap(self._of, "f")
         if hasattr(module, "gs_rand_int"):
             module.gs_rand_int = self._wrap(self._oi, "i")
@@ -47,6 +47,7 @@ class DrawLog:
         torch.rand_like = self._wrap_t(self._orl, "ul")
         torch.rand = self._wrap_t(self._or, "u")
         torch.randn = self._wrap_t(self._ornn, "nn")
+        torch.randint = self._wrap_t(self._ori, "ri")  # terrain_manager._sample_spawn_grid: tile row / column
 
     def _wrap(self, fn, kind):
         def w(*a, **k):
@@ -60,7 +61,7 @@ class DrawLog:
         def w(*a, **k):
             r = fn(*a, **k)
             caller = sys._getframe(1).f_code.co_name
-            if caller in ("_update_actor_lidar_scan", "_update_stair_info", "_sample_spawn_heightmap"):
+            if caller in ("_update_actor_lidar_scan", "_update_stair_info", "_sample_spawn_heightmap", "_sample_spawn_grid"):
                 self.calls.append((caller, kind, r.clone()))
             return r
 
@@ -73,7 +74,7 @@ class DrawLog:
 
     def restore(self):
         self.m.gs_rand_float, torch.randn_like = self._of, self._orn
-        torch.rand_like, torch.rand, torch.randn = self._orl, self._or, self._ornn
+        torch.rand_like, torch.rand, torch.randn, torch.randint = self._orl, self._or, self._ornn, self._ori
         if hasattr(self.m, "gs_rand_int"):
             self.m.gs_rand_int = self._oi
 
@@ -215,6 +216,13 @@ def draws_of_tick(env, kind, calls, done, ep_len_pre, A):
         if "init_euler_range" in env.env_cfg:
             row[ridx, abi.RP_ROLL] = rr[i][1]; row[ridx, abi.RP_PITCH] = rr[i + 1][1]; i += 2
         assert i == len(rr)
+        sg_ = by.pop("_sample_spawn_grid", [])
+        if sg_:  # terrain_manager.py:311-328: tile rows, tile columns, x jitter uniforms, y jitter uniforms
+            assert [k for k, _ in sg_] == ["ri", "ri", "u", "u"], [k for k, _ in sg_]
+            row[ridx, abi.RP_TILE] = sg_[0][1]
+            row[ridx, abi.RP_TILE + 1] = sg_[1][1]
+            row[ridx, abi.RP_SPAWN] = sg_[2][1]
+            row[ridx, abi.RP_SPAWN + 1] = sg_[3][1]
         sp_ = by.pop("_sample_spawn_heightmap", [])
         if sp_:  # terrain_manager.py:293-296: x uniforms, then y uniforms
             assert [k for k, _ in sp_] == ["u", "u"]
@@ -405,6 +413,29 @@ def walk_terrain_cfgs():
     return env_cfg, obs_cfg, reward_cfg, command_cfg
 
 
+def walk_grid_cfgs():
+    """The same train script with TERRAIN_MODE = "grid" (make_terrain_cfg_grid: 2 x 2 tiles of 8 m, two flat and two random_uniform
+    ones generated by Genesis' terrain parser with numpy's global RNG, seeded here), short episodes."""
+    import ast
+
+    path = os.path.join(REF, "examples/locomotion/go2_train_Omni_kplearn_varied_terrain.py")
+    tree = ast.parse(open(path).read())
+    keep = [n for n in tree.body if isinstance(n, (ast.FunctionDef, ast.Assign))]
+    ns = {"np": np}
+    exec(compile(ast.Module(body=keep, type_ignores=[]), path, "exec"), ns)
+    ns["TERRAIN_MODE"] = "grid"
+    with contextlib.redirect_stdout(io.StringIO()):
+        env_cfg, obs_cfg, reward_cfg, command_cfg = ns["get_cfgs"]()
+    assert "subterrain_types" in env_cfg["terrain"] and env_cfg["terrain"].get("height_field") is None
+    env_cfg["terrain"]["subterrain_size"] = list(env_cfg["terrain"]["subterrain_size"])
+    env_cfg["terrain"]["boundary_margin"] = 3.0  # max_wander = 1 m: the boundary reset occurs inside the fixture
+    env_cfg.update(episode_length_s=4.0, resampling_time_s=1.0)
+    env_cfg["curriculum"]["level_init"] = 1.0
+    env_cfg["terrain"]["np_seed"] = 29  # (fixture key) numpy's global generator is seeded with this right before the env is built
+    np.random.seed(29)
+    return env_cfg, obs_cfg, reward_cfg, command_cfg
+
+
 def terrain_env_cfgs():
     """go2_env_terrain.py has no train script in the tree: the height-map cfg above with what the class adds switched on - one more
     privileged-obs entry (ground height), the stumble reward (low threshold so that it fires) and the foot rewards it relies on."""
@@ -454,6 +485,7 @@ def main():
     jobs = {
         "stair_info_c1": lambda: (go2_env_stair_lidar_2.Go2Env, go2_env_stair_lidar_2, stair_info_cfgs(), "stair_info", 16, 300, 0.5, 2121, 16),
         "terrain_env_c1": lambda: (go2_env_terrain.Go2Env, go2_env_terrain, terrain_env_cfgs(), "terrain_env", 16, 300, 0.6, 616, 16),
+        "walk_grid_c1": lambda: (go2_env_wt.Go2Env, go2_env_wt, walk_grid_cfgs(), "walk_terrain", 16, 300, 0.5, 818, 16),
         "walk_terrain_c1": lambda: (go2_env_wt.Go2Env, go2_env_wt, walk_terrain_cfgs(), "walk_terrain", 16, 300, 0.5, 515, 16),
         "stair_lidar_c1": lambda: (go2_env_stair_lidar.Go2Env, go2_env_stair_lidar, stair_lidar_cfgs(), "stair_lidar", 16, 300, 0.5, 909, 16),
         "walk_c1": lambda: (go2_env_walk.Go2Env, go2_env_walk, walk_cfgs(), "walk", 32, 1000, 0.5, 1234, 16),

@@ -224,7 +224,14 @@ class Scene:
                                   base_quat=tuple(np.asarray(m.quat, dtype=float)))
         t = self._terrain_morph
         if t is not None:
-            hf = np.asarray(t.height_field, dtype=np.float64) * float(t.vertical_scale)
+            if getattr(t, "height_field", None) is None:  # sub-terrain grid: the restatement of genesis/utils/terrain.py parse_terrain
+                from go2_b200.terrain import build_subterrain_grid  # (pinned against the reference generators by oracle/ref_terrain_tiles.py)
+
+                t.generated_field = build_subterrain_grid(t.subterrain_types, t.subterrain_size, t.horizontal_scale, t.vertical_scale,
+                                                          getattr(t, "randomize", False), getattr(t, "subterrain_parameters", None))
+                hf = np.asarray(t.generated_field, dtype=np.float64) * float(t.vertical_scale)
+            else:
+                hf = np.asarray(t.height_field, dtype=np.float64) * float(t.vertical_scale)
             self._rigid.set_terrain(hf, float(t.horizontal_scale), np.asarray(t.pos, dtype=np.float64))
 
     def step(self):

@@ -34,7 +34,7 @@ FAST_EXTRA = lambda n: max(2, n // 2000)  # noqa: E731
 # copy in the privileged obs, the kept copy - are inside the band on all 4,800 env-ticks)
 # stair: 4.9 % of the env-ticks (hostemu) sit on rounded step-edge contacts whose MPR output is discontinuous at rounding level
 # (test_oracle_contact_output_is_discontinuous_at_rounding_level); every bit-exact output still matches on all of them
-CASES = [("walk_c1", "walk", 0), ("walk_hard", "walk", 0), ("base_allrew", "base", 0), ("stair_c1", "stair", 400), ("stair_lidar_c1", "stair_lidar", 420), ("stair_info_c1", "stair_info", 480), ("walk_terrain_c1", "walk_terrain", 240), ("terrain_env_c1", "terrain_env", 240)]
+CASES = [("walk_c1", "walk", 0), ("walk_hard", "walk", 0), ("base_allrew", "base", 0), ("stair_c1", "stair", 400), ("stair_lidar_c1", "stair_lidar", 420), ("stair_info_c1", "stair_info", 480), ("walk_terrain_c1", "walk_terrain", 240), ("walk_grid_c1", "walk_terrain", 240), ("terrain_env_c1", "terrain_env", 240)]
 EXACT_AFTER = ["kp_factors", "kd_factors", "motor_strength", "grav_off", "delay", "commands", "ep_len"]
 
 

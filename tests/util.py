@@ -24,6 +24,9 @@ def make_env(kind, cfgs, B, backend, hostemu_lib=None, **kw):
 
     cls = {"walk": Go2EnvWalk, "stair": Go2EnvStair, "stair_lidar": Go2EnvStairLidar, "stair_info": Go2EnvStairInfo, "walk_terrain": Go2EnvWalkTerrain, "terrain_env": Go2EnvTerrain}.get(kind, Go2EnvBaseFlavour)
     cfgs = json.loads(json.dumps(cfgs))
+    t = cfgs[0].get("terrain") if isinstance(cfgs[0], dict) else None
+    if isinstance(t, dict) and "np_seed" in t:  # a terrain generated with numpy's global generator (grid mode of the terrain manager)
+        np.random.seed(int(t["np_seed"]))
     if backend == "hostemu":
         from hostemu_core import HostEmuCore
 
