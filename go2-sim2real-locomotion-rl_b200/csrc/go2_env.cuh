@@ -22,6 +22,11 @@ namespace go2 {
 #define I32(id) ((int*)bf.p[id])
 #define U8(id) ((uint8_t*)bf.p[id])
 
+#ifdef __CUDA_ARCH__
+#define G2_LDCG(p) __ldcg(p)
+#else
+#define G2_LDCG(p) (*(p))
+#endif
 enum RngSlot { SLOT_ACT_NOISE = 0, SLOT_OBS_NOISE = 8, SLOT_PUSH = 32, SLOT_CMD = 33, SLOT_CMD_RESET = 34, SLOT_RESET = 40, SLOT_LIDAR = 56 };
 
 struct EnvStepOut {
@@ -455,7 +460,8 @@ G2_HDN void env_pre(const Go2Model& m, const EnvConfig& cfg, const StepParams& s
     for (int d = 0; d < NV; ++d) { p.ctrl_force[d] = 0.0f; p.ctrl_pos[d] = 0.0f; }
 
     if (sp.do_physics) {
-        for (int i = 0; i < A; ++i) e.act[i] = clampf(actions[b * A + i], -cfg.clip_actions, cfg.clip_actions);
+        // (L2 loads: with go2_step_host the rows are written by the copy engine while this kernel runs - no read-only-cache path)
+        for (int i = 0; i < A; ++i) e.act[i] = clampf(G2_LDCG(actions + b * A + i), -cfg.clip_actions, cfg.clip_actions);
         if (cfg.kind != ENV_BASE) {
             // ---- action delay ring (shared write index, per-env delay)
             float* hist = F32(B_HIST) + (size_t)b * H * A;
@@ -952,7 +958,28 @@ G2_HD void t_env_step(const Go2Model& m, const EnvConfig& cfg, const StepParams&
         velocities(m, p);
     }
     G2_FINE_SYNC2();
-    if (valid) env_pre(m, cfg, sp, bf, actions, b, p, e, out);
+    bool act_late = false;
+#ifdef __CUDA_ARCH__
+    if (sp.act_flag != nullptr) {  // go2_step_host: the action rows are still on their way (copy stream); see StepParams.act_flag
+        if (threadIdx.x == 0) {
+            unsigned long long t0, t1;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+            for (;;) {
+                unsigned int v;
+                asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(sp.act_flag) : "memory");
+                if (v == sp.act_seq) break;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                if (t1 - t0 > 2000000000ull) { act_late = true; break; }  // never hang the GPU: flag the env and go on
+                __nanosleep(200);
+            }
+        }
+        act_late = __syncthreads_or(act_late ? 1 : 0) != 0;
+    }
+#endif
+    if (valid) {
+        if (act_late) p.err |= ERR_ACTION_WAIT;
+        env_pre(m, cfg, sp, bf, actions, b, p, e, out);
+    }
     if (sp.do_physics) {
         for (int s = 0; s < 2; ++s) {
             G2_PHASE_SYNC();

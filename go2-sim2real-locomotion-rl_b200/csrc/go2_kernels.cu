@@ -9,6 +9,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <cstdlib>
 #include <string>
 #include <vector>
 #include "../../include/go2_b200.h"
@@ -38,6 +39,12 @@ struct go2_handle {
     int tpb, nblocks, small;  // launch shape of the step kernel; small = the 255-register instantiation
     int parity;          // double-buffer index the NEXT tick uses (B_GLOBALS / B_STATS)
     int post_pending;    // a deferred post-pass is outstanding (StepParams.defer_post)
+    // go2_step_host: action rows + a sequence word go over their own (non-blocking) stream while the step kernel already runs
+    cudaStream_t copy_stream;
+    cudaEvent_t copy_gate;     // work queued on the caller's stream before this tick (the previous kernel may still read the rows)
+    unsigned int* h_seq;       // pinned source of the sequence word
+    unsigned int* d_seq;       // device word the kernel polls (StepParams.act_flag)
+    unsigned int seq;
     std::string err;
 };
 
@@ -210,6 +217,17 @@ int go2_create(const int32_t* model_iv, int n_iv, const double* model_fv, int n_
     cudaMemcpy(h->d_cfg, &h->cfg, sizeof(EnvConfig), cudaMemcpyHostToDevice);
     cudaMallocHost(&h->h_stats, sizeof(float) * STATS_LEN * N_STAT_SLOTS);
     for (int i = 0; i < N_STAT_SLOTS; ++i) cudaEventCreateWithFlags(&h->stat_ev[i], cudaEventDisableTiming);
+    h->copy_stream = nullptr; h->copy_gate = nullptr; h->h_seq = nullptr; h->d_seq = nullptr; h->seq = 0;
+    {   // overlapped action upload of go2_step_host (step_host_begin); GO2_B200_SERIAL_UPLOAD=1 keeps the copy on the caller's stream
+        const char* off = getenv("GO2_B200_SERIAL_UPLOAD");
+        if (!(off && off[0] == '1')) {
+            bool ok = cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking) == cudaSuccess &&
+                      cudaEventCreateWithFlags(&h->copy_gate, cudaEventDisableTiming) == cudaSuccess &&
+                      cudaMallocHost(&h->h_seq, sizeof(unsigned int)) == cudaSuccess && cudaMalloc(&h->d_seq, sizeof(unsigned int)) == cudaSuccess;
+            if (ok) { *h->h_seq = 0; cudaMemset(h->d_seq, 0, sizeof(unsigned int)); }
+            else { cudaGetLastError(); if (h->copy_stream) cudaStreamDestroy(h->copy_stream); h->copy_stream = nullptr; }
+        }
+    }
     cudaFuncSetAttribute(go2_step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 0);  // all of L1 for thread-local data
     cudaFuncSetAttribute(go2_step_kernel_small, cudaFuncAttributePreferredSharedMemoryCarveout, 0);
     std::string init(h->arena_bytes, 0);
@@ -231,6 +249,10 @@ void go2_destroy(go2_handle* h) {
     cudaFree(h->d_cfg);
     cudaFreeHost(h->h_stats);
     for (int i = 0; i < N_STAT_SLOTS; ++i) cudaEventDestroy(h->stat_ev[i]);
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+    if (h->copy_gate) cudaEventDestroy(h->copy_gate);
+    if (h->h_seq) cudaFreeHost(h->h_seq);
+    if (h->d_seq) cudaFree(h->d_seq);
     delete h;
 }
 
@@ -263,7 +285,7 @@ static int launch_step(go2_handle* h, const float* d_actions, const void* params
     StepParams sp;
     memcpy(&sp, params, sizeof(sp));
     sp.parity = h->parity;
-    if (!host_call) sp.host_obs = nullptr, sp.host_rew = nullptr, sp.host_done = nullptr;  // only go2_step_host* sets them
+    if (!host_call) sp.host_obs = nullptr, sp.host_rew = nullptr, sp.host_done = nullptr, sp.act_flag = nullptr;  // only go2_step_host* sets them
     if (sp.replay_on && h->cfg.replay_rows != h->cfg.num_envs) { h->err = "replay_on needs EnvConfig.replay_rows == num_envs"; return -4; }
     if (cudaSetDevice(h->device) != cudaSuccess) { h->err = "cudaSetDevice"; return -1; }
     if (h->small)
@@ -328,7 +350,21 @@ static int step_host_begin(go2_handle* h, const float* h_actions, const void* pa
     sp.host_rew = direct ? (float*)mr : nullptr;
     sp.host_done = direct ? (uint8_t*)md : nullptr;
     *staged = direct ? 0 : 1;
-    if (!ck(h, cudaMemcpyAsync(h->bf.p[B_ACTIONS_IN], h_actions, B * c.num_actions * 4, cudaMemcpyHostToDevice, s), "H2D actions")) return -1;
+    if (h->copy_stream && sp.do_physics) {
+        // The opening phase of the kernel (state load, FK, velocities: ~0.1 ms at 65,536 envs) needs no actions, so the 4 MB upload
+        // runs beside it instead of before it: rows, then the sequence word, on the copy stream (ordered); the kernel waits for the
+        // word before env_pre.  Both copies are queued BEFORE the launch, so they can never sit behind the kernel.
+        h->seq += 1;
+        *h->h_seq = h->seq;
+        if (!ck(h, cudaEventRecord(h->copy_gate, s), "copy gate")) return -1;
+        if (!ck(h, cudaStreamWaitEvent(h->copy_stream, h->copy_gate, 0), "copy gate wait")) return -1;
+        if (!ck(h, cudaMemcpyAsync(h->bf.p[B_ACTIONS_IN], h_actions, B * c.num_actions * 4, cudaMemcpyHostToDevice, h->copy_stream), "H2D actions")) return -1;
+        if (!ck(h, cudaMemcpyAsync(h->d_seq, h->h_seq, sizeof(unsigned int), cudaMemcpyHostToDevice, h->copy_stream), "H2D action seq")) return -1;
+        sp.act_flag = h->d_seq;
+        sp.act_seq = h->seq;
+    } else {
+        if (!ck(h, cudaMemcpyAsync(h->bf.p[B_ACTIONS_IN], h_actions, B * c.num_actions * 4, cudaMemcpyHostToDevice, s), "H2D actions")) return -1;
+    }
     return launch_step(h, (const float*)h->bf.p[B_ACTIONS_IN], &sp, sizeof(sp), s, true);
 }
 

@@ -50,7 +50,7 @@ constexpr int LS_ITERS = 50;
 constexpr float LS_TOL = 1e-2f;
 
 enum GeomType { GEOM_SPHERE = 1, GEOM_CYLINDER = 3, GEOM_BOX = 5, GEOM_TERRAIN = 7 };
-enum ErrBits { ERR_CPAIR_OVERFLOW = 1, ERR_CONTACT_OVERFLOW = 2, ERR_NAN_FORCE = 4, ERR_NAN_ACC = 8, ERR_GJK_WANTED = 16 };
+enum ErrBits { ERR_CPAIR_OVERFLOW = 1, ERR_CONTACT_OVERFLOW = 2, ERR_NAN_FORCE = 4, ERR_NAN_ACC = 8, ERR_GJK_WANTED = 16, ERR_ACTION_WAIT = 32 /* the action upload of go2_step_host did not arrive within 2 s */ };
 enum EnvKind { ENV_WALK = 0, ENV_STAIR = 1, ENV_BASE = 2 };
 enum CtrlKind { CTRL_MANUAL_PLS = 0, CTRL_MANUAL_FIXED = 1, CTRL_GENESIS_PD = 2 };
 
@@ -212,6 +212,11 @@ struct StepParams {
     float* host_obs;
     float* host_rew;
     uint8_t* host_done;
+    // go2_step_host: the action rows travel on a copy stream WHILE the kernel's opening phase (state load, FK, velocities) runs; the
+    // copy stream writes act_seq to *act_flag after the rows, thread 0 of every block waits for it before env_pre (filled by the
+    // library; null = the actions are already in place)
+    const unsigned int* act_flag;
+    unsigned int act_seq;
 };
 
 // B_GLOBALS: [2][GLOBALS_LEN] global physics DR values in force (slot = StepParams.parity)

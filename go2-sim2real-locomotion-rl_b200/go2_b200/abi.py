@@ -119,6 +119,7 @@ class StepParams(C.Structure):
         ("cand_friction", _f), ("cand_mass", _f), ("cand_com", _f * 3), ("cand_leg", _f * 4),
         ("parity", _i), ("defer_post", _i), ("replay_on", _i), ("ext_on", _i),
         ("host_obs", C.c_void_p), ("host_rew", C.c_void_p), ("host_done", C.c_void_p),
+        ("act_flag", C.c_void_p), ("act_seq", C.c_uint),
     ]
 
 

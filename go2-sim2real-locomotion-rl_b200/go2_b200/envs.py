@@ -401,6 +401,8 @@ class _Go2EnvBase:
         bits = 0
         for v in torch.unique(self.core.buf["errno"]).tolist():
             bits |= int(v)
+        if bits & 32:
+            raise RuntimeError("go2_step_host: the action upload did not reach the device within 2 s (copy stream stalled)")
         if bits & 2:
             raise RuntimeError("Exceeding max number of contact pairs. Please increase 'max_collision_pairs'.")
         if bits & 1:

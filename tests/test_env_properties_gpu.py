@@ -124,10 +124,15 @@ def test_env_state_resume_is_bit_exact_on_cuda():
             assert torch.equal(u, v)
 
 
+@pytest.mark.parametrize("B,serial_upload", [(300, False), (300, True), (40000, False)])
 @pytest.mark.parametrize("pinned", [False, True])
-def test_step_host_matches_device_step(pinned):
-    """Pageable host buffers take the staged path (D2H copies), pinned ones are written by the step kernel itself."""
-    B = 300
+def test_step_host_matches_device_step(pinned, B, serial_upload, monkeypatch):
+    """Pageable host buffers take the staged path (D2H copies), pinned ones are written by the step kernel itself.  The action rows
+    go up on the library's copy stream while the kernel's opening phase runs (the kernel waits for a sequence word before env_pre),
+    or - GO2_B200_SERIAL_UPLOAD=1, read at create - on the caller's stream before the kernel: same results either way, on the
+    255-register kernel (300 envs) and the 128-register one (40,000)."""
+    if serial_upload:
+        monkeypatch.setenv("GO2_B200_SERIAL_UPLOAD", "1")
     cfgs = _cfgs("walk")
     a_env = make_env("walk", cfgs, B, "cuda", seed=5)
     b_env = make_env("walk", cfgs, B, "cuda", seed=5)
