@@ -337,7 +337,7 @@ def emit(args, workload, B, world, res, headline, cpu):
                                                        population="episode lengths randomised (rsl-rl init_at_random_ep_len), settle_ticks untimed ticks before the warm-up: steady-state poses and a steady stream of time-out resets"),
         "e2e": {"value": world * B * K / (res["ms_e2e"] * 1e-3), "unit": UNIT, "h2d_bytes_per_step": B * env.num_actions * 4,
                 "d2h_bytes_per_step": B * (env.num_obs * 4 + 4 + 1), "ms_per_step": res["ms_e2e"] / K,
-                "what": "go2_step_host: pinned actions H2D, step + post kernels, rew / done / obs D2H, stream sync - every tick"},
+                "what": "go2_step_host: pinned actions H2D (copy stream, beside the kernel's opening phase), step + post kernels, rew / done / obs written to the pinned host buffers by the kernel, stream sync - every tick"},
         "gpu_launches": int(res["launches"]),
         "launch_shape": res["shape"],
         "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
