@@ -122,6 +122,8 @@ def build_stair_terrain_variable_depth(terrain_cfg: dict):
 GS_EPS = np.finfo(np.float32).eps  # gs.EPS at precision "32"
 TILE_DEFAULTS = {  # genesis/options/morphs.py:1313-1356
     "flat_terrain": {},
+    "fractal_terrain": {"levels": 8, "scale": 5.0},
+    "stepping_stones_terrain": {"stone_size": 1.0, "stone_distance": 0.25, "max_height": 0.2, "platform_size": 0.0},
     "random_uniform_terrain": {"min_height": -0.1, "max_height": 0.1, "step": 0.1, "downsampled_scale": 0.5},
     "sloped_terrain": {"slope": -0.5},
     "pyramid_sloped_terrain": {"slope": -0.1},
@@ -231,6 +233,44 @@ def _tile(kind, W, L, hs, vs, p):
         while (x1 - x0) > plat and (y1 - y0) > plat:
             x0, x1, y0, y1, hgt = x0 + sw, x1 - sw, y0 + sw, y1 - sw, hgt + sh
             z[x0:x1, y0:y1] = hgt
+        return z
+    if kind == "fractal_terrain":  # genesis/utils/terrain.py:190-216: midpoint displacement, coarse to fine; a point takes the mean of
+        # the coarser level's points around it (the two on its row / column, or the four diagonal ones) plus a halving random term
+        levels, out = int(p["levels"]), np.zeros((W, L), dtype=np.float32)
+        for level in range(1, levels + 1):
+            st = 2 ** (levels - level)
+            for r in range(0, W, st):
+                odd_r = (r // st) % 2  # rows of the coarser level are the even multiples of st
+                dr = st * odd_r
+                for c in range(st * (1 - odd_r), L, st * (2 - odd_r)):
+                    dc = st * ((c // st) % 2)
+                    around = out[r - dr:r + dr + 1:2 * st, c - dc:c + dc + 1:2 * st]
+                    out[r, c] = around.mean() + p["scale"] * (2.0 ** (-level) * np.random.uniform(-1, 1))
+        out /= vs
+        return out
+    if kind == "stepping_stones_terrain":  # terrain_utils.py:266-322: stones in lanes along the longer side, holes of `depth` between
+        size, gap = int(p["stone_size"] / hs), int(p["stone_distance"] / hs)
+        top, plat = int(p["max_height"] / vs), int(p.get("platform_size", 1.0) / hs)
+        levels = np.arange(-top - 1, top, step=1)
+        z[:, :] = int(p.get("depth", -10) / vs)
+        lanes_along_x = L >= W  # lanes are strips of constant y, stones laid along x
+        n_lane, n_run = (L, W) if lanes_along_x else (W, L)
+        a = 0
+        while a < n_lane:
+            a1 = min(n_lane, a + size)
+            b = np.random.randint(0, size)
+            runs = [(0, max(0, b - gap))]  # the piece before the first stone
+            while b < n_run:
+                runs.append((b, min(n_run, b + size)))
+                b += size + gap
+            for b0, b1 in runs:
+                hgt = np.random.choice(levels)
+                if lanes_along_x:
+                    z[b0:b1, a:a1] = hgt
+                else:
+                    z[a:a1, b0:b1] = hgt
+            a += size + gap
+        z[(W - plat) // 2:(W + plat) // 2, (L - plat) // 2:(L + plat) // 2] = 0
         return z
     raise NotImplementedError(f"subterrain type '{kind}' is not built (supported: {sorted(TILE_DEFAULTS)})")
 

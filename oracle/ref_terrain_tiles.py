@@ -36,8 +36,10 @@ def reference_namespace():
     geom = _funcs(os.path.join(REF, "genesis/utils/geom.py"), ["cubic_spline_1d"], {"np": np, "gs": gs, "nb": nb})
     gu = types.SimpleNamespace(cubic_spline_1d=geom["cubic_spline_1d"])
     names = ["random_uniform_terrain", "sloped_terrain", "pyramid_sloped_terrain", "discrete_obstacles_terrain", "wave_terrain",
-             "stairs_terrain", "pyramid_stairs_terrain", "SubTerrain"]
-    return _funcs(os.path.join(REF, "genesis/ext/isaacgym/terrain_utils.py"), names, {"np": np, "gs": gs, "gu": gu})
+             "stairs_terrain", "pyramid_stairs_terrain", "stepping_stones_terrain", "SubTerrain"]
+    ns = _funcs(os.path.join(REF, "genesis/ext/isaacgym/terrain_utils.py"), names, {"np": np, "gs": gs, "gu": gu})
+    ns["fractal_terrain"] = _funcs(os.path.join(REF, "genesis/utils/terrain.py"), ["fractal_terrain"], {"np": np, "gs": gs})["fractal_terrain"]
+    return ns
 
 
 def reference_grid(ns, types_, size, hs, vs, randomize, params):
@@ -70,6 +72,9 @@ CASES = {
     "all_types_fixed": dict(types_=[["flat_terrain", "random_uniform_terrain", "sloped_terrain", "pyramid_sloped_terrain"],
                                     ["discrete_obstacles_terrain", "wave_terrain", "stairs_terrain", "pyramid_stairs_terrain"]],
                             size=(12.0, 12.0), hs=0.25, vs=0.005, randomize=False, params=None),
+    "fractal_stones": dict(types_=[["fractal_terrain", "stepping_stones_terrain"], ["stepping_stones_terrain", "fractal_terrain"]], size=(6.0, 8.0), hs=0.25, vs=0.005,
+                           randomize=True, params={"fractal_terrain": {"levels": 5, "scale": 0.4}, "stepping_stones_terrain": {"stone_size": 0.75, "platform_size": 1.0}}),
+    "stones_wide": dict(types_=[["stepping_stones_terrain", "fractal_terrain"]], size=(8.0, 5.0), hs=0.25, vs=0.005, randomize=True, params=None),
     "all_types_random": dict(types_=[["pyramid_stairs_terrain", "discrete_obstacles_terrain"], ["random_uniform_terrain", "wave_terrain"]],
                              size=(6.0, 9.0), hs=0.1, vs=0.005, randomize=True, params={"random_uniform_terrain": {"step": 0.02, "downsampled_scale": 0.3}}),
 }

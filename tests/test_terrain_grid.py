@@ -23,6 +23,10 @@ REF_DIGESTS = [
     (ALL8, (12.0, 12.0), 0.25, 0.005, False, None, (97, 193), "04c9eca2f14b60337ec1ec77223e9a1c3a99cc3f9001cbf2c5ece30df7ab1eab"),
     ([["pyramid_stairs_terrain", "discrete_obstacles_terrain"], ["random_uniform_terrain", "wave_terrain"]], (6.0, 9.0), 0.1, 0.005, True,
      {"random_uniform_terrain": {"step": 0.02, "downsampled_scale": 0.3}}, (121, 181), "78e2697becc4b702724174776f51587e4760f1b07186cfe3e18a3b091ff291f1"),
+    ([["fractal_terrain", "stepping_stones_terrain"], ["stepping_stones_terrain", "fractal_terrain"]], (6.0, 8.0), 0.25, 0.005, True,
+     {"fractal_terrain": {"levels": 5, "scale": 0.4}, "stepping_stones_terrain": {"stone_size": 0.75, "platform_size": 1.0}}, (49, 65),
+     "39563c94648b1014424e6aa6cf9683720f467e54d41389dcd4bdb2f1fc01fd0f"),
+    ([["stepping_stones_terrain", "fractal_terrain"]], (8.0, 5.0), 0.25, 0.005, True, None, (33, 41), "0dc8328f7c77657d57d11510016dc3d3e38843be330a6e39f3953b798bd78ef6"),
 ]
 
 
@@ -49,7 +53,7 @@ def test_generated_fields_match_the_reference_generators():
     xv = np.linspace(0.0, 3.0, 50)
     assert np.allclose(not_a_knot_spline(x, y, xv)[:, 0], xv**3 - 2 * xv, atol=2e-4)
     with pytest.raises(NotImplementedError):
-        build_subterrain_grid([["stepping_stones_terrain"]], (4.0, 4.0), 0.25, 0.005, False, None)
+        build_subterrain_grid([["lunar_terrain"]], (4.0, 4.0), 0.25, 0.005, False, None)
 
 
 def _grid_cfgs():

@@ -71,7 +71,7 @@ def test_dropin_modules_of_the_terrain_variant(hostemu_lib):
     g = TerrainManager({"enabled": True, "subterrain_types": [["flat_terrain"]]}, 4)  # grid mode: tests/test_terrain_grid.py
     assert not g.use_custom_heightmap and (g.n_rows, g.n_cols) == (1, 1) and g._flat_row_indices == [0] and g._height_field is None
     with pytest.raises(NotImplementedError):
-        TerrainManager({"enabled": True, "subterrain_types": [["fractal_terrain"]]}, 4)
+        TerrainManager({"enabled": True, "subterrain_types": [["lunar_terrain"]]}, 4)
     assert not TerrainManager({}, 4).enabled
 
 
