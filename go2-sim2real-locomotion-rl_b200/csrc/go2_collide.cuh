@@ -340,6 +340,9 @@ G2_HDN bool pair_contacts(const Go2Model& m, Phys& p, int ga, int gb, v3 nws, bo
 }
 
 // squared distance in the xy plane from point q to triangle (a, b, c); 0 inside
+#ifndef G2_SPHERE_CULL_3D
+#define G2_SPHERE_CULL_3D 1  // 0: only the horizontal footprint test (A/B, and the cross-check that the contacts are unchanged)
+#endif
 G2_HD float seg_dist2_xy(v3 q, v3 a, v3 b) {
     float ex = b.x - a.x, ey = b.y - a.y, px = q.x - a.x, py = q.y - a.y;
     float l2 = ex * ex + ey * ey;
@@ -353,6 +356,68 @@ G2_HD float tri_dist2_xy(v3 q, v3 a, v3 b, v3 c) {
     float s2 = (a.x - c.x) * (q.y - c.y) - (a.y - c.y) * (q.x - c.x);
     if ((s0 >= 0.0f && s1 >= 0.0f && s2 >= 0.0f) || (s0 <= 0.0f && s1 <= 0.0f && s2 <= 0.0f)) return 0.0f;
     return fminf(seg_dist2_xy(q, a, b), fminf(seg_dist2_xy(q, b, c), seg_dist2_xy(q, c, a)));
+}
+
+// Squared distance from point q to the triangle (a, b, c) in 3-D (closest point by Voronoi region)
+G2_HD float tri_dist2_3d(v3 q, v3 a, v3 b, v3 c) {
+    const v3 ab = b - a, ac = c - a, aq = q - a;
+    const float d1 = dot(ab, aq), d2 = dot(ac, aq);
+    v3 cp;
+    if (d1 <= 0.0f && d2 <= 0.0f) cp = a;
+    else {
+        const v3 bq = q - b;
+        const float d3 = dot(ab, bq), d4 = dot(ac, bq);
+        if (d3 >= 0.0f && d4 <= d3) cp = b;
+        else {
+            const float vc = d1 * d4 - d3 * d2;
+            if (vc <= 0.0f && d1 >= 0.0f && d3 <= 0.0f) cp = a + ab * (d1 / (d1 - d3));
+            else {
+                const v3 cq = q - c;
+                const float d5 = dot(ab, cq), d6 = dot(ac, cq);
+                if (d6 >= 0.0f && d5 <= d6) cp = c;
+                else {
+                    const float vb = d5 * d2 - d1 * d6;
+                    if (vb <= 0.0f && d2 >= 0.0f && d6 <= 0.0f) cp = a + ac * (d2 / (d2 - d6));
+                    else {
+                        const float va = d3 * d6 - d5 * d4;
+                        if (va <= 0.0f && (d4 - d3) >= 0.0f && (d5 - d6) >= 0.0f) cp = b + (c - b) * ((d4 - d3) / ((d4 - d3) + (d5 - d6)));
+                        else {
+                            const float den = 1.0f / (va + vb + vc);
+                            cp = a + ab * (vb * den) + ac * (vc * den);
+                        }
+                    }
+                }
+            }
+        }
+    }
+    const v3 e = q - cp;
+    return dot(e, e);
+}
+// Squared distance from point q to the prism under the triangle (a, b, c) (its top face; the prism goes straight down, far below q):
+// 0 inside; else the nearest boundary point is on the top face or on a side wall.  On the wall under edge (u, v) the nearest point
+// is level with q when q is not above the wall's top there - then the distance is the horizontal one.
+G2_HD float prism_wall_dist2(v3 q, v3 u, v3 v) {
+    const float ex = v.x - u.x, ey = v.y - u.y, px = q.x - u.x, py = q.y - u.y;
+    const float l2 = ex * ex + ey * ey;
+    const float t = l2 > 0.0f ? clampf((px * ex + py * ey) / l2, 0.0f, 1.0f) : 0.0f;
+    if (q.z > u.z + t * (v.z - u.z)) return 1e30f;  // above the wall's top: the top face / its edges are nearer
+    const float dx = px - t * ex, dy = py - t * ey;
+    return dx * dx + dy * dy;
+}
+G2_HD float prism_dist2(v3 q, v3 a, v3 b, v3 c) {
+    const float s0 = (b.x - a.x) * (q.y - a.y) - (b.y - a.y) * (q.x - a.x);
+    const float s1 = (c.x - b.x) * (q.y - b.y) - (c.y - b.y) * (q.x - b.x);
+    const float s2 = (a.x - c.x) * (q.y - c.y) - (a.y - c.y) * (q.x - c.x);
+    const bool inside_xy = (s0 >= 0.0f && s1 >= 0.0f && s2 >= 0.0f) || (s0 <= 0.0f && s1 <= 0.0f && s2 <= 0.0f);
+    if (inside_xy) {
+        const v3 nrm = cross(b - a, c - a);  // height of the top face above / below q along z
+        if (fabsf(nrm.z) > 1e-12f) {
+            const float ztop = a.z - (nrm.x * (q.x - a.x) + nrm.y * (q.y - a.y)) / nrm.z;
+            if (q.z <= ztop) return 0.0f;
+        }
+        return tri_dist2_3d(q, a, b, c);
+    }
+    return fminf(tri_dist2_3d(q, a, b, c), fminf(prism_wall_dist2(q, a, b), fminf(prism_wall_dist2(q, b, c), prism_wall_dist2(q, c, a))));
 }
 
 // Geom g against the heightfield terrain (collider/narrowphase.py:346-512 func_contact_mpr_terrain): the cells under
@@ -406,6 +471,7 @@ G2_HDN void terrain_contacts(const Go2Model& m, Phys& p, int g, float mu) {
     int n_con = 0, first = p.n_contacts;
     const bool sphere = m.g_type[g] == GEOM_SPHERE;
     const float sph_r2 = (m.g_size[g][0] + 1e-5f) * (m.g_size[g][0] + 1e-5f);
+    const float sph_r3 = (m.g_size[g][0] + 1e-4f) * (m.g_size[g][0] + 1e-4f);
     // Two passes per batch of candidates so that the lanes of a warp run MPR together: (1) walk the vertex strip of each row
     // (vertex n of row r = cell column c_min + (n-1)/2, row r + (n-1)%2) and record the prisms whose top reaches the geom's
     // lowest point; (2) rebuild each recorded prism and run MPR on it, in strip order (so duplicates and the contact cap
@@ -427,11 +493,15 @@ G2_HDN void terrain_contacts(const Go2Model& m, Phys& p, int g, float mu) {
                     // xy plane (MPR answers "no collision" for shapes separated along a horizontal axis): skips ~2/3 of the
                     // foot candidates, whose 2 x 2-cell footprint holds 8-12 prisms of which the foot touches 1-3
                     v3 t[3];
+                    const float hz[3] = {hA, hB, h};
                     for (int j = 0; j < 3; ++j) {
                         int vn = n - 2 + j;
-                        t[j] = mk3(sh * (float)(r + ((vn - 1) & 1)), sh * (float)(c_min + ((vn - 1) >> 1)), 0.0f);
+                        t[j] = mk3(sh * (float)(r + ((vn - 1) & 1)), sh * (float)(c_min + ((vn - 1) >> 1)), G2_SPHERE_CULL_3D ? hz[j] : 0.0f);
                     }
-                    keep = tri_dist2_xy(c.pa, t[0], t[1], t[2]) <= sph_r2;
+                    // ... and, exactly: only if the centre is within one radius (+ 0.1 mm) of the PRISM in 3-D.  A foot standing on
+                    // a tread is ~21 mm above it, so of the triangles inside its 22 mm footprint only those within ~7 mm of the
+                    // contact point can touch it.
+                    keep = G2_SPHERE_CULL_3D ? prism_dist2(c.pa, t[0], t[1], t[2]) <= sph_r3 : tri_dist2_xy(c.pa, t[0], t[1], t[2]) <= sph_r2;
                 }
                 if (keep) cand[ncand++] = (r << 12) | n;
             }
