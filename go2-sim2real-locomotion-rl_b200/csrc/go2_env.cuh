@@ -27,6 +27,15 @@ namespace go2 {
 #else
 #define G2_LDCG(p) (*(p))
 #endif
+// Per-env rows in global memory are touched once per tick: streaming (evict-first) accesses keep them from pushing the thread-local
+// working set out of L2 (-DG2_NO_STREAM_HINTS: plain accesses, for A/B)
+#if defined(__CUDA_ARCH__) && !defined(G2_NO_STREAM_HINTS)
+#define G2_ST(p, v) __stcs((p), (v))
+#define G2_LD(p) __ldcs(p)
+#else
+#define G2_ST(p, v) (*(p) = (v))
+#define G2_LD(p) (*(p))
+#endif
 enum RngSlot { SLOT_ACT_NOISE = 0, SLOT_OBS_NOISE = 8, SLOT_PUSH = 32, SLOT_CMD = 33, SLOT_CMD_RESET = 34, SLOT_RESET = 40, SLOT_LIDAR = 56 };
 
 struct EnvStepOut {
@@ -306,8 +315,8 @@ G2_HDN void reset_env(const Go2Model& m, const EnvConfig& cfg, const StepParams&
                 u4 r1 = rng4(rng, SLOT_RESET + k), r2 = rng4(rng, SLOT_RESET + 3 + k);
                 uint32_t a1[4] = {r1.a, r1.b, r1.c, r1.d}, a2[4] = {r2.a, r2.b, r2.c, r2.d};
                 for (int j = 0; j < 4; ++j) {
-                    if (cfg.has_kp_factor) F32(B_KP_FACTORS)[b * NHINGE + 4 * k + j] = rp ? rp[RP_KPF + 4 * k + j] : urange(sp.kpf_lo, sp.kpf_hi, a1[j]);
-                    if (cfg.has_kd_factor) F32(B_KD_FACTORS)[b * NHINGE + 4 * k + j] = rp ? rp[RP_KDF + 4 * k + j] : urange(sp.kdf_lo, sp.kdf_hi, a2[j]);
+                    if (cfg.has_kp_factor) G2_ST(F32(B_KP_FACTORS) + (b * NHINGE + 4 * k + j), rp ? rp[RP_KPF + 4 * k + j] : urange(sp.kpf_lo, sp.kpf_hi, a1[j]));
+                    if (cfg.has_kd_factor) G2_ST(F32(B_KD_FACTORS) + (b * NHINGE + 4 * k + j), rp ? rp[RP_KDF + 4 * k + j] : urange(sp.kdf_lo, sp.kdf_hi, a2[j]));
                 }
             }
         }
@@ -315,24 +324,24 @@ G2_HDN void reset_env(const Go2Model& m, const EnvConfig& cfg, const StepParams&
             u4 r = rng4(rng, SLOT_RESET + 11);
             float kp = rp ? rp[RP_KP] : urange(sp.kp_lo, sp.kp_hi, r.a), kd = rp ? rp[RP_KD] : urange(sp.kd_lo, sp.kd_hi, r.b);
             for (int j = 0; j < NHINGE; ++j) {
-                F32(B_EFF_KP)[b * NHINGE + j] = kp * F32(B_KP_FACTORS)[b * NHINGE + j];
-                F32(B_EFF_KD)[b * NHINGE + j] = kd * F32(B_KD_FACTORS)[b * NHINGE + j];
+                G2_ST(F32(B_EFF_KP) + (b * NHINGE + j), kp * F32(B_KP_FACTORS)[b * NHINGE + j]);
+                G2_ST(F32(B_EFF_KD) + (b * NHINGE + j), kd * F32(B_KD_FACTORS)[b * NHINGE + j]);
             }
         }
         if (cfg.has_motor_strength) {
             for (int k = 0; k < 3; ++k) {
                 u4 r = rng4(rng, SLOT_RESET + 6 + k);
                 uint32_t a[4] = {r.a, r.b, r.c, r.d};
-                for (int j = 0; j < 4; ++j) F32(B_MOTOR_STRENGTH)[b * NHINGE + 4 * k + j] = rp ? rp[RP_MS + 4 * k + j] : urange(sp.ms_lo, sp.ms_hi, a[j]);
+                for (int j = 0; j < 4; ++j) G2_ST(F32(B_MOTOR_STRENGTH) + (b * NHINGE + 4 * k + j), rp ? rp[RP_MS + 4 * k + j] : urange(sp.ms_lo, sp.ms_hi, a[j]));
             }
         }
         u4 rg = rng4(rng, SLOT_RESET + 9);
         if (cfg.has_gravity_offset) {
-            F32(B_GRAV_OFF)[b * 3 + 0] = rp ? rp[RP_GO + 0] : urange(sp.go_lo, sp.go_hi, rg.a);
-            F32(B_GRAV_OFF)[b * 3 + 1] = rp ? rp[RP_GO + 1] : urange(sp.go_lo, sp.go_hi, rg.b);
-            F32(B_GRAV_OFF)[b * 3 + 2] = rp ? rp[RP_GO + 2] : urange(sp.go_lo, sp.go_hi, rg.c);
+            G2_ST(F32(B_GRAV_OFF) + (b * 3 + 0), rp ? rp[RP_GO + 0] : urange(sp.go_lo, sp.go_hi, rg.a));
+            G2_ST(F32(B_GRAV_OFF) + (b * 3 + 1), rp ? rp[RP_GO + 1] : urange(sp.go_lo, sp.go_hi, rg.b));
+            G2_ST(F32(B_GRAV_OFF) + (b * 3 + 2), rp ? rp[RP_GO + 2] : urange(sp.go_lo, sp.go_hi, rg.c));
         }
-        I32(B_DELAY)[b] = rp ? (int)rp[RP_DELAY] : sp.delay_lo + (int)(rg.d % (uint32_t)(sp.delay_hi - sp.delay_lo + 1));
+        G2_ST(I32(B_DELAY) + (b), rp ? (int)rp[RP_DELAY] : sp.delay_lo + (int)(rg.d % (uint32_t)(sp.delay_hi - sp.delay_lo + 1)));
     }
     // joint + base state
     for (int j = 0; j < NHINGE; ++j) {
@@ -373,7 +382,7 @@ G2_HDN void reset_env(const Go2Model& m, const EnvConfig& cfg, const StepParams&
         e.base_pos.x = cfg.tm_safe_half_x > 0.0f ? add_nf(cx, mul_nf(ux * 2.0f - 1.0f, cfg.tm_safe_half_x)) : cx;  // torch: separate multiply and add
         e.base_pos.y = cfg.tm_safe_half_y > 0.0f ? add_nf(cy, mul_nf(uy * 2.0f - 1.0f, cfg.tm_safe_half_y)) : cy;
         e.base_pos.z = ground_height_bilinear(m, cfg, e.base_pos.x, e.base_pos.y) + cfg.base_init_pos[2] + cfg.tm_spawn_offset;
-        F32(B_SPAWN_POS)[b * 3] = e.base_pos.x; F32(B_SPAWN_POS)[b * 3 + 1] = e.base_pos.y; F32(B_SPAWN_POS)[b * 3 + 2] = e.base_pos.z;
+        G2_ST(F32(B_SPAWN_POS) + (b * 3), e.base_pos.x); G2_ST(F32(B_SPAWN_POS) + (b * 3 + 1), e.base_pos.y); G2_ST(F32(B_SPAWN_POS) + (b * 3 + 2), e.base_pos.z);
     } else if (cfg.has_init_z) e.base_pos.z = rp ? rp[RP_INIT_Z] : urange(cfg.init_z_lo, cfg.init_z_hi, rq.a);
     if (cfg.has_init_euler) {
         float roll = rp ? rp[RP_ROLL] : urange(cfg.init_euler_lo, cfg.init_euler_hi, rq.b);
@@ -390,15 +399,15 @@ G2_HDN void reset_env(const Go2Model& m, const EnvConfig& cfg, const StepParams&
     for (int j = 0; j < NHINGE; ++j) e.last_dof_vel[j] = 0.0f;
     if (cfg.kind != ENV_BASE) {
         for (int i = 0; i < A; ++i) e.applied[i] = 0.0f;
-        for (int i = 0; i < cfg.hist_size * A; ++i) F32(B_HIST)[b * cfg.hist_size * A + i] = 0.0f;
+        for (int i = 0; i < cfg.hist_size * A; ++i) G2_ST(F32(B_HIST) + (b * cfg.hist_size * A + i), 0.0f);
         if (cfg.has_push) {
-            F32(B_PUSH_FORCE)[b * 3 + 0] = F32(B_PUSH_FORCE)[b * 3 + 1] = F32(B_PUSH_FORCE)[b * 3 + 2] = 0.0f;
-            I32(B_PUSH_REMAIN)[b] = 0;
+            G2_ST(F32(B_PUSH_FORCE) + (b * 3 + 0), F32(B_PUSH_FORCE)[b * 3 + 1] = F32(B_PUSH_FORCE)[b * 3 + 2] = 0.0f);
+            G2_ST(I32(B_PUSH_REMAIN) + (b), 0);
         }
         for (int i = 0; i < 4; ++i) { e.air[i] = 0.0f; e.fc[i] = 0; e.lfc[i] = 0; }
         e.last_x = e.base_pos.x;  // stair: forward_progress restarts at the spawn (go2_env_stair.py:1568)
         if (G2_LIDAR_ON(cfg))  // go2_env_stair_lidar.py: reset_idx zeroes the scan buffers of the reset envs
-            for (int i = 0; i < cfg.n_actor_scan; ++i) F32(B_ACTOR_SCAN)[(size_t)b * cfg.n_actor_scan + i] = 0.0f;
+            for (int i = 0; i < cfg.n_actor_scan; ++i) G2_ST(F32(B_ACTOR_SCAN) + ((size_t)b * cfg.n_actor_scan + i), 0.0f);
     }
     // episode statistics, then clear the sums
     float ep_s = fmaxf((float)e.ep_len, 1.0f) * dt;
@@ -407,7 +416,7 @@ G2_HDN void reset_env(const Go2Model& m, const EnvConfig& cfg, const StepParams&
         float s = F32(B_EP_SUMS)[b * cfg.n_rew + k];
         out.ep_stat[k] = cfg.kind == ENV_BASE ? s : s / ep_s;
         if (cfg.rew_id[k] == R_TRACKING_LIN_VEL || cfg.rew_id[k] == R_TRACKING_ANG_VEL) out.tracking_per_sec += s / ep_s;
-        F32(B_EP_SUMS)[b * cfg.n_rew + k] = 0.0f;
+        G2_ST(F32(B_EP_SUMS) + (b * cfg.n_rew + k), 0.0f);
     }
     e.ep_len = 0;
     resample_commands(cfg, sp, rng, SLOT_CMD_RESET, cfg.env_offset + b, e.cmd, rp ? rp + RP_CMD_RESET : nullptr);
@@ -494,8 +503,8 @@ G2_HDN void env_pre(const Go2Model& m, const EnvConfig& cfg, const StepParams& s
                         float kd = 0.2f * sqrtf(kp);
                         ekp = kp * F32(B_KP_FACTORS)[b * NHINGE + j] * F32(B_MOTOR_STRENGTH)[b * NHINGE + j];
                         ekd = kd * F32(B_KD_FACTORS)[b * NHINGE + j];
-                        F32(B_EFF_KP)[b * NHINGE + j] = ekp;
-                        F32(B_EFF_KD)[b * NHINGE + j] = ekd;
+                        G2_ST(F32(B_EFF_KP) + (b * NHINGE + j), ekp);
+                        G2_ST(F32(B_EFF_KD) + (b * NHINGE + j), ekd);
                     } else {
                         ekp = F32(B_EFF_KP)[b * NHINGE + j];
                         ekd = F32(B_EFF_KD)[b * NHINGE + j];
@@ -510,20 +519,20 @@ G2_HDN void env_pre(const Go2Model& m, const EnvConfig& cfg, const StepParams& s
             if (cfg.has_push && sp.push_enable) {
                 if (sp.push_resample) {
                     u4 r = rng4(rng, SLOT_PUSH);
-                    F32(B_PUSH_FORCE)[b * 3 + 0] = rp ? rp[RP_PUSH] : urange(sp.push_lo, sp.push_hi, r.a);
-                    F32(B_PUSH_FORCE)[b * 3 + 1] = rp ? rp[RP_PUSH + 1] : urange(sp.push_lo, sp.push_hi, r.b);
-                    F32(B_PUSH_FORCE)[b * 3 + 2] = 0.0f;
-                    I32(B_PUSH_REMAIN)[b] = rp ? (int)rp[RP_PUSH + 2] : cfg.push_dur_lo + (int)(r.c % (uint32_t)(cfg.push_dur_hi - cfg.push_dur_lo + 1));
+                    G2_ST(F32(B_PUSH_FORCE) + (b * 3 + 0), rp ? rp[RP_PUSH] : urange(sp.push_lo, sp.push_hi, r.a));
+                    G2_ST(F32(B_PUSH_FORCE) + (b * 3 + 1), rp ? rp[RP_PUSH + 1] : urange(sp.push_lo, sp.push_hi, r.b));
+                    G2_ST(F32(B_PUSH_FORCE) + (b * 3 + 2), 0.0f);
+                    G2_ST(I32(B_PUSH_REMAIN) + (b), rp ? (int)rp[RP_PUSH + 2] : cfg.push_dur_lo + (int)(r.c % (uint32_t)(cfg.push_dur_hi - cfg.push_dur_lo + 1)));
                 }
                 int rem = I32(B_PUSH_REMAIN)[b];
                 float on = rem > 0 ? 1.0f : 0.0f;
                 cur = mk3(F32(B_PUSH_FORCE)[b * 3] * on, F32(B_PUSH_FORCE)[b * 3 + 1] * on, F32(B_PUSH_FORCE)[b * 3 + 2] * on);
-                I32(B_PUSH_REMAIN)[b] = rem - 1 > 0 ? rem - 1 : 0;
+                G2_ST(I32(B_PUSH_REMAIN) + (b), rem - 1 > 0 ? rem - 1 : 0);
                 p.ext_link = cfg.push_link;
                 p.ext_f = cur;
                 p.ext_t = cross(p.lpos[cfg.push_link] - p.root_com, cur);
             }
-            if (cfg.has_push) { F32(B_CUR_PUSH)[b * 3] = cur.x; F32(B_CUR_PUSH)[b * 3 + 1] = cur.y; F32(B_CUR_PUSH)[b * 3 + 2] = cur.z; }
+            if (cfg.has_push) { G2_ST(F32(B_CUR_PUSH) + (b * 3), cur.x); G2_ST(F32(B_CUR_PUSH) + (b * 3 + 1), cur.y); G2_ST(F32(B_CUR_PUSH) + (b * 3 + 2), cur.z); }
         } else {
             // base env: 1-step latency through last_actions, PD evaluated inside every substep
             p.pd_mode = 1; p.pd_kp = sp.kp_genesis; p.pd_kv = sp.kd_genesis;
@@ -651,7 +660,7 @@ G2_HDN void stair_info_update(const Go2Model& m, const EnvConfig& cfg, const Ste
 G2_HD void stair_priv_tail(const Go2Model& m, const EnvConfig& cfg, float* pr, int k, int terrain_row, v3 base_pos, q4 q, bool was_reset) {
     if (k < cfg.num_priv) {
         int den = cfg.n_terrain_rows - 1 > 1 ? cfg.n_terrain_rows - 1 : 1;
-        pr[k++] = cfg.has_terrain ? (float)terrain_row / (float)den : 0.0f;
+        G2_ST(pr + (k++), cfg.has_terrain ? (float)terrain_row / (float)den : 0.0f);
     }
     float cy, sy;
     yaw_cs(q, cy, sy);
@@ -659,18 +668,18 @@ G2_HD void stair_priv_tail(const Go2Model& m, const EnvConfig& cfg, float* pr, i
         if (k + 4 <= cfg.num_priv) {
             float edge = 0.0f, dir = 0.0f;
             if (!was_reset) stair_edge(m, cfg, base_pos, q, edge, dir);
-            pr[k++] = was_reset ? 0.0f : edge * cfg.si_scale[0];
-            pr[k++] = was_reset ? 0.0f : cfg.si_row_height[terrain_row] * cfg.si_scale[1];
-            pr[k++] = was_reset ? 0.0f : cfg.si_row_depth[terrain_row] * cfg.si_scale[2];
-            pr[k++] = was_reset ? 0.0f : dir * cfg.si_scale[3];
+            G2_ST(pr + (k++), was_reset ? 0.0f : edge * cfg.si_scale[0]);
+            G2_ST(pr + (k++), was_reset ? 0.0f : cfg.si_row_height[terrain_row] * cfg.si_scale[1]);
+            G2_ST(pr + (k++), was_reset ? 0.0f : cfg.si_row_depth[terrain_row] * cfg.si_scale[2]);
+            G2_ST(pr + (k++), was_reset ? 0.0f : dir * cfg.si_scale[3]);
         }
         return;
     }
     if (G2_LIDAR_ON(cfg)) {
         if (cfg.n_critic_scan > 0 && k + cfg.n_critic_scan <= cfg.num_priv)
             for (int i = 0; i < cfg.n_critic_scan; ++i)
-                pr[k++] = was_reset ? 0.0f
-                                    : clampf(lidar_point(m, cfg, base_pos, cy, sy, cfg.critic_lx[i], cfg.critic_ly[i]), -cfg.lidar_clip, cfg.lidar_clip) * cfg.lidar_scale;
+                G2_ST(pr + (k++), was_reset ? 0.0f
+                                    : clampf(lidar_point(m, cfg, base_pos, cy, sy, cfg.critic_lx[i], cfg.critic_ly[i]), -cfg.lidar_clip, cfg.lidar_clip) * cfg.lidar_scale);
         return;
     }
     int ns = cfg.scan_nx * cfg.scan_ny;
@@ -680,7 +689,7 @@ G2_HD void stair_priv_tail(const Go2Model& m, const EnvConfig& cfg, float* pr, i
             for (int iy = 0; iy < cfg.scan_ny; ++iy) {
                 float ly = cfg.scan_ny > 1 ? cfg.scan_y0 + (cfg.scan_y1 - cfg.scan_y0) * (float)iy / (float)(cfg.scan_ny - 1) : cfg.scan_y0;
                 float wx = base_pos.x + cy * lx - sy * ly, wy = base_pos.y + sy * lx + cy * ly;
-                pr[k++] = cfg.has_terrain ? terrain_height(m, wx, wy) - base_pos.z : 0.0f;
+                G2_ST(pr + (k++), cfg.has_terrain ? terrain_height(m, wx, wy) - base_pos.z : 0.0f);
             }
         }
     }
@@ -722,7 +731,7 @@ G2_HDN void env_post(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
         }
         if (cfg.tm_on) {  // go2_env_Omni_kplearn_varied_terrain.py: _ground_height[:] = terrain.get_height_at_robot(base_pos[:, :2])
             e.ground_h = ground_height_bilinear(m, cfg, e.base_pos.x, e.base_pos.y);
-            F32(B_GROUND_H)[b] = e.ground_h;
+            G2_ST(F32(B_GROUND_H) + (b), e.ground_h);
         }
         if (e.ep_len % cfg.resample_steps == 0) resample_commands(cfg, sp, rng, SLOT_CMD, cfg.env_offset + b, e.cmd, rp ? rp + RP_CMD : nullptr);
     } else {
@@ -764,7 +773,7 @@ G2_HDN void env_post(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
                 float r = reward_term(cfg.rew_id[k], m, cfg, p, e) * cfg.rew_scale[k];
                 rew += r;
                 F32(B_EP_SUMS)[b * cfg.n_rew + k] += r;
-                if (cfg.export_rew_terms) F32(B_REW_TERMS)[b * cfg.n_rew + k] = r;
+                if (cfg.export_rew_terms) G2_ST(F32(B_REW_TERMS) + (b * cfg.n_rew + k), r);
             }
         }
     } else {
@@ -773,7 +782,7 @@ G2_HDN void env_post(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
                 float r = reward_term(cfg.rew_id[k], m, cfg, p, e) * cfg.rew_scale[k];
                 rew += r;
                 F32(B_EP_SUMS)[b * cfg.n_rew + k] += r;
-                if (cfg.export_rew_terms) F32(B_REW_TERMS)[b * cfg.n_rew + k] = r;
+                if (cfg.export_rew_terms) G2_ST(F32(B_REW_TERMS) + (b * cfg.n_rew + k), r);
             }
         }
         if (rst) reset_env(m, cfg, sp, bf, b, rng, p, e, out);
@@ -808,72 +817,72 @@ G2_HDN void env_post(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
             }
         }
         const int n_scan = G2_LIDAR_ON(cfg) ? cfg.n_actor_scan : 0, n_prop = cfg.num_obs - n_scan;
-        for (int i = 0; i < n_prop; ++i) obs[i] = o[i];
-        for (int i = 0; i < n_scan; ++i) obs[n_prop + i] = F32(B_ACTOR_SCAN)[(size_t)b * n_scan + i];  // go2_env_stair_lidar.py:1626-1627
+        for (int i = 0; i < n_prop; ++i) G2_ST(obs + i, o[i]);
+        for (int i = 0; i < n_scan; ++i) G2_ST(obs + n_prop + i, F32(B_ACTOR_SCAN)[(size_t)b * n_scan + i]);  // go2_env_stair_lidar.py:1626-1627
         if (cfg.num_priv > 0) {  // go2_env_walk.py:1115-1141
             float* pr = F32(B_PRIV) + (size_t)b * cfg.num_priv;
             int k = 0;
-            for (int i = 0; i < cfg.num_obs; ++i) pr[k++] = obs[i];
-            pr[k++] = e.lin_vel.x * cfg.obs_scale_lin_vel; pr[k++] = e.lin_vel.y * cfg.obs_scale_lin_vel; pr[k++] = e.lin_vel.z * cfg.obs_scale_lin_vel;
-            pr[k++] = gl[G_FRIC_GROUND];  // patched by the post-pass kernel when this tick's resets change the global DR
-            for (int j = 0; j < NHINGE; ++j) pr[k++] = F32(B_KP_FACTORS)[b * NHINGE + j];
-            for (int j = 0; j < NHINGE; ++j) pr[k++] = F32(B_KD_FACTORS)[b * NHINGE + j];
-            for (int j = 0; j < NHINGE; ++j) pr[k++] = F32(B_MOTOR_STRENGTH)[b * NHINGE + j];
-            pr[k++] = gl[G_MASS_SHIFT];
-            pr[k++] = gl[G_COM_SHIFT]; pr[k++] = gl[G_COM_SHIFT + 1]; pr[k++] = gl[G_COM_SHIFT + 2];
+            for (int i = 0; i < cfg.num_obs; ++i) G2_ST(pr + (k++), obs[i]);
+            G2_ST(pr + (k++), e.lin_vel.x * cfg.obs_scale_lin_vel); G2_ST(pr + (k++), e.lin_vel.y * cfg.obs_scale_lin_vel); G2_ST(pr + (k++), e.lin_vel.z * cfg.obs_scale_lin_vel);
+            G2_ST(pr + (k++), gl[G_FRIC_GROUND]);  // patched by the post-pass kernel when this tick's resets change the global DR
+            for (int j = 0; j < NHINGE; ++j) G2_ST(pr + (k++), F32(B_KP_FACTORS)[b * NHINGE + j]);
+            for (int j = 0; j < NHINGE; ++j) G2_ST(pr + (k++), F32(B_KD_FACTORS)[b * NHINGE + j]);
+            for (int j = 0; j < NHINGE; ++j) G2_ST(pr + (k++), F32(B_MOTOR_STRENGTH)[b * NHINGE + j]);
+            G2_ST(pr + (k++), gl[G_MASS_SHIFT]);
+            G2_ST(pr + (k++), gl[G_COM_SHIFT]); G2_ST(pr + (k++), gl[G_COM_SHIFT + 1]); G2_ST(pr + (k++), gl[G_COM_SHIFT + 2]);
             // leg mass shifts in cfg order FR, FL, RR, RL (robot links 2, 1, 4, 3)
-            for (int i = 0; i < 4; ++i) pr[k++] = cfg.has_leg_mass_dr ? gl[G_MASS_SHIFT + cfg.hip_link[i]] : 0.0f;
-            pr[k++] = go[0]; pr[k++] = go[1]; pr[k++] = go[2];
-            pr[k++] = F32(B_CUR_PUSH)[b * 3]; pr[k++] = F32(B_CUR_PUSH)[b * 3 + 1]; pr[k++] = F32(B_CUR_PUSH)[b * 3 + 2];
-            pr[k++] = cfg.max_delay > 0 ? (float)I32(B_DELAY)[b] / (float)cfg.max_delay : 0.0f;
-            if (cfg.tm_variant && k < cfg.num_priv) pr[k++] = cfg.tm_on ? e.ground_h : 0.0f;  // go2_env_terrain.py:1139-1141
+            for (int i = 0; i < 4; ++i) G2_ST(pr + (k++), cfg.has_leg_mass_dr ? gl[G_MASS_SHIFT + cfg.hip_link[i]] : 0.0f);
+            G2_ST(pr + (k++), go[0]); G2_ST(pr + (k++), go[1]); G2_ST(pr + (k++), go[2]);
+            G2_ST(pr + (k++), F32(B_CUR_PUSH)[b * 3]); G2_ST(pr + (k++), F32(B_CUR_PUSH)[b * 3 + 1]); G2_ST(pr + (k++), F32(B_CUR_PUSH)[b * 3 + 2]);
+            G2_ST(pr + (k++), cfg.max_delay > 0 ? (float)I32(B_DELAY)[b] / (float)cfg.max_delay : 0.0f);
+            if (cfg.tm_variant && k < cfg.num_priv) G2_ST(pr + (k++), cfg.tm_on ? e.ground_h : 0.0f);  // go2_env_terrain.py:1139-1141
             if (cfg.kind == ENV_STAIR)
                 stair_priv_tail(m, cfg, pr, k, e.terrain_row, G2_LIDAR_ON(cfg) ? lid_pos : e.base_pos, G2_LIDAR_ON(cfg) ? lid_q : e.base_quat, rst);
         }
-        F32(B_REW)[b] = rew;
+        G2_ST(F32(B_REW) + (b), rew);
         for (int i = 0; i < A; ++i) e.last_act[i] = e.act[i];
         for (int j = 0; j < NHINGE; ++j) e.last_dof_vel[j] = e.dof_vel[j];
     }
 
     // ---- write back
-    U8(B_RESET)[b] = rst ? 1 : 0;
+    G2_ST(U8(B_RESET) + (b), rst ? 1 : 0);
     U8(B_FK_FRESH)[b] = rst ? 1 : 0;
-    F32(B_TIMEOUT)[b] = tout ? 1.0f : 0.0f;
-    I32(B_EP_LEN)[b] = e.ep_len;
-    F32(B_LAST_X)[b] = e.last_x;
-    I32(B_TERRAIN_ROW)[b] = e.terrain_row;
+    G2_ST(F32(B_TIMEOUT) + (b), tout ? 1.0f : 0.0f);
+    G2_ST(I32(B_EP_LEN) + (b), e.ep_len);
+    G2_ST(F32(B_LAST_X) + (b), e.last_x);
+    G2_ST(I32(B_TERRAIN_ROW) + (b), e.terrain_row);
     I32(B_ERRNO)[b] |= p.err;
-    I32(B_NCONTACT)[b] = p.n_contacts;
-    I32(B_NNEWTON)[b] = p.n_newton;
-    for (int i = 0; i < 3; ++i) F32(B_COMMANDS)[b * 3 + i] = e.cmd[i];
+    G2_ST(I32(B_NCONTACT) + (b), p.n_contacts);
+    G2_ST(I32(B_NNEWTON) + (b), p.n_newton);
+    for (int i = 0; i < 3; ++i) G2_ST(F32(B_COMMANDS) + (b * 3 + i), e.cmd[i]);
     for (int i = 0; i < A; ++i) {
-        F32(B_LAST_ACTIONS)[b * A + i] = e.last_act[i];
-        if (cfg.kind != ENV_BASE) F32(B_APPLIED)[b * A + i] = e.applied[i];
+        G2_ST(F32(B_LAST_ACTIONS) + (b * A + i), e.last_act[i]);
+        if (cfg.kind != ENV_BASE) G2_ST(F32(B_APPLIED) + (b * A + i), e.applied[i]);
     }
     for (int j = 0; j < NHINGE; ++j) {
-        F32(B_DOF_POS)[b * NHINGE + j] = e.dof_pos[j];
-        F32(B_DOF_VEL)[b * NHINGE + j] = e.dof_vel[j];
-        F32(B_LAST_DOF_VEL)[b * NHINGE + j] = e.last_dof_vel[j];
-        F32(B_TARGET)[b * NHINGE + j] = e.target[j];
-        F32(B_TORQUE)[b * NHINGE + j] = e.torque[j];
+        G2_ST(F32(B_DOF_POS) + (b * NHINGE + j), e.dof_pos[j]);
+        G2_ST(F32(B_DOF_VEL) + (b * NHINGE + j), e.dof_vel[j]);
+        G2_ST(F32(B_LAST_DOF_VEL) + (b * NHINGE + j), e.last_dof_vel[j]);
+        G2_ST(F32(B_TARGET) + (b * NHINGE + j), e.target[j]);
+        G2_ST(F32(B_TORQUE) + (b * NHINGE + j), e.torque[j]);
     }
-    F32(B_BASE_POS)[b * 3] = e.base_pos.x; F32(B_BASE_POS)[b * 3 + 1] = e.base_pos.y; F32(B_BASE_POS)[b * 3 + 2] = e.base_pos.z;
-    F32(B_BASE_QUAT)[b * 4] = e.base_quat.w; F32(B_BASE_QUAT)[b * 4 + 1] = e.base_quat.x; F32(B_BASE_QUAT)[b * 4 + 2] = e.base_quat.y; F32(B_BASE_QUAT)[b * 4 + 3] = e.base_quat.z;
-    F32(B_BASE_LIN_VEL)[b * 3] = e.lin_vel.x; F32(B_BASE_LIN_VEL)[b * 3 + 1] = e.lin_vel.y; F32(B_BASE_LIN_VEL)[b * 3 + 2] = e.lin_vel.z;
-    F32(B_BASE_ANG_VEL)[b * 3] = e.ang_vel.x; F32(B_BASE_ANG_VEL)[b * 3 + 1] = e.ang_vel.y; F32(B_BASE_ANG_VEL)[b * 3 + 2] = e.ang_vel.z;
-    F32(B_PROJ_G)[b * 3] = e.proj_g.x; F32(B_PROJ_G)[b * 3 + 1] = e.proj_g.y; F32(B_PROJ_G)[b * 3 + 2] = e.proj_g.z;
-    F32(B_BASE_EULER)[b * 3] = e.euler.x; F32(B_BASE_EULER)[b * 3 + 1] = e.euler.y; F32(B_BASE_EULER)[b * 3 + 2] = e.euler.z;
+    G2_ST(F32(B_BASE_POS) + (b * 3), e.base_pos.x); G2_ST(F32(B_BASE_POS) + (b * 3 + 1), e.base_pos.y); G2_ST(F32(B_BASE_POS) + (b * 3 + 2), e.base_pos.z);
+    G2_ST(F32(B_BASE_QUAT) + (b * 4), e.base_quat.w); G2_ST(F32(B_BASE_QUAT) + (b * 4 + 1), e.base_quat.x); G2_ST(F32(B_BASE_QUAT) + (b * 4 + 2), e.base_quat.y); G2_ST(F32(B_BASE_QUAT) + (b * 4 + 3), e.base_quat.z);
+    G2_ST(F32(B_BASE_LIN_VEL) + (b * 3), e.lin_vel.x); G2_ST(F32(B_BASE_LIN_VEL) + (b * 3 + 1), e.lin_vel.y); G2_ST(F32(B_BASE_LIN_VEL) + (b * 3 + 2), e.lin_vel.z);
+    G2_ST(F32(B_BASE_ANG_VEL) + (b * 3), e.ang_vel.x); G2_ST(F32(B_BASE_ANG_VEL) + (b * 3 + 1), e.ang_vel.y); G2_ST(F32(B_BASE_ANG_VEL) + (b * 3 + 2), e.ang_vel.z);
+    G2_ST(F32(B_PROJ_G) + (b * 3), e.proj_g.x); G2_ST(F32(B_PROJ_G) + (b * 3 + 1), e.proj_g.y); G2_ST(F32(B_PROJ_G) + (b * 3 + 2), e.proj_g.z);
+    G2_ST(F32(B_BASE_EULER) + (b * 3), e.euler.x); G2_ST(F32(B_BASE_EULER) + (b * 3 + 1), e.euler.y); G2_ST(F32(B_BASE_EULER) + (b * 3 + 2), e.euler.z);
     if (cfg.has_foot_tracking) {
         for (int i = 0; i < 4; ++i) {
-            F32(B_AIR_TIME)[b * 4 + i] = e.air[i];
-            U8(B_FOOT_CONTACT)[b * 4 + i] = (uint8_t)e.fc[i];
-            U8(B_LAST_FOOT_CONTACT)[b * 4 + i] = (uint8_t)e.lfc[i];
+            G2_ST(F32(B_AIR_TIME) + (b * 4 + i), e.air[i]);
+            G2_ST(U8(B_FOOT_CONTACT) + (b * 4 + i), (uint8_t)e.fc[i]);
+            G2_ST(U8(B_LAST_FOOT_CONTACT) + (b * 4 + i), (uint8_t)e.lfc[i]);
         }
     }
     for (int l = 0; l < NLINK; ++l) {
-        F32(B_CONTACT_FORCE)[(b * NLINK + l) * 3] = p.cforce[l].x;
-        F32(B_CONTACT_FORCE)[(b * NLINK + l) * 3 + 1] = p.cforce[l].y;
-        F32(B_CONTACT_FORCE)[(b * NLINK + l) * 3 + 2] = p.cforce[l].z;
+        G2_ST(F32(B_CONTACT_FORCE) + (b * NLINK + l) * 3, p.cforce[l].x);
+        G2_ST(F32(B_CONTACT_FORCE) + (b * NLINK + l) * 3 + 1, p.cforce[l].y);
+        G2_ST(F32(B_CONTACT_FORCE) + (b * NLINK + l) * 3 + 2, p.cforce[l].z);
     }
 }
 
@@ -882,9 +891,9 @@ G2_HDN void env_post(const Go2Model& m, const EnvConfig& cfg, const StepParams& 
 // private working set (registers + thread-local memory).  Persistent physics state is env-major in HBM.
 // ---------------------------------------------------------------------------------------------------
 G2_HD void load_phys(const Buffers& bf, int b, Phys& p) {
-    for (int i = 0; i < NQ; ++i) p.qpos[i] = F32(B_QPOS)[b * NQ + i];
-    for (int i = 0; i < NV; ++i) p.qvel[i] = F32(B_QVEL)[b * NV + i];
-    for (int i = 0; i < NV; ++i) p.qacc_ws[i] = F32(B_QACC_WS)[b * NV + i];
+    for (int i = 0; i < NQ; ++i) p.qpos[i] = G2_LD(F32(B_QPOS) + b * NQ + i);
+    for (int i = 0; i < NV; ++i) p.qvel[i] = G2_LD(F32(B_QVEL) + b * NV + i);
+    for (int i = 0; i < NV; ++i) p.qacc_ws[i] = G2_LD(F32(B_QACC_WS) + b * NV + i);
     p.warm = I32(B_WARM)[b];
     int nc = I32(B_NCACHE)[b];
     p.n_cache = nc;
@@ -903,13 +912,13 @@ G2_HD void load_phys(const Buffers& bf, int b, Phys& p) {
     p.n_newton = 0;
 }
 G2_HD void store_phys(const Buffers& bf, int b, const Phys& p) {
-    for (int i = 0; i < NQ; ++i) F32(B_QPOS)[b * NQ + i] = p.qpos[i];
-    for (int i = 0; i < NV; ++i) F32(B_QVEL)[b * NV + i] = p.qvel[i];
-    for (int i = 0; i < NV; ++i) F32(B_QACC_WS)[b * NV + i] = p.qacc_ws[i];
-    I32(B_WARM)[b] = p.warm;
-    I32(B_NCACHE)[b] = p.n_cache;
+    for (int i = 0; i < NQ; ++i) G2_ST(F32(B_QPOS) + b * NQ + i, p.qpos[i]);
+    for (int i = 0; i < NV; ++i) G2_ST(F32(B_QVEL) + b * NV + i, p.qvel[i]);
+    for (int i = 0; i < NV; ++i) G2_ST(F32(B_QACC_WS) + b * NV + i, p.qacc_ws[i]);
+    G2_ST(I32(B_WARM) + (b), p.warm);
+    G2_ST(I32(B_NCACHE) + (b), p.n_cache);
     for (int k = 0; k < p.n_cache; ++k) {
-        I32(B_CACHE_PAIR)[b * MAX_CPAIRS + k] = p.cache_pair[k];
+        G2_ST(I32(B_CACHE_PAIR) + (b * MAX_CPAIRS + k), p.cache_pair[k]);
         float* cn = F32(B_CACHE_N) + (size_t)b * MAX_CPAIRS * 3 + 3 * k;
         cn[0] = p.cache_n[k].x; cn[1] = p.cache_n[k].y; cn[2] = p.cache_n[k].z;
     }
@@ -1051,9 +1060,9 @@ G2_HD void post_patch_priv(const EnvConfig& cfg, const float* g, float* pr) {
     int k = cfg.num_obs + 3;
     pr[k] = g[G_FRIC_GROUND];
     k += 1 + 3 * NHINGE;
-    pr[k++] = g[G_MASS_SHIFT];
-    pr[k++] = g[G_COM_SHIFT]; pr[k++] = g[G_COM_SHIFT + 1]; pr[k++] = g[G_COM_SHIFT + 2];
-    for (int i = 0; i < 4; ++i) pr[k++] = cfg.has_leg_mass_dr ? g[G_MASS_SHIFT + cfg.hip_link[i]] : 0.0f;
+    G2_ST(pr + (k++), g[G_MASS_SHIFT]);
+    G2_ST(pr + (k++), g[G_COM_SHIFT]); G2_ST(pr + (k++), g[G_COM_SHIFT + 1]); G2_ST(pr + (k++), g[G_COM_SHIFT + 2]);
+    for (int i = 0; i < 4; ++i) G2_ST(pr + (k++), cfg.has_leg_mass_dr ? g[G_MASS_SHIFT + cfg.hip_link[i]] : 0.0f);
 }
 
 // Post-pass, stair env: the row of every env reset in this tick is redrawn with the tick's true reset count n (all ranks) -
@@ -1074,10 +1083,10 @@ G2_HD void post_stair_rows(const Go2Model& m, const EnvConfig& cfg, const StepPa
         u4 rq = rng4(rng, SLOT_RESET + 10);
         pos.z = pos.z + urange(cfg.init_z_lo, cfg.init_z_hi, rq.a) - cfg.base_init_pos[2] + cfg.base_init_pos[2];
     }
-    I32(B_TERRAIN_ROW)[b] = row;
-    F32(B_QPOS)[b * NQ] = pos.x; F32(B_QPOS)[b * NQ + 1] = pos.y; F32(B_QPOS)[b * NQ + 2] = pos.z;
-    F32(B_BASE_POS)[b * 3] = pos.x; F32(B_BASE_POS)[b * 3 + 1] = pos.y; F32(B_BASE_POS)[b * 3 + 2] = pos.z;
-    F32(B_LAST_X)[b] = pos.x;
+    G2_ST(I32(B_TERRAIN_ROW) + (b), row);
+    G2_ST(F32(B_QPOS) + (b * NQ), pos.x); G2_ST(F32(B_QPOS) + (b * NQ + 1), pos.y); G2_ST(F32(B_QPOS) + (b * NQ + 2), pos.z);
+    G2_ST(F32(B_BASE_POS) + (b * 3), pos.x); G2_ST(F32(B_BASE_POS) + (b * 3 + 1), pos.y); G2_ST(F32(B_BASE_POS) + (b * 3 + 2), pos.z);
+    G2_ST(F32(B_LAST_X) + (b), pos.x);
     if (cfg.num_priv > 0)
         stair_priv_tail(m, cfg, F32(B_PRIV) + (size_t)b * cfg.num_priv, cfg.num_obs + 55, row, pos, ld4(F32(B_BASE_QUAT) + b * 4), true);
 }
