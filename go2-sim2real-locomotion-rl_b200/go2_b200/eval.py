@@ -55,10 +55,11 @@ def eval_cfgs(cfgs, terminate=False, kp=None, kd=None):
     return env_cfg, obs_cfg, reward_cfg, command_cfg
 
 
-def respawn(env, envs_idx, terrain_row=None):
+def respawn(env, envs_idx, terrain_row=None, tile=None):
     """Put the given envs back on their spawn point with the default pose and cleared action buffers: `respawn_at_start` of
     go2_eval_stairs.py:314-361 (spawn = centre of the env's terrain row + base height) and the flat-ground branch of
-    `respawn_on_tile` of go2_eval_walk.py:399-413,471-488, for any set of envs.  `terrain_row` moves them to that row first."""
+    `respawn_on_tile` of go2_eval_walk.py:399-488 (flat ground, tile grid: centre of tile `tile` = (row, col), custom height map: map
+    centre), for any set of envs.  `terrain_row` moves them to that stair row first."""
     ii = torch.as_tensor(envs_idx, device=env.device).long().reshape(-1)
     n = int(ii.numel())
     if n == 0:
@@ -71,8 +72,15 @@ def respawn(env, envs_idx, terrain_row=None):
         spawn = centers[env._env_terrain_row[ii].long()].clone()
         spawn[:, 2] += env.base_init_pos[2]
     T = getattr(env, "terrain", None)
-    if T is not None and T.enabled:  # custom height map (go2_eval_walk.py:441-464): map centre, on top of the interpolated ground
-        xy = torch.zeros(n, 2, device=env.device)
+    if T is not None and T.enabled:
+        xy = torch.zeros(n, 2, device=env.device)  # custom height map (go2_eval_walk.py:441-464): map centre, on top of the interpolated ground
+        if getattr(T, "_tile_centers", None) is not None:  # tile grid (:417-439): centre of the (clamped) tile; tile=None keeps each env's tile
+            if tile is not None:
+                r = torch.full((n,), min(int(tile[0]), T.n_rows - 1), device=env.device, dtype=torch.long)
+                c = torch.full((n,), min(int(tile[1]), T.n_cols - 1), device=env.device, dtype=torch.long)
+            else:
+                r, c = T._env_tile_row[ii], T._env_tile_col[ii]
+            xy = T._tile_centers.to(env.device)[r, c, :2].clone()
         spawn = torch.cat([xy, (T._query_height_batch(xy[:, 0], xy[:, 1]) + float(env.base_init_pos[2]) + T.spawn_height_offset)[:, None]], 1)
         T._env_spawn_pos[ii] = spawn
     env.dof_pos[ii] = env.default_dof_pos

@@ -104,3 +104,24 @@ def test_grid_spawn_blind_heights_and_boundary(backend, hostemu_lib):
     old = T._env_spawn_pos[7].clone()
     _, _, done, _ = env.step(zero)
     assert bool(done[7]) and not torch.equal(T._env_spawn_pos[7], old)
+
+
+def test_respawn_on_a_tile(hostemu_lib):
+    """go2_eval_walk.py:417-439 respawn_on_tile on a tile grid: centre of the chosen (clamped) tile, z from the (blind) height query."""
+    from go2_b200 import eval as g2eval
+
+    env = make_env("walk_terrain", _grid_cfgs(), 6, "hostemu", hostemu_lib, seed=4)
+    env.reset()
+    T = env.terrain
+    g2eval.respawn(env, [1, 4], tile=(1, 7))  # column clamped to the last one
+    q = env.core.buf["qpos"]
+    want = T._tile_centers[1, 2]
+    for e in (1, 4):
+        assert float(q[e, 0]) == float(want[0]) and float(q[e, 1]) == float(want[1]) and abs(float(q[e, 2]) - (0.45 + 0.05)) < 1e-6
+        assert torch.equal(T._env_spawn_pos[e], q[e, :3]) and int(T._env_tile_row[e]) == 1 and int(T._env_tile_col[e]) == 2
+        assert T.get_terrain_type_string(e) == "stairs_terrain" and int(env.episode_length_buf[e]) == 0
+    keep = T._env_spawn_pos[0].clone()
+    g2eval.respawn(env, [0])  # tile=None: back to the centre of the env's own tile
+    r, c = int(T._env_tile_row[0]), int(T._env_tile_col[0])
+    assert torch.allclose(env.core.buf["qpos"][0, :2], T._tile_centers[r, c, :2]) and (T._tile_of(0, 6.0, 2)[0] == r)
+    assert not torch.equal(keep, T._env_spawn_pos[0]) or torch.allclose(keep[:2], T._tile_centers[r, c, :2])
