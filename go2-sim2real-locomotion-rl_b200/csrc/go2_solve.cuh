@@ -814,7 +814,7 @@ constexpr int MAX_RANK1 = 6;  // more flips than this in one Newton iteration ->
 
 // Block-wide "does any thread still iterate": keeps the warps of a block in the same Newton iteration so that
 // they share instruction fetches (the solver body is ~60 KB of straight-line code).  Host: a single env.
-#if defined(__CUDA_ARCH__) && defined(G2_WARP_ASYNC)  // experiment: warps run free of each other (profiles/r02_experiments.md)
+#if defined(__CUDA_ARCH__) && (defined(G2_WARP_ASYNC) || defined(G2_WARP_NEWTON))  // experiments: warps run free of each other / only inside the Newton loop (profiles/r02_experiments.md)
 #define G2_BLOCK_ANY(x) (__any_sync(0xffffffffu, (x)) != 0)
 #elif defined(__CUDA_ARCH__)
 #define G2_BLOCK_ANY(x) (__syncthreads_or((x) ? 1 : 0) != 0)
